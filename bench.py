@@ -1,0 +1,350 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the paged-KV decode-attention hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3] [--impl ours|reference]
+    torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...      (N > 1)
+
+A "step" is ONE decode-attention call of one layer over one synthetic batch:
+store_kvcache of the batch's new tokens, then paged decode attention (split kernel + combine)
+[+ NCCL all-gather of the per-rank heads when N > 1].  tokens/s = batch / step time, the
+definition of reference benchmark_models.py:161.  Default workload: BASELINE.json configs[2]
+("c3": Qwen3-8B shape, batch 256, contexts 1k-8k, bf16) — the config the north star's roofline
+target is quoted on.  N > 1 runs the SAME batch sharded by KV head (strong scaling).
+
+Prints ONE JSON line (rank 0).  Keys beyond the base contract:
+  roofline      dominant kernel (the split-KV decode kernel): algorithmic bytes per launch /
+                CUDA-event duration of that launch, against MEASURED_PEAKS.json
+  cpu_baseline  the oracle port of the reference's vectorised-PyTorch CPU path, bounded sample
+  e2e           same metric through the host-buffer C-ABI entry (pinned H2D + D2H every step)
+--impl reference times that CPU path alone (rank 0; other ranks exit 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+import workloads  # noqa: E402
+
+METRIC = "decode attn tokens/s (HBM GB/s and % of B200 peak in roofline)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--workload", default="c3", choices=sorted(workloads.SPECS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--chunk", type=int, default=0, help="split size override (tokens)")
+    ap.add_argument("--cpu-seqs", type=int, default=8, help="sequences in the CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------ clocks during the timed region
+class ClockSampler:
+    REASONS = {
+        0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+        0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+        0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting",
+    }
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                mask = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.01)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons - {"gpu_idle"}), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------ CPU baseline (oracle port)
+def cpu_sample(t: workloads.Tables, nseq: int):
+    """A bounded sample of the workload on CPU: ``nseq`` evenly strided sequences with a compacted
+    block pool (only the blocks those sequences reference)."""
+    sp = t.spec
+    B = len(t.ctx)
+    pick = np.unique(np.linspace(0, B - 1, min(nseq, B)).astype(np.int64))
+    ctx = t.ctx[pick]
+    nblk = (ctx + sp.BS - 1) // sp.BS
+    used = np.unique(np.concatenate([t.tables[b, :n] for b, n in zip(pick, nblk)]))
+    remap = np.full(t.num_blocks, -1, dtype=np.int32)
+    remap[used] = np.arange(len(used), dtype=np.int32)
+    width = int(nblk.max())
+    tables = np.full((len(pick), width), -1, dtype=np.int32)
+    for i, (b, n) in enumerate(zip(pick, nblk)):
+        tables[i, :n] = remap[t.tables[b, :n]]
+    dt = {"f32": torch.float32, "bf16": torch.bfloat16, "f16": torch.float16}[sp.dtype]
+    g = torch.Generator().manual_seed(sp.seed)
+    q = torch.randn(len(pick), sp.H, sp.D, generator=g).to(dt)
+    kc = torch.randn(len(used), sp.BS, sp.KVH, sp.D, generator=g).to(dt)
+    vc = torch.randn(len(used), sp.BS, sp.KVH, sp.D, generator=g).to(dt)
+    return dict(q=q, k_cache=kc, v_cache=vc, block_tables=torch.from_numpy(tables),
+                context_lens=torch.from_numpy(ctx), scale=1.0 / sp.D ** 0.5, H=sp.H, KVH=sp.KVH,
+                D=sp.D, BS=sp.BS, n=len(pick), tokens=int(ctx.sum()))
+
+
+def cpu_step(s):
+    from oracle import paged_attention_oracle as po  # the checker, used here only as CPU baseline
+    return po.decode_attention_padded(s["q"], s["k_cache"], s["v_cache"], s["block_tables"],
+                                      s["context_lens"], s["scale"], s["H"], s["KVH"], s["D"], s["BS"])
+
+
+def time_cpu(s, steps: int, warmup: int, budget_s: float = 1e9):
+    torch.set_num_threads(os.cpu_count() or 1)
+    for _ in range(warmup):
+        cpu_step(s)
+    t0 = time.perf_counter()
+    done = 0
+    for _ in range(steps):
+        cpu_step(s)
+        done += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    return (time.perf_counter() - t0) / done, done
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    t = workloads.build_tables(args.workload)
+    s = cpu_sample(t, args.cpu_seqs)
+    warm = max(args.warmup, 1)
+    per_step, done = time_cpu(s, args.steps, min(warm, 3), budget_s=240.0)
+    value = s["n"] / per_step
+    sample = (f"{s['n']} of {len(t.ctx)} sequences of workload {args.workload} (evenly strided, "
+              f"{s['tokens']} context tokens) per step; {done} steps")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": args.gpus,
+        "steps": done, "warmup": min(warm, 3), "ms_per_step": per_step * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": t.spec.dtype, "data": "synthetic",
+        "config": {"workload": args.workload, "shape": f"{t.spec.H}Q/{t.spec.KVH}KV/D{t.spec.D}",
+                   "block_size": t.spec.BS, "batch": len(t.ctx), "path": "oracle port of "
+                   "decode_torch_optimized (vectorised PyTorch, CPU)"},
+        "cpu_baseline": {"value": value, "unit": "tokens/s", "cores": torch.get_num_threads(),
+                         "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ the CUDA arm
+def run_ours(args, rank, world, local_rank):
+    import torch.distributed as dist
+
+    from minivllm_b200 import _ext
+    from minivllm_b200.head_shard import gather_heads, shard_plan
+    from minivllm_b200.layers.attention import HostDecodeStep, paged_attention_decode, store_kvcache
+
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    t = workloads.build_tables(args.workload)
+    sp = t.spec
+    sh = shard_plan(sp.H, sp.KVH, world, rank)
+    w = workloads.materialize(t, dev, kv_heads=sh.kv_heads, seed_offset=rank)
+    B = w["B"]
+    out = torch.empty_like(w["q"])
+    staging = torch.empty((world, B, w["H"], w["D"]), dtype=out.dtype, device=dev) if world > 1 else None
+    dec_args = (w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"], w["H"],
+                w["KVH"], w["D"], w["BS"])
+    lib = _ext.lib()
+    code = {"f32": 0, "f16": 1, "bf16": 2}[sp.dtype]
+    chunk = args.chunk or lib.mvl_paged_decode_default_chunk(B, w["H"], w["KVH"], w["D"],
+                                                             t.tables.shape[1], w["BS"], code)
+    multi_split = t.tables.shape[1] * sp.BS > chunk
+
+    def step(ev=None):
+        store_kvcache(w["k"], w["v"], w["k_cache"], w["v_cache"], w["slot_mapping"], w["BS"])
+        if ev is not None:
+            ev[0].record()
+        paged_attention_decode(w["q"], *dec_args, out=out, chunk_tokens=args.chunk,
+                               flags=_ext.DECODE_SKIP_COMBINE)
+        if ev is not None:
+            ev[1].record()
+        if multi_split:
+            paged_attention_decode(w["q"], *dec_args, out=out, chunk_tokens=args.chunk,
+                                   flags=_ext.DECODE_ONLY_COMBINE)
+        if world > 1:
+            return gather_heads(out, staging=staging)
+        return out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
+        step()
+    barrier()
+    K = args.steps
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        barrier()
+        e0.record()
+        for i in range(K):
+            step(kev[i])
+        e1.record()
+        barrier()
+    ms_total = e0.elapsed_time(e1)
+    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
+    if world > 1:
+        red = torch.tensor([ms_total, kern_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(red, op=dist.ReduceOp.MAX)
+        ms_total, kern_ms = red.tolist()
+    ms_step = ms_total / K
+    value = B / (ms_step * 1e-3)
+
+    # ---- end-to-end through the host-buffer C-ABI entry (pinned H2D + D2H inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        hs = HostDecodeStep(w["k_cache"], w["v_cache"], B, t.tables.shape[1], w["H"], w["scale"],
+                            index_dtype=torch.int64, chunk_tokens=args.chunk)
+        hs.q_h.copy_(w["q"].cpu()), hs.k_h.copy_(w["k"].cpu()), hs.v_h.copy_(w["v"].cpu())
+        hs.slot_h.copy_(w["slot_mapping"].cpu()), hs.ctx_h.copy_(w["context_lens"].cpu())
+        hs.bt_h.copy_(w["block_tables"].cpu())
+        for _ in range(3):
+            hs()
+        ke = max(K // 4, min(K, 10))
+        barrier()
+        h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        checksum = 0.0
+        h0.record()
+        for _ in range(ke):
+            res = hs()                       # synchronises: the host reads the result every step
+            checksum += float(res[0, 0, 0])
+        h1.record()
+        barrier()
+        e2e_ms = h0.elapsed_time(h1) / ke
+        if world > 1:
+            red = torch.tensor([e2e_ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(red, op=dist.ReduceOp.MAX)
+            e2e_ms = float(red[0])
+        e2e = {"value": B / (e2e_ms * 1e-3), "unit": "tokens/s", "ms_per_step": e2e_ms, "steps": ke,
+               "h2d_bytes_per_step": hs.h2d_bytes, "d2h_bytes_per_step": hs.d2h_bytes,
+               "api": "HostDecodeStep -> mvl_decode_step_host (per rank: its head shard)"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peaks()
+    alg = workloads.algorithmic_bytes(t, kvh_local=w["KVH"], h_local=w["H"])
+    alg_unique = workloads.algorithmic_bytes(t, kvh_local=w["KVH"], h_local=w["H"], unique=True)
+    achieved = alg_unique / (kern_ms * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": "paged_decode_split_kernel", "achieved": achieved, "peak": peak,
+            "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": alg_unique, "logical_bytes_per_launch": alg,
+            "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / ms_step,
+            "frac_of_nominal_8TBs": achieved / 8000.0}
+    prof = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof):
+        try:
+            with open(prof) as f:
+                roof["traffic"] = json.load(f).get(args.workload)
+        except Exception:
+            pass
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        s = cpu_sample(t, args.cpu_seqs)
+        per_step, done = time_cpu(s, 50, 1, budget_s=15.0)
+        cpu = {"value": s["n"] / per_step, "unit": "tokens/s", "cores": torch.get_num_threads(),
+               "kind": "port", "ms_per_sample": per_step * 1e3,
+               "sample": f"{s['n']} of {B} sequences (evenly strided, {s['tokens']} context tokens), "
+                         f"{done} repetitions, oracle port of decode_torch_optimized in {sp.dtype}"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": world, "steps": K,
+        "warmup": warm, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": sp.dtype, "data": "synthetic",
+        "config": {"workload": args.workload, "shape": f"{sp.H}Q/{sp.KVH}KV/D{sp.D}", "batch": B,
+                   "block_size": sp.BS, "context_tokens": int(t.ctx.sum()),
+                   "context_range": [int(t.ctx.min()), int(t.ctx.max())], "chunk_tokens": int(chunk),
+                   "parallelism": f"kv-head-shard x{world}" + (" + NCCL all-gather" if world > 1 else ""),
+                   "l2": "inputs larger than L2 (KV bytes per step >> 126 MB); no flush needed"
+                         if alg_unique > 4 * 126e6 else "KV fits in L2: number is L2-assisted"},
+        "hbm_gbs_step": alg_unique / (ms_step * 1e-3) / 1e9,
+        "roofline": roof, "cpu_baseline": cpu, "e2e": e2e,
+        "gpu_launches": K * (3 if multi_split else 2),
+        "clocks": clocks.summary(),
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world != args.gpus:
+        if args.gpus != 1 or world != 1:
+            raise SystemExit(f"--gpus {args.gpus} needs torchrun with {args.gpus} ranks (WORLD_SIZE={world})")
+    run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,146 @@
+/*
+ * mvl_abi.h — C ABI of libmvl_b200.so: paged-KV decode attention for MinivLLM on B200 (sm_100a).
+ *
+ * This is the drop-in boundary. The reference has no native layer: its Python host code hands
+ * torch tensors to Triton JIT kernels (reference src/myvllm/layers/attention.py:97-108 and
+ * :455-471).  Here the same Python host code (minivllm_b200/layers/attention.py) hands raw device
+ * pointers and sizes to the functions below through ctypes.  No torch types, no C++ types, no
+ * exceptions cross this boundary.
+ *
+ * Conventions
+ *   - Every function returns MVL_OK (0) or a negative mvl_status; nothing throws or aborts.
+ *   - The library never allocates, frees or retains device memory.  Scratch memory ("workspace")
+ *     is owned by the caller and sized with mvl_paged_decode_workspace_bytes().
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  All work is
+ *     enqueued on it; no call synchronises the device or reads device memory on the host, and the
+ *     grid depends only on host-known sizes, so calls may be captured in a CUDA graph
+ *     (reference src/myvllm/engine/model_runner.py:317-369 captures the decode forward).
+ *   - All data pointers must be 16-byte aligned; rows (head_dim * elem size) are multiples of 16 B.
+ *   - KV-cache layout is the reference's: (num_blocks, block_size, num_kv_heads, head_dim),
+ *     contiguous (reference attention.py:22,52-56; model_runner.py:162).
+ */
+#ifndef MVL_ABI_H_
+#define MVL_ABI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MVL_ABI_VERSION 1
+
+typedef enum mvl_status {
+  MVL_OK = 0,
+  MVL_ERR_NULL_POINTER = -1,  /* a required pointer is NULL */
+  MVL_ERR_DTYPE = -2,         /* elem_dtype is not one of mvl_dtype */
+  MVL_ERR_SHAPE = -3,         /* head_dim / head counts / block_size / sizes not supported */
+  MVL_ERR_ALIGNMENT = -4,     /* a pointer or stride is not 16-byte aligned */
+  MVL_ERR_WORKSPACE = -5,     /* workspace missing or smaller than ..._workspace_bytes() */
+  MVL_ERR_CUDA = -6,          /* a CUDA runtime call / launch failed; see mvl_last_cuda_error() */
+  MVL_ERR_LIMIT = -7          /* a size exceeds a documented fixed limit */
+} mvl_status;
+
+typedef enum mvl_dtype {
+  MVL_DTYPE_F32 = 0,
+  MVL_DTYPE_F16 = 1,
+  MVL_DTYPE_BF16 = 2
+} mvl_dtype;
+
+/* Flags for mvl_paged_decode (bit mask). */
+#define MVL_DECODE_SKIP_COMBINE 1u /* profiling only: launch the split kernel, not the combine */
+#define MVL_DECODE_ONLY_COMBINE 2u /* profiling only: launch the combine kernel alone */
+
+/* Library / ABI identification.  No reference counterpart (the reference has no native layer). */
+int mvl_abi_version(void);
+
+/* Human-readable text for an mvl_status. */
+const char* mvl_strerror(int status);
+
+/* Text of the last CUDA error seen by the calling thread inside this library ("" if none). */
+const char* mvl_last_cuda_error(void);
+
+/*
+ * mvl_store_kvcache — slot-mapped scatter of new K/V rows into the paged cache.
+ * Replaces: store_kvcache() + store_kvcache_kernel, reference attention.py:67-108 and :7-64.
+ *
+ *   for t in [0, num_tokens):  s = slot_mapping[t];  if s < 0 (reference: == -1) skip;
+ *     k_cache.view(-1, KVH, D)[s] = key[t];  v_cache.view(-1, KVH, D)[s] = value[t]
+ *
+ * key/value: (num_tokens, num_kv_heads, head_dim), head dims contiguous, token stride given in
+ * ELEMENTS (so the q/k/v split views of reference qwen3.py:86-101 need no .contiguous() copy).
+ * slot_mapping: int32 or int64 (engine uses int64, model_runner.py:252).  num_slots =
+ * num_blocks * block_size; slots >= num_slots are skipped (memory safety; the reference would
+ * write out of bounds).  Bit-exact copy; cache bytes of untouched slots are not written.
+ */
+int mvl_store_kvcache(const void* key, const void* value, void* k_cache, void* v_cache,
+                      const void* slot_mapping, int slot_is_i64, int64_t num_tokens,
+                      int num_kv_heads, int head_dim, int64_t key_token_stride,
+                      int64_t value_token_stride, int64_t num_slots, int elem_dtype,
+                      void* stream);
+
+/*
+ * Split-KV planning.  A sequence's tokens are cut into chunks of `chunk_tokens`; each
+ * (sequence, kv head, chunk) is one CTA.  mvl_paged_decode_default_chunk() returns the chunk the
+ * library picks when the caller passes chunk_tokens = 0; it depends only on the arguments and the
+ * SM count of the current device.  Returns a negative mvl_status on bad arguments.
+ * No reference counterpart (the Triton kernel walks the whole context in one program,
+ * attention.py:323-326).
+ */
+int mvl_paged_decode_default_chunk(int64_t batch, int num_heads, int num_kv_heads, int head_dim,
+                                   int64_t max_num_blocks, int block_size, int elem_dtype);
+
+/* Bytes of scratch mvl_paged_decode needs for these sizes (0 if one chunk covers every row). */
+size_t mvl_paged_decode_workspace_bytes(int64_t batch, int num_heads, int num_kv_heads,
+                                        int head_dim, int64_t max_num_blocks, int block_size,
+                                        int elem_dtype, int chunk_tokens);
+
+/*
+ * mvl_paged_decode — block-table GQA decode attention over the paged cache, one query per row.
+ * Replaces: paged_attention_decode() + paged_attention_decode_kernel, reference
+ * attention.py:418-473 and :283-415 (same as benchmark_decoding.py:6-133).
+ *
+ *   out[b, h, :] = softmax_j( scale * <query[b,h,:], K[b,j,h/G,:]> ) @ V[b,:,h/G,:],
+ *   j in [0, context_lens[b]),  G = num_heads / num_kv_heads,
+ *   K[b,j] = k_cache[block_tables[b, j / block_size], j % block_size]      (attention.py:347-361)
+ *
+ * query/out: (batch, num_heads, head_dim) contiguous, elem_dtype.  block_tables: int32,
+ * row stride block_table_stride (elements), entries past ceil(ctx/block_size) are never read.
+ * context_lens: int32 or int64.  context_lens[b] <= 0 yields a zero row (the reference yields
+ * NaN, attention.py:411; such rows are CUDA-graph padding, model_runner.py:283).
+ * context_lens[b] is clamped to max_num_blocks * block_size.  Scores and softmax run in fp32;
+ * one rounding to elem_dtype on store.
+ * workspace: >= mvl_paged_decode_workspace_bytes(...) bytes, 16-byte aligned; may be NULL when
+ * that size is 0.  Calls sharing one workspace must be ordered on the stream.
+ */
+int mvl_paged_decode(void* out, const void* query, const void* k_cache, const void* v_cache,
+                     const int32_t* block_tables, const void* context_lens, int ctx_is_i64,
+                     int64_t batch, int64_t max_num_blocks, int64_t block_table_stride,
+                     int num_heads, int num_kv_heads, int head_dim, int block_size,
+                     int64_t num_blocks, float scale, int elem_dtype, void* workspace,
+                     size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream);
+
+/*
+ * mvl_decode_step_host — one decode-attention step of a layer driven from HOST buffers:
+ * async H2D of the step's inputs (pinned host memory recommended) into caller-provided device
+ * staging buffers, mvl_store_kvcache, mvl_paged_decode, async D2H of the result.  The caller
+ * synchronises the stream before reading out_host.  Mirrors what reference
+ * model_runner.py:231-256 (prepare_decode's H2D copies) + attention.py:493-557
+ * (Attention.forward decode branch) do per layer.  slot_mapping/context_lens are int64 when
+ * idx_is_i64 != 0 else int32.  Staging buffers must hold at least the host arrays' bytes.
+ */
+int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_host,
+                         const void* slot_mapping_host, const void* context_lens_host,
+                         const int32_t* block_tables_host, void* out_host, void* q_dev,
+                         void* k_dev, void* v_dev, void* slot_mapping_dev, void* context_lens_dev,
+                         int32_t* block_tables_dev, void* out_dev, void* k_cache, void* v_cache,
+                         int idx_is_i64, int64_t batch, int64_t max_num_blocks, int num_heads,
+                         int num_kv_heads, int head_dim, int block_size, int64_t num_blocks,
+                         float scale, int elem_dtype, void* workspace, size_t workspace_bytes,
+                         int chunk_tokens, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MVL_ABI_H_ */

@@ -1,0 +1,327 @@
+// abi.cu — the extern "C" surface of libmvl_b200.so (declared in include/mvl_abi.h):
+// argument validation -> status codes, split-KV planning, kernel dispatch.  No allocation, no
+// synchronisation, no host reads of device memory.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "host.h"
+#include "mvl_abi.h"
+
+namespace {
+
+thread_local char g_cuda_err[256] = "";
+
+int cuda_fail(cudaError_t e, const char* where) {
+  snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s (%s)", where, cudaGetErrorName(e),
+           cudaGetErrorString(e));
+  return MVL_ERR_CUDA;
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+int elem_size(int dtype) {
+  switch (dtype) {
+    case MVL_DTYPE_F32: return 4;
+    case MVL_DTYPE_F16:
+    case MVL_DTYPE_BF16: return 2;
+  }
+  return 0;
+}
+
+int ilog2_exact(long long v) {  // log2(v) if v is a power of two, else -1
+  if (v <= 0 || (v & (v - 1))) return -1;
+  int s = 0;
+  while ((1ll << s) < v) ++s;
+  return s;
+}
+
+// SM count of the current device, cached per device ordinal.
+int current_sm_count(int* out) {
+  static int cache[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+  if (dev >= 0 && dev < 64 && cache[dev] > 0) {
+    *out = cache[dev];
+    return MVL_OK;
+  }
+  int n = 0;
+  e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetAttribute");
+  if (dev >= 0 && dev < 64) cache[dev] = n;
+  *out = n;
+  return MVL_OK;
+}
+
+// Head tile: how many query heads of a GQA group one CTA carries (1, 2, 4 or 8).
+int pick_gt(int G) {
+  if (G >= 8) return 8;
+  if (G > 2) return 4;
+  return G;  // 1 or 2
+}
+
+int tile_rows(int dtype, int head_dim, int gt) {
+  switch (dtype) {
+    case MVL_DTYPE_F32: return mvl::decode_tile_rows<float>(head_dim, gt);
+    case MVL_DTYPE_F16: return mvl::decode_tile_rows<__half>(head_dim, gt);
+    case MVL_DTYPE_BF16: return mvl::decode_tile_rows<__nv_bfloat16>(head_dim, gt);
+  }
+  return -1;
+}
+
+struct Plan {
+  int gt, n_gt, tr, chunk, max_splits, bs_shift;
+  long long max_ctx;
+};
+
+constexpr int kWarps = 4;
+constexpr int kMaxChunk = 1024;
+
+// Shape checks shared by the planning entry points and mvl_paged_decode.
+int make_plan(long long batch, int H, int KVH, int D, long long max_num_blocks, int block_size,
+              int dtype, int chunk_req, int num_sms, Plan* pl) {
+  if (elem_size(dtype) == 0) return MVL_ERR_DTYPE;
+  if (batch < 0 || H <= 0 || KVH <= 0 || H % KVH != 0 || max_num_blocks <= 0) return MVL_ERR_SHAPE;
+  if (D != 64 && D != 128) return MVL_ERR_SHAPE;
+  const int bs_shift = ilog2_exact(block_size);
+  if (bs_shift < 0) return MVL_ERR_SHAPE;
+  const long long max_ctx = max_num_blocks * (long long)block_size;
+  if (max_ctx >= (1ll << 31) || batch > 65535) return MVL_ERR_LIMIT;
+  const int G = H / KVH;
+  pl->gt = pick_gt(G);
+  pl->n_gt = (G + pl->gt - 1) / pl->gt;
+  pl->tr = tile_rows(dtype, D, pl->gt);
+  if (pl->tr <= 0) return MVL_ERR_SHAPE;
+  pl->bs_shift = bs_shift;
+  pl->max_ctx = max_ctx;
+  const int cta_rows = pl->tr * kWarps;  // tokens one CTA consumes per round of its warps
+  int chunk;
+  if (chunk_req > 0) {
+    chunk = ((chunk_req + cta_rows - 1) / cta_rows) * cta_rows;
+  } else {
+    // Aim for >= 6 CTAs per SM over the worst-case token count, within [cta_rows, kMaxChunk].
+    const double units = (double)(batch > 0 ? batch : 1) * KVH * pl->n_gt;
+    const double want = units * (double)max_ctx / ((double)num_sms * 6.0);
+    chunk = cta_rows;
+    while (chunk < kMaxChunk && chunk < want) chunk *= 2;
+  }
+  if ((long long)chunk > ((max_ctx + cta_rows - 1) / cta_rows) * cta_rows)
+    chunk = (int)(((max_ctx + cta_rows - 1) / cta_rows) * cta_rows);
+  pl->chunk = chunk;
+  const long long splits = (max_ctx + chunk - 1) / chunk;
+  if (splits > 65535) return MVL_ERR_LIMIT;
+  pl->max_splits = (int)splits;
+  return MVL_OK;
+}
+
+size_t plan_workspace(const Plan& pl, long long batch, int H, int D) {
+  if (pl.max_splits <= 1) return 0;
+  const size_t rows = (size_t)batch * H * pl.max_splits;
+  return rows * D * sizeof(float) + rows * sizeof(float2);
+}
+
+}  // namespace
+
+extern "C" {
+
+int mvl_abi_version(void) { return MVL_ABI_VERSION; }
+
+const char* mvl_strerror(int status) {
+  switch (status) {
+    case MVL_OK: return "ok";
+    case MVL_ERR_NULL_POINTER: return "a required pointer is NULL";
+    case MVL_ERR_DTYPE: return "unsupported element dtype (expect f32, f16 or bf16)";
+    case MVL_ERR_SHAPE:
+      return "unsupported shape (head_dim in {64,128}, num_heads % num_kv_heads == 0, "
+             "power-of-two block_size, positive sizes)";
+    case MVL_ERR_ALIGNMENT: return "pointer or stride not 16-byte aligned";
+    case MVL_ERR_WORKSPACE: return "workspace is NULL or smaller than mvl_paged_decode_workspace_bytes()";
+    case MVL_ERR_CUDA: return "CUDA error (see mvl_last_cuda_error())";
+    case MVL_ERR_LIMIT: return "size exceeds a fixed limit (batch <= 65535, context < 2^31, splits <= 65535)";
+  }
+  return "unknown mvl_status";
+}
+
+const char* mvl_last_cuda_error(void) { return g_cuda_err; }
+
+int mvl_store_kvcache(const void* key, const void* value, void* k_cache, void* v_cache,
+                      const void* slot_mapping, int slot_is_i64, int64_t num_tokens,
+                      int num_kv_heads, int head_dim, int64_t key_token_stride,
+                      int64_t value_token_stride, int64_t num_slots, int elem_dtype,
+                      void* stream) {
+  const int es = elem_size(elem_dtype);
+  if (es == 0) return MVL_ERR_DTYPE;
+  if (num_tokens < 0 || num_kv_heads <= 0 || head_dim <= 0 || num_slots < 0) return MVL_ERR_SHAPE;
+  if (num_tokens == 0) return MVL_OK;
+  if (!key || !value || !k_cache || !v_cache || !slot_mapping) return MVL_ERR_NULL_POINTER;
+  const long long row_bytes = (long long)num_kv_heads * head_dim * es;
+  if (row_bytes % 16 != 0 || row_bytes / 16 > 0x7fffffffll) return MVL_ERR_SHAPE;
+  if (key_token_stride < (long long)num_kv_heads * head_dim ||
+      value_token_stride < (long long)num_kv_heads * head_dim)
+    return MVL_ERR_SHAPE;
+  if ((key_token_stride * es) % 16 != 0 || (value_token_stride * es) % 16 != 0 ||
+      !aligned16(key) || !aligned16(value) || !aligned16(k_cache) || !aligned16(v_cache))
+    return MVL_ERR_ALIGNMENT;
+  int sms = 0;
+  int st = current_sm_count(&sms);
+  if (st != MVL_OK) return st;
+  mvl::launch_store_kvcache(key, value, k_cache, v_cache, slot_mapping, slot_is_i64, num_tokens,
+                            (int)(row_bytes / 16), key_token_stride * es / 16,
+                            value_token_stride * es / 16, num_slots, sms, (cudaStream_t)stream);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "store_kvcache launch");
+  return MVL_OK;
+}
+
+int mvl_paged_decode_default_chunk(int64_t batch, int num_heads, int num_kv_heads, int head_dim,
+                                   int64_t max_num_blocks, int block_size, int elem_dtype) {
+  int sms = 0;
+  int st = current_sm_count(&sms);
+  if (st != MVL_OK) return st;
+  Plan pl;
+  st = make_plan(batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, elem_dtype, 0,
+                 sms, &pl);
+  return st != MVL_OK ? st : pl.chunk;
+}
+
+size_t mvl_paged_decode_workspace_bytes(int64_t batch, int num_heads, int num_kv_heads,
+                                        int head_dim, int64_t max_num_blocks, int block_size,
+                                        int elem_dtype, int chunk_tokens) {
+  int sms = 0;
+  if (current_sm_count(&sms) != MVL_OK) return 0;
+  Plan pl;
+  if (make_plan(batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, elem_dtype,
+                chunk_tokens, sms, &pl) != MVL_OK)
+    return 0;
+  return plan_workspace(pl, batch, num_heads, head_dim);
+}
+
+int mvl_paged_decode(void* out, const void* query, const void* k_cache, const void* v_cache,
+                     const int32_t* block_tables, const void* context_lens, int ctx_is_i64,
+                     int64_t batch, int64_t max_num_blocks, int64_t block_table_stride,
+                     int num_heads, int num_kv_heads, int head_dim, int block_size,
+                     int64_t num_blocks, float scale, int elem_dtype, void* workspace,
+                     size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream) {
+  int sms = 0;
+  int st = current_sm_count(&sms);
+  if (st != MVL_OK) return st;
+  Plan pl;
+  st = make_plan(batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, elem_dtype,
+                 chunk_tokens, sms, &pl);
+  if (st != MVL_OK) return st;
+  if (batch == 0) return MVL_OK;
+  if (num_blocks <= 0 || block_table_stride < max_num_blocks) return MVL_ERR_SHAPE;
+  if (!out || !query || !k_cache || !v_cache || !block_tables || !context_lens)
+    return MVL_ERR_NULL_POINTER;
+  if (!aligned16(out) || !aligned16(query) || !aligned16(k_cache) || !aligned16(v_cache) ||
+      (reinterpret_cast<uintptr_t>(block_tables) & 3u) ||
+      (reinterpret_cast<uintptr_t>(context_lens) & (ctx_is_i64 ? 7u : 3u)))
+    return MVL_ERR_ALIGNMENT;
+  const size_t need = plan_workspace(pl, batch, num_heads, head_dim);
+  if (need > 0 && (!workspace || workspace_bytes < need)) return MVL_ERR_WORKSPACE;
+  if (need > 0 && !aligned16(workspace)) return MVL_ERR_ALIGNMENT;
+
+  mvl::DecodeParams p;
+  memset(&p, 0, sizeof(p));
+  p.out = out;
+  p.q = query;
+  p.kc = k_cache;
+  p.vc = v_cache;
+  p.bt = block_tables;
+  p.ctx = context_lens;
+  const size_t rows = (size_t)batch * num_heads * pl.max_splits;
+  p.part_o = reinterpret_cast<float*>(workspace);
+  p.part_ml = need ? reinterpret_cast<float2*>(reinterpret_cast<char*>(workspace) +
+                                               rows * head_dim * sizeof(float))
+                   : nullptr;
+  p.bt_stride = block_table_stride;
+  p.max_ctx = pl.max_ctx;
+  p.ctx_is_i64 = ctx_is_i64 ? 1 : 0;
+  p.H = num_heads;
+  p.KVH = num_kv_heads;
+  p.G = num_heads / num_kv_heads;
+  p.n_gt = pl.n_gt;
+  p.bs_shift = pl.bs_shift;
+  p.chunk = pl.chunk;
+  p.max_splits = pl.max_splits;
+  p.qscale = scale * 1.4426950408889634f;
+
+  cudaStream_t s = (cudaStream_t)stream;
+  if (!(flags & MVL_DECODE_ONLY_COMBINE)) {
+    dim3 grid((unsigned)(num_kv_heads * pl.n_gt), (unsigned)pl.max_splits, (unsigned)batch);
+    int e = -1000;
+    switch (elem_dtype) {
+      case MVL_DTYPE_F32: e = mvl::launch_decode_split<float>(p, head_dim, pl.gt, grid, s); break;
+      case MVL_DTYPE_F16: e = mvl::launch_decode_split<__half>(p, head_dim, pl.gt, grid, s); break;
+      case MVL_DTYPE_BF16:
+        e = mvl::launch_decode_split<__nv_bfloat16>(p, head_dim, pl.gt, grid, s);
+        break;
+    }
+    if (e == -1000) return MVL_ERR_SHAPE;
+    if (e != 0) return cuda_fail((cudaError_t)e, "paged_decode_split launch");
+  }
+  if (pl.max_splits > 1 && !(flags & MVL_DECODE_SKIP_COMBINE)) {
+    const long long bh = (long long)batch * num_heads;
+    int e = -1000;
+    switch (elem_dtype) {
+      case MVL_DTYPE_F32: e = mvl::launch_decode_combine<float>(p, head_dim, bh, s); break;
+      case MVL_DTYPE_F16: e = mvl::launch_decode_combine<__half>(p, head_dim, bh, s); break;
+      case MVL_DTYPE_BF16: e = mvl::launch_decode_combine<__nv_bfloat16>(p, head_dim, bh, s); break;
+    }
+    if (e == -1000) return MVL_ERR_SHAPE;
+    if (e != 0) return cuda_fail((cudaError_t)e, "paged_decode_combine launch");
+  }
+  return MVL_OK;
+}
+
+int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_host,
+                         const void* slot_mapping_host, const void* context_lens_host,
+                         const int32_t* block_tables_host, void* out_host, void* q_dev,
+                         void* k_dev, void* v_dev, void* slot_mapping_dev, void* context_lens_dev,
+                         int32_t* block_tables_dev, void* out_dev, void* k_cache, void* v_cache,
+                         int idx_is_i64, int64_t batch, int64_t max_num_blocks, int num_heads,
+                         int num_kv_heads, int head_dim, int block_size, int64_t num_blocks,
+                         float scale, int elem_dtype, void* workspace, size_t workspace_bytes,
+                         int chunk_tokens, void* stream) {
+  const int es = elem_size(elem_dtype);
+  if (es == 0) return MVL_ERR_DTYPE;
+  if (batch < 0 || num_heads <= 0 || num_kv_heads <= 0 || head_dim <= 0 || max_num_blocks <= 0)
+    return MVL_ERR_SHAPE;
+  if (batch == 0) return MVL_OK;
+  if (!q_host || !k_host || !v_host || !slot_mapping_host || !context_lens_host ||
+      !block_tables_host || !out_host || !q_dev || !k_dev || !v_dev || !slot_mapping_dev ||
+      !context_lens_dev || !block_tables_dev || !out_dev)
+    return MVL_ERR_NULL_POINTER;
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t qb = (size_t)batch * num_heads * head_dim * es;
+  const size_t kb = (size_t)batch * num_kv_heads * head_dim * es;
+  const size_t ib = (size_t)batch * (idx_is_i64 ? 8 : 4);
+  const size_t tb = (size_t)batch * max_num_blocks * sizeof(int32_t);
+  cudaError_t e;
+#define MVL_H2D(dst, src, n)                                          \
+  e = cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, s);        \
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync H2D " #dst)
+  MVL_H2D(q_dev, q_host, qb);
+  MVL_H2D(k_dev, k_host, kb);
+  MVL_H2D(v_dev, v_host, kb);
+  MVL_H2D(slot_mapping_dev, slot_mapping_host, ib);
+  MVL_H2D(context_lens_dev, context_lens_host, ib);
+  MVL_H2D(block_tables_dev, block_tables_host, tb);
+#undef MVL_H2D
+  int st = mvl_store_kvcache(k_dev, v_dev, k_cache, v_cache, slot_mapping_dev, idx_is_i64, batch,
+                             num_kv_heads, head_dim, (int64_t)num_kv_heads * head_dim,
+                             (int64_t)num_kv_heads * head_dim, num_blocks * block_size, elem_dtype,
+                             stream);
+  if (st != MVL_OK) return st;
+  st = mvl_paged_decode(out_dev, q_dev, k_cache, v_cache, block_tables_dev, context_lens_dev,
+                        idx_is_i64, batch, max_num_blocks, max_num_blocks, num_heads, num_kv_heads,
+                        head_dim, block_size, num_blocks, scale, elem_dtype, workspace,
+                        workspace_bytes, chunk_tokens, 0u, stream);
+  if (st != MVL_OK) return st;
+  e = cudaMemcpyAsync(out_host, out_dev, qb, cudaMemcpyDeviceToHost, s);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync D2H out");
+  return MVL_OK;
+}
+
+}  // extern "C"

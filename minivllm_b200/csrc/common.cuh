@@ -1,0 +1,167 @@
+// common.cuh — small device helpers shared by the sm_100a kernels of libmvl_b200.
+// Everything here is written for sm_100a only (packed fp32 FFMA2, cp.async, TMA bulk copies).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mvl {
+
+typedef unsigned long long u64;
+
+// ---------------------------------------------------------------- packed fp32 pairs (FFMA2)
+__device__ __forceinline__ u64 pack2(float lo, float hi) {
+  u64 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+// d = a * b + c on two fp32 lanes with one instruction (SASS: FFMA2).
+__device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {
+  u64 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ u64 fmul2(u64 a, u64 b) {
+  u64 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ float hsum2(u64 v) {
+  float lo, hi;
+  unpack2(v, lo, hi);
+  return lo + hi;
+}
+
+// ---------------------------------------------------------------- shared-memory access by address
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ uint4 lds128(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint2 lds64(uint32_t a) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, uint4 v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w));
+}
+__device__ __forceinline__ void sts64(uint32_t a, uint2 v) {
+  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a), "r"(v.x), "r"(v.y));
+}
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v));
+}
+
+// ---------------------------------------------------------------- cp.async (SASS: LDGSTS)
+// 16-byte global->shared copy that bypasses L1; src_bytes = 0 zero-fills the destination.
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src),
+               "r"(src_bytes)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// ---------------------------------------------------------------- 16-byte chunk -> fp32 pairs
+// A 16-byte chunk of the KV cache holds VEC elements; it is widened to VEC/2 packed fp32 pairs.
+template <typename T>
+struct Chunk;
+
+template <>
+struct Chunk<__nv_bfloat16> {
+  static constexpr int VEC = 8;
+  static constexpr int NP = 4;
+  // bf16 -> fp32 is a 16-bit shift: low half (w << 16), high half (w & 0xffff0000).
+  static __device__ __forceinline__ void widen(const uint4& v, u64 (&p)[4]) {
+    p[0] = pack2(__uint_as_float(v.x << 16), __uint_as_float(v.x & 0xffff0000u));
+    p[1] = pack2(__uint_as_float(v.y << 16), __uint_as_float(v.y & 0xffff0000u));
+    p[2] = pack2(__uint_as_float(v.z << 16), __uint_as_float(v.z & 0xffff0000u));
+    p[3] = pack2(__uint_as_float(v.w << 16), __uint_as_float(v.w & 0xffff0000u));
+  }
+  static __device__ __forceinline__ uint32_t narrow2(float lo, float hi) {
+    __nv_bfloat162 r = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&r);
+  }
+};
+
+template <>
+struct Chunk<__half> {
+  static constexpr int VEC = 8;
+  static constexpr int NP = 4;
+  static __device__ __forceinline__ u64 w2(uint32_t w) {
+    float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
+    return pack2(f.x, f.y);
+  }
+  static __device__ __forceinline__ void widen(const uint4& v, u64 (&p)[4]) {
+    p[0] = w2(v.x);
+    p[1] = w2(v.y);
+    p[2] = w2(v.z);
+    p[3] = w2(v.w);
+  }
+  static __device__ __forceinline__ uint32_t narrow2(float lo, float hi) {
+    __half2 r = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&r);
+  }
+};
+
+template <>
+struct Chunk<float> {
+  static constexpr int VEC = 4;
+  static constexpr int NP = 2;
+  static __device__ __forceinline__ void widen(const uint4& v, u64 (&p)[2]) {
+    p[0] = pack2(__uint_as_float(v.x), __uint_as_float(v.y));
+    p[1] = pack2(__uint_as_float(v.z), __uint_as_float(v.w));
+  }
+};
+
+// Store 4 consecutive fp32 results as 4 elements of T (16 B for fp32, 8 B for 16-bit types).
+template <typename T>
+__device__ __forceinline__ void store4(T* dst, float a, float b, float c, float d) {
+  uint2 v;
+  v.x = Chunk<T>::narrow2(a, b);
+  v.y = Chunk<T>::narrow2(c, d);
+  *reinterpret_cast<uint2*>(dst) = v;
+}
+template <>
+__device__ __forceinline__ void store4<float>(float* dst, float a, float b, float c, float d) {
+  *reinterpret_cast<float4*>(dst) = make_float4(a, b, c, d);
+}
+
+// Store 2 consecutive fp32 results as 2 elements of T.
+template <typename T>
+__device__ __forceinline__ void store2(T* dst, float a, float b) {
+  *reinterpret_cast<uint32_t*>(dst) = Chunk<T>::narrow2(a, b);
+}
+template <>
+__device__ __forceinline__ void store2<float>(float* dst, float a, float b) {
+  *reinterpret_cast<float2*>(dst) = make_float2(a, b);
+}
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+}  // namespace mvl

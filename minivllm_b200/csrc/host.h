@@ -1,0 +1,24 @@
+// host.h — internal (non-ABI) declarations shared by the translation units of libmvl_b200.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "paged_decode.cuh"
+
+namespace mvl {
+
+int launch_store_kvcache(const void* key, const void* value, void* k_cache, void* v_cache,
+                         const void* slot_mapping, int slot_is_i64, long long num_tokens,
+                         int chunks_per_row, long long key_stride16, long long value_stride16,
+                         long long num_slots, int num_sms, cudaStream_t stream);
+
+// Launchers, one translation unit per element type (keeps nvcc parallel and fast).
+// Return cudaSuccess (0) or the cudaError_t of the failed call; -1000 if (D, GT) is not built.
+template <typename T>
+int launch_decode_split(const DecodeParams& p, int head_dim, int gt, dim3 grid, cudaStream_t s);
+template <typename T>
+int launch_decode_combine(const DecodeParams& p, int head_dim, long long rows, cudaStream_t s);
+// Rows of one warp tile for (T, head_dim, gt): the chunk must be a multiple of 4 warps x this.
+template <typename T>
+int decode_tile_rows(int head_dim, int gt);
+
+}  // namespace mvl

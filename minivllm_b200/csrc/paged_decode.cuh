@@ -1,0 +1,493 @@
+// paged_decode.cuh — split-KV paged GQA decode attention for sm_100a (kernel templates).
+//
+// Replaces the reference's Triton kernel paged_attention_decode_kernel
+// (reference src/myvllm/layers/attention.py:283-415): same math, different machine mapping.
+//
+// Work decomposition
+//   grid = (num_kv_heads * head_tiles, max_splits, batch).  One CTA owns the tokens
+//   [split*chunk, min(ctx, (split+1)*chunk)) of one sequence for ONE kv head and ALL query heads of
+//   its GQA group (GT heads per tile), so every K/V byte is fetched from HBM once per group instead
+//   of once per query head (the reference's grid (batch, num_heads) re-reads it G times,
+//   attention.py:455).  CTAs whose chunk starts past the sequence's length exit at once, which is
+//   how ragged batches are handled under a host-fixed (graph-capturable) grid.
+//
+// Inside a CTA
+//   NW warps, each streaming its own interleaved tiles of TR rows (rows = tokens) through a private
+//   3-slot cp.async ring in shared memory (K tile, V tile, next K tile ... each 4 KB, 16-byte
+//   cp.async.cg, coalesced 128-bit lanes).  No block-level barrier in the streaming loop.
+//   A lane holds one 16-byte chunk of a row (VEC elements): LPR lanes cover a row, a warp covers
+//   RPP rows per pass and R passes per tile.  q (pre-scaled by scale*log2e) and the output
+//   accumulators live in registers as packed fp32 pairs; all FMAs are FFMA2.
+//   Scores: per-lane partial dot products are transposed through a swizzled shared buffer and summed
+//   so each lane owns VPL complete scores; the running maximum is only refreshed when a score exceeds
+//   it by more than 8 (log2 units), so the common path has no cross-lane max reduction.
+//   Probabilities are published to shared memory as (p,p) pairs and consumed by the P.V pass.
+//   At the end the NW warps' (m, l, o) states are merged through shared memory and the CTA writes
+//   either the final row (sequence fits one chunk) or an fp32 partial for the combine kernel.
+#pragma once
+#include "common.cuh"
+
+namespace mvl {
+
+struct DecodeParams {
+  void* out;
+  const void* q;
+  const void* kc;
+  const void* vc;
+  const int32_t* bt;
+  const void* ctx;
+  float* part_o;   // [batch][H][max_splits][D] fp32, un-normalised
+  float2* part_ml; // [batch][H][max_splits] (m in log2 units, l)
+  long long bt_stride;
+  long long max_ctx;  // max_num_blocks * block_size
+  int ctx_is_i64;
+  int H, KVH, G;
+  int n_gt;       // head tiles per kv head = ceil(G / GT)
+  int bs_shift;   // log2(block_size)
+  int chunk;      // tokens per split
+  int max_splits;
+  float qscale;      // scale * log2(e)
+};
+
+template <typename T, int D_, int GT_>
+struct DecodeCfg {
+  static constexpr int D = D_;
+  static constexpr int GT = GT_;
+  static constexpr int NW = 4;                  // warps per CTA
+  static constexpr int ES = sizeof(T);
+  static constexpr int VEC = Chunk<T>::VEC;     // elements per 16-byte chunk
+  static constexpr int NP = Chunk<T>::NP;       // fp32 pairs per chunk
+  static constexpr int LPR = D / VEC;           // lanes per row
+  static constexpr int RPP = 32 / LPR;          // rows per pass
+  static constexpr int R = (GT_ >= 8) ? 4 : 8;   // passes per tile
+  static constexpr int TR = R * RPP;            // rows per warp tile
+  static constexpr int ROWB = D * ES;           // bytes per row of one kv head
+  static constexpr int TILEB = TR * ROWB;       // bytes per K (or V) tile = R * 512
+  static constexpr int NV = R * GT;             // partial scores per lane and tile
+  static constexpr int NQ = NV / 4;             // ... in 16-byte quads
+  static constexpr int VPL = (NV / LPR) > 0 ? (NV / LPR) : 1;  // complete scores per lane
+  static constexpr int XB_BYTES = 32 * NV * 4;  // transpose buffer
+  static constexpr int PB_BYTES = TR * GT * 8;  // (p,p) pairs
+  static constexpr int RING = (GT_ >= 8) ? 5 : 3;  // ring slots; RING-1 half tiles in flight
+  static constexpr int WARP_SMEM = RING * TILEB + XB_BYTES + PB_BYTES;
+  static constexpr int SMEM = NW * WARP_SMEM;
+  static constexpr int MRG_BYTES = RPP * GT * D * 4 + GT * 8;  // merge area, aliases the ring
+  static_assert(LPR >= 8 && LPR <= 32, "head_dim / dtype combination not supported");
+  static_assert(MRG_BYTES <= RING * TILEB, "merge area must fit in the ring");
+  static_assert(NV % 4 == 0 && NQ >= 2, "NV must be a multiple of 8");
+};
+
+// XOR swizzle of the transpose buffer: lane L stores quad k at quad (k ^ key(L)).
+template <int NQ>
+__device__ __forceinline__ int xb_key(int L) {
+  if (NQ >= 8) return L & 7;
+  if (NQ == 4) return (L >> 1) & 3;
+  return (L >> 2) & 1;  // NQ == 2
+}
+
+// UNIFORM: every warp tile lies inside one page (block_size % TR == 0), so one block-table entry
+// addresses the whole tile; otherwise each row looks up its own page.
+template <typename T, int D, int GT, bool UNIFORM>
+__global__ void __launch_bounds__(DecodeCfg<T, D, GT>::NW * 32, (GT >= 8 ? 2 : 3))
+paged_decode_split_kernel(const DecodeParams p) {
+  using C = DecodeCfg<T, D, GT>;
+  constexpr int NP = C::NP, R = C::R, RPP = C::RPP, LPR = C::LPR, TR = C::TR, NV = C::NV,
+                NQ = C::NQ, VPL = C::VPL, NW = C::NW, ROWB = C::ROWB, TILEB = C::TILEB,
+                RING = C::RING;
+  extern __shared__ __align__(128) unsigned char smem[];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int h = lane / LPR, c = lane % LPR;
+  const int kvh = blockIdx.x / p.n_gt, gt = blockIdx.x % p.n_gt;
+  const int split = blockIdx.y, b = blockIdx.z;
+  const int head0 = kvh * p.G + gt * GT;
+  const int g_valid = min(GT, p.G - gt * GT);
+
+  long long ctx_ll = p.ctx_is_i64 ? reinterpret_cast<const long long*>(p.ctx)[b]
+                                  : (long long)reinterpret_cast<const int*>(p.ctx)[b];
+  if (ctx_ll > p.max_ctx) ctx_ll = p.max_ctx;
+  const int ctx = (int)ctx_ll;
+  T* out = reinterpret_cast<T*>(p.out);
+
+  if (ctx <= 0) {  // graph-padding row: defined as zeros (reference gives 0/0)
+    if (split == 0)
+      for (int i = threadIdx.x; i < g_valid * (D / 4); i += NW * 32) {
+        const int g = i / (D / 4), dq = i % (D / 4);
+        store4<T>(out + ((long long)b * p.H + head0 + g) * D + dq * 4, 0.f, 0.f, 0.f, 0.f);
+      }
+    return;
+  }
+  const int start = split * p.chunk;
+  if (start >= ctx) return;
+  const int end = min(ctx, start + p.chunk);
+  const int n_act = (ctx + p.chunk - 1) / p.chunk;
+
+  const uint32_t wbase = smem_u32(smem) + warp * C::WARP_SMEM;
+  const uint32_t ring = wbase;
+  const uint32_t xbuf = wbase + C::RING * TILEB;
+  const uint32_t pbuf = xbuf + C::XB_BYTES;
+
+  // ---- q for the GT heads of this tile, as packed fp32 pairs scaled by scale*log2(e)
+  u64 q2[GT][NP];
+  {
+    const u64 qs = pack2(p.qscale, p.qscale);
+#pragma unroll
+    for (int g = 0; g < GT; ++g) {
+      uint4 raw = make_uint4(0, 0, 0, 0);
+      if (g < g_valid)
+        raw = *reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.q) +
+                                              ((long long)b * p.H + head0 + g) * D + c * C::VEC);
+      Chunk<T>::widen(raw, q2[g]);
+#pragma unroll
+      for (int e = 0; e < NP; ++e) q2[g][e] = fmul2(q2[g][e], qs);
+    }
+  }
+
+  // ---- per-lane ownership of complete scores: slot i <-> (pass j_i, head g_i), row rr_i
+  int rr_s[VPL], g_s[VPL];
+  bool ok_s[VPL];
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int idx = c * VPL + i;
+    ok_s[i] = idx < NV;
+    g_s[i] = idx % GT;
+    rr_s[i] = (idx / GT) * RPP + h;
+  }
+  const int idx0 = (c * VPL < NV) ? c * VPL : 0;  // first owned score (clamped for idle lanes)
+
+  // ---- this warp's tiles: tile = warp, warp + NW, ...
+  const int ntiles = (end - start + TR - 1) / TR;
+  const int my_nt = (warp < ntiles) ? (ntiles - warp + NW - 1) / NW : 0;
+  const long long row_pitch = (long long)p.KVH * ROWB;  // bytes between consecutive slots
+  const int bs_mask = (1 << p.bs_shift) - 1;
+  const int32_t* bt_row = p.bt + (long long)b * p.bt_stride;
+  const char* kbase = reinterpret_cast<const char*>(p.kc) + (long long)kvh * ROWB + c * 16;
+  const char* vbase = reinterpret_cast<const char*>(p.vc) + (long long)kvh * ROWB + c * 16;
+
+  // Issue the n-th half tile (even: K of tile n/2, odd: V) into ring slot n % RING; always commits.
+  auto issue = [&](int n) {
+    if (n < 2 * my_nt) {
+      const int tstart = start + (warp + (n >> 1) * NW) * TR;
+      const char* base = (n & 1) ? vbase : kbase;
+      const uint32_t dst = ring + (n % RING) * TILEB + h * ROWB + c * 16;
+      if (UNIFORM) {
+        const long long blk = __ldg(bt_row + (tstart >> p.bs_shift));
+        const char* src = base + ((blk << p.bs_shift) + (tstart & bs_mask) + h) * row_pitch;
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+          const bool valid = tstart + j * RPP + h < end;
+          cp_async16(dst + j * RPP * ROWB, src + (long long)(j * RPP) * row_pitch, valid ? 16u : 0u);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+          const int t = tstart + j * RPP + h;
+          const bool valid = t < end;
+          const int tt = valid ? t : end - 1;
+          const long long blk = __ldg(bt_row + (tt >> p.bs_shift));
+          const char* src = base + ((blk << p.bs_shift) + (tt & bs_mask)) * row_pitch;
+          cp_async16(dst + j * RPP * ROWB, src, valid ? 16u : 0u);
+        }
+      }
+    }
+    cp_async_commit();
+  };
+
+#pragma unroll
+  for (int n = 0; n < RING - 1; ++n) issue(n);
+
+  float m_all[GT];
+  u64 o2[GT][NP];
+  float m_slot[VPL], l_slot[VPL];
+#pragma unroll
+  for (int g = 0; g < GT; ++g) {
+    m_all[g] = -INFINITY;
+#pragma unroll
+    for (int e = 0; e < NP; ++e) o2[g][e] = 0ull;
+  }
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    m_slot[i] = -INFINITY;
+    l_slot[i] = 0.f;
+  }
+
+  for (int it = 0; it < my_nt; ++it) {
+    const int tstart = start + (warp + it * NW) * TR;
+    // ================================================================ K: scores
+    cp_async_wait<RING - 2>();
+    __syncwarp();
+    issue(2 * it + RING - 1);
+    {
+      const uint32_t ks = ring + ((2 * it) % RING) * TILEB + h * ROWB + c * 16;
+      float sv[NV];
+      const int key = xb_key<NQ>(lane);
+      const uint32_t xrow = xbuf + lane * (NV * 4);
+#pragma unroll
+      for (int j = 0; j < R; ++j) {
+        u64 k2[NP];
+        Chunk<T>::widen(lds128(ks + j * RPP * ROWB), k2);
+#pragma unroll
+        for (int g = 0; g < GT; ++g) {
+          u64 acc = 0ull;
+#pragma unroll
+          for (int e = 0; e < NP; ++e) acc = ffma2(q2[g][e], k2[e], acc);
+          sv[j * GT + g] = hsum2(acc);
+        }
+        // publish the quads of partial scores completed by this pass (keeps few of them live)
+#pragma unroll
+        for (int k = (j * GT) / 4; k < ((j + 1) * GT) / 4; ++k) {
+          uint4 v = make_uint4(__float_as_uint(sv[4 * k]), __float_as_uint(sv[4 * k + 1]),
+                               __float_as_uint(sv[4 * k + 2]), __float_as_uint(sv[4 * k + 3]));
+          sts128(xrow + ((k ^ key) << 4), v);
+        }
+      }
+    }
+    __syncwarp();
+    float sc[VPL];
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) sc[i] = 0.f;
+    {
+      const int quad = idx0 >> 2, w = idx0 & 3;
+#pragma unroll
+      for (int cc = 0; cc < LPR; ++cc) {
+        // source lane L' = h*LPR + cc; its key depends only on cc (see xb_key and LPR >= 8)
+        const uint32_t a = xbuf + (h * LPR + cc) * (NV * 4) + ((quad ^ xb_key<NQ>(cc)) << 4) + w * 4;
+        if (VPL == 1) {
+          sc[0] += __uint_as_float(lds32(a));
+        } else if (VPL == 2) {
+          uint2 v = lds64(a);
+          sc[0] += __uint_as_float(v.x);
+          sc[1 % VPL] += __uint_as_float(v.y);
+        } else {
+          uint4 v = lds128(a);
+          sc[0] += __uint_as_float(v.x);
+          sc[1 % VPL] += __uint_as_float(v.y);
+          sc[2 % VPL] += __uint_as_float(v.z);
+          sc[3 % VPL] += __uint_as_float(v.w);
+        }
+      }
+    }
+    // ---- online softmax with a lazily refreshed maximum
+    bool need = false;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      const bool valid = ok_s[i] && (tstart + rr_s[i] < end);
+      sc[i] = valid ? sc[i] : -INFINITY;
+      need |= sc[i] > m_slot[i] + 8.f;
+    }
+    if (__any_sync(0xffffffffu, need)) {
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < VPL; ++i)
+        if (ok_s[i]) sts32(pbuf + (rr_s[i] * GT + g_s[i]) * 4, __float_as_uint(sc[i]));
+      __syncwarp();
+      float mx[GT];
+#pragma unroll
+      for (int g = 0; g < GT; ++g) mx[g] = m_all[g];
+#pragma unroll
+      for (int qd = 0; qd < TR * GT / 4; ++qd) {
+        uint4 v = lds128(pbuf + qd * 16);
+        mx[(4 * qd + 0) % GT] = fmaxf(mx[(4 * qd + 0) % GT], __uint_as_float(v.x));
+        mx[(4 * qd + 1) % GT] = fmaxf(mx[(4 * qd + 1) % GT], __uint_as_float(v.y));
+        mx[(4 * qd + 2) % GT] = fmaxf(mx[(4 * qd + 2) % GT], __uint_as_float(v.z));
+        mx[(4 * qd + 3) % GT] = fmaxf(mx[(4 * qd + 3) % GT], __uint_as_float(v.w));
+      }
+#pragma unroll
+      for (int g = 0; g < GT; ++g) {
+        const float alpha = fast_exp2(m_all[g] - mx[g]);  // m_all = -inf -> 0
+        const u64 a2 = pack2(alpha, alpha);
+#pragma unroll
+        for (int e = 0; e < NP; ++e) o2[g][e] = fmul2(o2[g][e], a2);
+#pragma unroll
+        for (int i = 0; i < VPL; ++i)
+          if (g_s[i] == g) {
+            l_slot[i] *= alpha;
+            m_slot[i] = mx[g];
+          }
+        m_all[g] = mx[g];
+      }
+      __syncwarp();
+    }
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      const float pr = fast_exp2(sc[i] - m_slot[i]);  // masked rows: exp2(-inf) = 0
+      l_slot[i] += pr;
+      if (ok_s[i])
+        sts64(pbuf + (rr_s[i] * GT + g_s[i]) * 8, make_uint2(__float_as_uint(pr), __float_as_uint(pr)));
+    }
+    // ================================================================ V: accumulate P.V
+    cp_async_wait<RING - 2>();
+    __syncwarp();
+    issue(2 * it + RING);
+    {
+      const uint32_t vs = ring + ((2 * it + 1) % RING) * TILEB + h * ROWB + c * 16;
+#pragma unroll
+      for (int j = 0; j < R; ++j) {
+        u64 v2[NP];
+        Chunk<T>::widen(lds128(vs + j * RPP * ROWB), v2);
+        const uint32_t pa = pbuf + (j * RPP + h) * GT * 8;
+        if (GT == 1) {
+          uint2 pp = lds64(pa);
+          const u64 p2 = pack2(__uint_as_float(pp.x), __uint_as_float(pp.y));
+#pragma unroll
+          for (int e = 0; e < NP; ++e) o2[0][e] = ffma2(p2, v2[e], o2[0][e]);
+        } else {
+#pragma unroll
+          for (int g = 0; g < GT; g += 2) {
+            uint4 pp = lds128(pa + g * 8);
+            const u64 pA = pack2(__uint_as_float(pp.x), __uint_as_float(pp.y));
+            const u64 pB = pack2(__uint_as_float(pp.z), __uint_as_float(pp.w));
+#pragma unroll
+            for (int e = 0; e < NP; ++e) {
+              o2[g][e] = ffma2(pA, v2[e], o2[g][e]);
+              o2[(g + 1) % GT][e] = ffma2(pB, v2[e], o2[(g + 1) % GT][e]);
+            }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  }
+  cp_async_wait<0>();
+  __syncwarp();
+
+  // ---- warp state -> merge area (aliases this warp's ring): o[h][g][D] fp32, then (m,l)[g]
+  const uint32_t mo = ring;
+  const uint32_t mml = ring + RPP * GT * D * 4;
+  {
+    // l per head: gather every lane's slot sums through the transpose buffer
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) sts32(xbuf + (lane * VPL + i) * 4, __float_as_uint(l_slot[i]));
+    __syncwarp();
+    float lsum[GT];
+#pragma unroll
+    for (int g = 0; g < GT; ++g) lsum[g] = 0.f;
+#pragma unroll
+    for (int L = 0; L < 32; ++L)
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) {
+        const int idx = (L % LPR) * VPL + i;
+        if (idx < NV) lsum[idx % GT] += __uint_as_float(lds32(xbuf + (L * VPL + i) * 4));
+      }
+#pragma unroll
+    for (int g = 0; g < GT; ++g) {
+      float lo, hi;
+#pragma unroll
+      for (int e = 0; e < NP; e += 2) {
+        float a0, a1, a2, a3;
+        unpack2(o2[g][e], a0, a1);
+        unpack2(o2[g][e + 1], a2, a3);
+        sts128(mo + ((h * GT + g) * D + c * C::VEC + e * 2) * 4,
+               make_uint4(__float_as_uint(a0), __float_as_uint(a1), __float_as_uint(a2),
+                          __float_as_uint(a3)));
+      }
+      (void)lo;
+      (void)hi;
+      if (lane == 0)
+        sts64(mml + g * 8, make_uint2(__float_as_uint(m_all[g]), __float_as_uint(lsum[g])));
+    }
+  }
+  __syncthreads();
+
+  // ---- merge the NW warps and write the row (one chunk) or an fp32 partial (several chunks)
+  const uint32_t sbase = smem_u32(smem);
+  for (int item = threadIdx.x; item < GT * (D / 4); item += NW * 32) {
+    const int g = item / (D / 4), dq = item % (D / 4);
+    if (g >= g_valid) continue;
+    float M = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < NW; ++w)
+      M = fmaxf(M, __uint_as_float(lds32(sbase + w * C::WARP_SMEM + RPP * GT * D * 4 + g * 8)));
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, Lsum = 0.f;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+      const uint32_t wb = sbase + w * C::WARP_SMEM;
+      uint2 ml = lds64(wb + RPP * GT * D * 4 + g * 8);
+      const float sw = fast_exp2(__uint_as_float(ml.x) - M);  // idle warp: exp2(-inf) = 0
+      Lsum += sw * __uint_as_float(ml.y);
+#pragma unroll
+      for (int hh = 0; hh < RPP; ++hh) {
+        uint4 v = lds128(wb + ((hh * GT + g) * D + dq * 4) * 4);
+        a0 += sw * __uint_as_float(v.x);
+        a1 += sw * __uint_as_float(v.y);
+        a2 += sw * __uint_as_float(v.z);
+        a3 += sw * __uint_as_float(v.w);
+      }
+    }
+    const long long bh = (long long)b * p.H + head0 + g;
+    if (n_act == 1) {
+      const float inv = 1.f / Lsum;
+      store4<T>(out + bh * D + dq * 4, a0 * inv, a1 * inv, a2 * inv, a3 * inv);
+    } else {
+      const long long pi = bh * p.max_splits + split;
+      *reinterpret_cast<float4*>(p.part_o + pi * D + dq * 4) = make_float4(a0, a1, a2, a3);
+      if (dq == 0) p.part_ml[pi] = make_float2(M, Lsum);
+    }
+  }
+}
+
+// Combine kernel: one warp per (sequence, head); merges the active chunks' partials.
+// out = sum_s 2^(m_s - M) o_s / sum_s 2^(m_s - M) l_s.  Rows with <= 1 chunk were written by the
+// split kernel and are skipped here.
+template <typename T, int D>
+__global__ void __launch_bounds__(128) paged_decode_combine_kernel(const DecodeParams p, long long rows) {
+  constexpr int EPL = D / 32;  // floats per lane (2 or 4)
+  const long long bh = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (bh >= rows) return;
+  const long long b = bh / p.H;
+  long long ctx_ll = p.ctx_is_i64 ? reinterpret_cast<const long long*>(p.ctx)[b]
+                                  : (long long)reinterpret_cast<const int*>(p.ctx)[b];
+  if (ctx_ll > p.max_ctx) ctx_ll = p.max_ctx;
+  if (ctx_ll <= p.chunk) return;
+  const int n_act = (int)((ctx_ll + p.chunk - 1) / p.chunk);
+  const float2* ml = p.part_ml + bh * p.max_splits;
+  const float* po = p.part_o + bh * p.max_splits * D + lane * EPL;
+
+  float M = -INFINITY;
+  for (int s = lane; s < n_act; s += 32) M = fmaxf(M, ml[s].x);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+
+  float acc[EPL];
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) acc[e] = 0.f;
+  float Lsum = 0.f;
+  int s = 0;
+  for (; s + 4 <= n_act; s += 4) {
+    float w[4], v[4][EPL];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const float2 x = ml[s + u];
+      w[u] = fast_exp2(x.x - M);
+      Lsum += w[u] * x.y;
+      if (EPL == 4) {
+        float4 t = *reinterpret_cast<const float4*>(po + (long long)(s + u) * D);
+        v[u][0] = t.x; v[u][1] = t.y; v[u][2 % EPL] = t.z; v[u][3 % EPL] = t.w;
+      } else {
+        float2 t = *reinterpret_cast<const float2*>(po + (long long)(s + u) * D);
+        v[u][0] = t.x; v[u][1] = t.y;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) acc[e] += w[u] * v[u][e];
+  }
+  for (; s < n_act; ++s) {
+    const float2 x = ml[s];
+    const float w = fast_exp2(x.x - M);
+    Lsum += w * x.y;
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) acc[e] += w * po[(long long)s * D + e];
+  }
+  const float inv = 1.f / Lsum;
+  T* dst = reinterpret_cast<T*>(p.out) + bh * D + lane * EPL;
+  if (EPL == 4) {
+    store4<T>(dst, acc[0] * inv, acc[1] * inv, acc[2 % EPL] * inv, acc[3 % EPL] * inv);
+  } else {
+    store2<T>(dst, acc[0] * inv, acc[1] * inv);
+  }
+}
+
+}  // namespace mvl

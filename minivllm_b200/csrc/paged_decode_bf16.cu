@@ -1,0 +1,3 @@
+// paged_decode_bf16.cu — decode kernels instantiated for __nv_bfloat16.
+#define MVL_T __nv_bfloat16
+#include "paged_decode_inst.cuh"

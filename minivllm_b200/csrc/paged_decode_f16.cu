@@ -1,0 +1,3 @@
+// paged_decode_f16.cu — decode kernels instantiated for __half.
+#define MVL_T __half
+#include "paged_decode_inst.cuh"

@@ -1,0 +1,78 @@
+// paged_decode_inst.cuh — launcher bodies, included once per element type with MVL_T defined.
+#include <mutex>
+
+#include "host.h"
+
+namespace mvl {
+
+template <typename T, int D, int GT, bool UNIFORM>
+static int launch_split_u(const DecodeParams& p, dim3 grid, cudaStream_t s) {
+  using C = DecodeCfg<T, D, GT>;
+  auto kern = paged_decode_split_kernel<T, D, GT, UNIFORM>;
+  // Opt in to > 48 KB dynamic shared memory once per device.
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 64 && !configured[dev]) {
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    if (e != cudaSuccess) return (int)e;
+    configured[dev] = true;
+  } else if (dev >= 64) {
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    if (e != cudaSuccess) return (int)e;
+  }
+  kern<<<grid, C::NW * 32, C::SMEM, s>>>(p);
+  return (int)cudaGetLastError();
+}
+
+template <typename T, int D, int GT>
+static int launch_split_one(const DecodeParams& p, dim3 grid, cudaStream_t s) {
+  const bool uniform = ((1 << p.bs_shift) % DecodeCfg<T, D, GT>::TR) == 0;
+  return uniform ? launch_split_u<T, D, GT, true>(p, grid, s)
+                 : launch_split_u<T, D, GT, false>(p, grid, s);
+}
+
+template <typename T, int D>
+static int launch_split_d(const DecodeParams& p, int gt, dim3 grid, cudaStream_t s) {
+  switch (gt) {
+    case 1: return launch_split_one<T, D, 1>(p, grid, s);
+    case 2: return launch_split_one<T, D, 2>(p, grid, s);
+    case 4: return launch_split_one<T, D, 4>(p, grid, s);
+    case 8: return launch_split_one<T, D, 8>(p, grid, s);
+  }
+  return -1000;
+}
+
+template <>
+int launch_decode_split<MVL_T>(const DecodeParams& p, int head_dim, int gt, dim3 grid,
+                               cudaStream_t s) {
+  switch (head_dim) {
+    case 64: return launch_split_d<MVL_T, 64>(p, gt, grid, s);
+    case 128: return launch_split_d<MVL_T, 128>(p, gt, grid, s);
+  }
+  return -1000;
+}
+
+template <>
+int launch_decode_combine<MVL_T>(const DecodeParams& p, int head_dim, long long rows,
+                                 cudaStream_t s) {
+  const unsigned blocks = (unsigned)((rows + 3) / 4);
+  switch (head_dim) {
+    case 64: paged_decode_combine_kernel<MVL_T, 64><<<blocks, 128, 0, s>>>(p, rows); break;
+    case 128: paged_decode_combine_kernel<MVL_T, 128><<<blocks, 128, 0, s>>>(p, rows); break;
+    default: return -1000;
+  }
+  return (int)cudaGetLastError();
+}
+
+template <>
+int decode_tile_rows<MVL_T>(int head_dim, int gt) {
+  switch (head_dim) {
+    case 64: return gt >= 8 ? DecodeCfg<MVL_T, 64, 8>::TR : DecodeCfg<MVL_T, 64, 4>::TR;
+    case 128: return gt >= 8 ? DecodeCfg<MVL_T, 128, 8>::TR : DecodeCfg<MVL_T, 128, 4>::TR;
+  }
+  return -1;
+}
+
+}  // namespace mvl

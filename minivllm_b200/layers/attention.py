@@ -1,0 +1,291 @@
+"""Host-side mirror of the reference attention operator interface, backed by libmvl_b200.
+
+Same names, positional order and return conventions as reference
+src/myvllm/layers/attention.py: ``store_kvcache`` (:67-108), ``paged_attention_decode``
+(:418-473) and the ``Attention`` module (:476-557).  Where the reference launches Triton
+programs, these functions pass raw device pointers to the C ABI (include/mvl_abi.h) on torch's
+current stream.  Nothing here computes on the CPU and nothing falls back: non-CUDA tensors and a
+missing library are errors.
+
+Prefill (reference ``flash_attention_prefill``, :212-280) is outside this path (SURVEY.md §8(f)
+row N3); ``Attention.forward`` raises NotImplementedError for ``context.is_prefill``.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+from torch import nn
+
+from .. import _ext
+from ..utils.context import get_context
+
+_DTYPES = {torch.float32: _ext.F32, torch.float16: _ext.F16, torch.bfloat16: _ext.BF16}
+
+# One scratch tensor per (device, stream) for split-KV partials, grown on demand and reused, so
+# steady-state calls allocate nothing (a CUDA-graph capture sees a fixed pointer).
+_workspaces: dict = {}
+
+
+def _dtype_code(t: torch.Tensor) -> int:
+    try:
+        return _DTYPES[t.dtype]
+    except KeyError:
+        raise ValueError(f"unsupported dtype {t.dtype}; expected float32, float16 or bfloat16") from None
+
+
+def _need_cuda(**tensors: torch.Tensor) -> torch.device:
+    dev = None
+    for name, t in tensors.items():
+        if not isinstance(t, torch.Tensor):
+            raise TypeError(f"{name} must be a torch.Tensor")
+        if not t.is_cuda:
+            raise ValueError(f"{name} must be a CUDA tensor (minivllm_b200 has no CPU path)")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise ValueError(f"{name} is on {t.device}, expected {dev}")
+    return dev
+
+
+def _index_flag(name: str, t: torch.Tensor) -> int:
+    if t.dtype == torch.int64:
+        return 1
+    if t.dtype == torch.int32:
+        return 0
+    raise ValueError(f"{name} must be int32 or int64, got {t.dtype}")
+
+
+def _stream_ptr(dev: torch.device) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def workspace_for(dev: torch.device, nbytes: int) -> Optional[torch.Tensor]:
+    """Scratch for the split-KV partials on torch's current stream of ``dev`` (None if nbytes == 0)."""
+    if nbytes == 0:
+        return None
+    key = (dev.index, _stream_ptr(dev))
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=dev)
+        _workspaces[key] = ws
+    return ws
+
+
+def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor,
+                  v_cache: torch.Tensor, slot_mapping: torch.Tensor, block_size: int) -> None:
+    """Scatter ``key``/``value`` rows into the paged caches at ``slot_mapping`` (-1 = skip).
+
+    key, value: (num_tokens, num_kv_heads, head_dim); k_cache, v_cache:
+    (num_blocks, block_size, num_kv_heads, head_dim) contiguous; slot_mapping: (num_tokens,).
+    Mutates the caches in place, returns None (reference attention.py:67-108).  Views whose last
+    two dims are dense (e.g. the k/v slices of a fused qkv projection) are consumed without a copy.
+    """
+    dev = _need_cuda(key=key, value=value, k_cache=k_cache, v_cache=v_cache, slot_mapping=slot_mapping)
+    if key.dim() != 3 or value.shape != key.shape:
+        raise ValueError("key and value must both be (num_tokens, num_kv_heads, head_dim)")
+    num_tokens, num_kv_heads, head_dim = key.shape
+    assert k_cache.shape == v_cache.shape, "K and V cache shapes must match"
+    assert slot_mapping.numel() == num_tokens, "Slot mapping size must match number of tokens"
+    if k_cache.dim() != 4 or k_cache.shape[2] != num_kv_heads or k_cache.shape[3] != head_dim:
+        raise ValueError("k_cache must be (num_blocks, block_size, num_kv_heads, head_dim)")
+    if k_cache.shape[1] != block_size:
+        raise ValueError(f"block_size {block_size} != k_cache.shape[1] {k_cache.shape[1]}")
+    if not (k_cache.is_contiguous() and v_cache.is_contiguous()):
+        raise ValueError("k_cache and v_cache must be contiguous")
+    if key.dtype != k_cache.dtype or value.dtype != v_cache.dtype or key.dtype != value.dtype:
+        raise ValueError("key, value and the caches must share one dtype")
+
+    def rows(x: torch.Tensor) -> torch.Tensor:
+        dense = x.stride(2) == 1 and x.stride(1) == head_dim and (
+            num_tokens <= 1 or x.stride(0) >= num_kv_heads * head_dim)
+        return x if dense else x.contiguous()
+
+    key, value = rows(key), rows(value)
+    slot_mapping = slot_mapping.contiguous()
+    dense_stride = num_kv_heads * head_dim
+    with torch.cuda.device(dev):
+        _ext.check(_ext.lib().mvl_store_kvcache(
+            key.data_ptr(), value.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+            slot_mapping.data_ptr(), _index_flag("slot_mapping", slot_mapping), num_tokens,
+            num_kv_heads, head_dim,
+            key.stride(0) if num_tokens > 1 else dense_stride,
+            value.stride(0) if num_tokens > 1 else dense_stride,
+            k_cache.shape[0] * k_cache.shape[1], _dtype_code(key), _stream_ptr(dev)))
+
+
+def paged_attention_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                           block_tables: torch.Tensor, context_lens: torch.Tensor, scale: float,
+                           num_heads: int, num_kv_heads: int, head_dim: int, block_size: int,
+                           *, out: Optional[torch.Tensor] = None, chunk_tokens: int = 0,
+                           flags: int = 0) -> torch.Tensor:
+    """Decode attention of one query per sequence over the paged KV cache.
+
+    query: (batch, num_heads, head_dim); caches as in ``store_kvcache``; block_tables:
+    (batch, max_num_blocks) int32, padded with -1; context_lens: (batch,) int32/int64.
+    Returns a new (batch, num_heads, head_dim) tensor in query's dtype (reference
+    attention.py:418-473).  ``out``, ``chunk_tokens`` and ``flags`` are keyword-only additions
+    (preallocated output, split size override, profiling flags); defaults reproduce the
+    reference call.
+    """
+    dev = _need_cuda(query=query, k_cache=k_cache, v_cache=v_cache, block_tables=block_tables,
+                     context_lens=context_lens)
+    if query.dim() != 3 or query.shape[1] != num_heads or query.shape[2] != head_dim:
+        raise ValueError("query must be (batch, num_heads, head_dim)")
+    if k_cache.dim() != 4 or k_cache.shape != v_cache.shape:
+        raise ValueError("k_cache and v_cache must be (num_blocks, block_size, num_kv_heads, head_dim)")
+    if tuple(k_cache.shape[1:]) != (block_size, num_kv_heads, head_dim):
+        raise ValueError(
+            f"cache shape {tuple(k_cache.shape)} does not match block_size={block_size}, "
+            f"num_kv_heads={num_kv_heads}, head_dim={head_dim}")
+    if not (k_cache.is_contiguous() and v_cache.is_contiguous()):
+        raise ValueError("k_cache and v_cache must be contiguous")
+    if query.dtype != k_cache.dtype or k_cache.dtype != v_cache.dtype:
+        raise ValueError("query and the caches must share one dtype")
+    if block_tables.dim() != 2 or block_tables.dtype != torch.int32:
+        raise ValueError("block_tables must be a 2-D int32 tensor")
+    batch = query.shape[0]
+    if block_tables.shape[0] != batch or context_lens.numel() != batch:
+        raise ValueError("block_tables / context_lens batch size does not match query")
+    query = query.contiguous()
+    context_lens = context_lens.contiguous()
+    if block_tables.stride(1) != 1:
+        block_tables = block_tables.contiguous()
+    if out is None:
+        out = torch.empty_like(query)
+    elif out.shape != query.shape or out.dtype != query.dtype or not out.is_contiguous():
+        raise ValueError("out must be a contiguous tensor shaped and typed like query")
+    max_num_blocks = block_tables.shape[1]
+    if batch == 0 or max_num_blocks == 0:
+        return out.zero_() if max_num_blocks == 0 else out
+    code = _dtype_code(query)
+    handle = _ext.lib()
+    with torch.cuda.device(dev):
+        nbytes = handle.mvl_paged_decode_workspace_bytes(
+            batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, code, chunk_tokens)
+        ws = workspace_for(dev, nbytes)
+        _ext.check(handle.mvl_paged_decode(
+            out.data_ptr(), query.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+            block_tables.data_ptr(), context_lens.data_ptr(), _index_flag("context_lens", context_lens),
+            batch, max_num_blocks, block_tables.stride(0), num_heads, num_kv_heads, head_dim,
+            block_size, k_cache.shape[0], float(scale), code,
+            ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0,
+            chunk_tokens, flags, _stream_ptr(dev)))
+    return out
+
+
+class Attention(nn.Module):
+    """Paged attention layer with the reference's constructor and forward signature.
+
+    ``k_cache`` / ``v_cache`` start as empty placeholders and are assigned per-layer views of the
+    engine's cache allocation by the model runner, which finds this module by those two
+    attribute names (reference attention.py:477-491, model_runner.py:164-168).
+    """
+
+    def __init__(self, num_heads: int, head_dim: int, scale: float = 1.0,
+                 num_kv_heads: Optional[int] = None, block_size: int = 16):
+        super().__init__()
+        self.num_heads = num_heads
+        self.head_dim = head_dim
+        self.scale = scale
+        self.num_kv_heads = num_kv_heads if num_kv_heads is not None else num_heads
+        self.block_size = block_size
+        self.k_cache = self.v_cache = torch.tensor([])
+
+    def _effective_block_size(self) -> int:
+        # The reference builds Attention with block_size 16 while the engine's cache uses 256
+        # (qwen3.py:56-61 vs model_runner.py:19,162).  The attached cache
+        # is the ground truth for the page size.
+        if self.k_cache.dim() == 4:
+            return self.k_cache.shape[1]
+        return self.block_size
+
+    def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
+        context = get_context()
+        k_cache, v_cache = self.k_cache, self.v_cache
+        block_size = self._effective_block_size()
+
+        if k_cache.numel() > 0 and v_cache.numel() > 0 and context.slot_mapping is not None:
+            if k.dim() == 4:  # (B, N, KVH, D) -> (B*N, KVH, D)
+                k = k.reshape(-1, k.shape[-2], k.shape[-1])
+                v = v.reshape(-1, v.shape[-2], v.shape[-1])
+            store_kvcache(k, v, k_cache, v_cache, context.slot_mapping, block_size)
+
+        scale = self.scale / (self.head_dim ** 0.5)
+
+        if context.is_prefill:
+            raise NotImplementedError(
+                "prefill attention is outside the B200 decode path (SURVEY.md §8(f) N3)")
+        if q.dim() == 4:  # (B, 1, H, D) -> (B, H, D)
+            q = q.squeeze(1)
+        o = paged_attention_decode(q, k_cache, v_cache, context.block_tables, context.context_lens,
+                                   scale, self.num_heads, self.num_kv_heads, self.head_dim,
+                                   block_size)
+        return o.reshape(o.shape[0], self.num_heads * self.head_dim)
+
+
+class HostDecodeStep:
+    """One layer's decode-attention step driven from HOST (pinned) buffers.
+
+    Wraps ``mvl_decode_step_host``: per call it copies the step's inputs (q, the new token's k/v,
+    slot_mapping, context_lens, block_tables) host->device into staging buffers owned by this
+    object, scatters k/v into the resident paged cache, runs the split-KV decode and copies the
+    (batch, num_heads, head_dim) result device->host.  This is the path an engine takes when its
+    model runner builds the step on the CPU (reference model_runner.py:231-256 then
+    attention.py:493-557).  The KV cache itself stays resident in HBM, as in the reference engine.
+    All buffers are allocated here, once; ``__call__`` allocates nothing.
+    """
+
+    def __init__(self, k_cache: torch.Tensor, v_cache: torch.Tensor, batch: int, max_num_blocks: int,
+                 num_heads: int, scale: float, index_dtype: torch.dtype = torch.int64,
+                 chunk_tokens: int = 0):
+        dev = _need_cuda(k_cache=k_cache, v_cache=v_cache)
+        if k_cache.dim() != 4 or k_cache.shape != v_cache.shape or not (
+                k_cache.is_contiguous() and v_cache.is_contiguous()):
+            raise ValueError("caches must be contiguous (num_blocks, block_size, num_kv_heads, head_dim)")
+        self.dev, self.k_cache, self.v_cache = dev, k_cache, v_cache
+        self.num_blocks, self.block_size, self.num_kv_heads, self.head_dim = k_cache.shape
+        self.batch, self.max_num_blocks, self.num_heads = batch, max_num_blocks, num_heads
+        self.scale, self.chunk_tokens = float(scale), chunk_tokens
+        self.idx_flag = 1 if index_dtype == torch.int64 else 0
+        dt = k_cache.dtype
+        self.code = _DTYPES[dt]
+
+        def pair(shape, dtype):
+            return (torch.empty(shape, dtype=dtype, pin_memory=True),
+                    torch.empty(shape, dtype=dtype, device=dev))
+
+        self.q_h, self.q_d = pair((batch, num_heads, self.head_dim), dt)
+        self.k_h, self.k_d = pair((batch, self.num_kv_heads, self.head_dim), dt)
+        self.v_h, self.v_d = pair((batch, self.num_kv_heads, self.head_dim), dt)
+        self.slot_h, self.slot_d = pair((batch,), index_dtype)
+        self.ctx_h, self.ctx_d = pair((batch,), index_dtype)
+        self.bt_h, self.bt_d = pair((batch, max_num_blocks), torch.int32)
+        self.out_h, self.out_d = pair((batch, num_heads, self.head_dim), dt)
+        with torch.cuda.device(dev):
+            nbytes = _ext.lib().mvl_paged_decode_workspace_bytes(
+                batch, num_heads, self.num_kv_heads, self.head_dim, max_num_blocks, self.block_size,
+                self.code, chunk_tokens)
+        self.ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+        self.ws_bytes = nbytes
+        self.h2d_bytes = sum(t.numel() * t.element_size() for t in
+                             (self.q_h, self.k_h, self.v_h, self.slot_h, self.ctx_h, self.bt_h))
+        self.d2h_bytes = self.out_h.numel() * self.out_h.element_size()
+
+    def __call__(self, synchronize: bool = True) -> torch.Tensor:
+        """Run one step on the host buffers ``q_h, k_h, v_h, slot_h, ctx_h, bt_h``; returns ``out_h``
+        (valid once the stream is synchronised, which ``synchronize=True`` does)."""
+        with torch.cuda.device(self.dev):
+            stream = _stream_ptr(self.dev)
+            _ext.check(_ext.lib().mvl_decode_step_host(
+                self.q_h.data_ptr(), self.k_h.data_ptr(), self.v_h.data_ptr(), self.slot_h.data_ptr(),
+                self.ctx_h.data_ptr(), self.bt_h.data_ptr(), self.out_h.data_ptr(),
+                self.q_d.data_ptr(), self.k_d.data_ptr(), self.v_d.data_ptr(), self.slot_d.data_ptr(),
+                self.ctx_d.data_ptr(), self.bt_d.data_ptr(), self.out_d.data_ptr(),
+                self.k_cache.data_ptr(), self.v_cache.data_ptr(), self.idx_flag, self.batch,
+                self.max_num_blocks, self.num_heads, self.num_kv_heads, self.head_dim,
+                self.block_size, self.num_blocks, self.scale, self.code, self.ws.data_ptr(),
+                self.ws_bytes, self.chunk_tokens, stream))
+            if synchronize:
+                torch.cuda.current_stream(self.dev).synchronize()
+        return self.out_h

@@ -1,0 +1,294 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI, against the oracle and the goldens.
+
+Bars (BASELINE.json north_star): KV-cache write bit-exact; attention within 1e-4 abs when both
+sides are fp32, within 2e-2 abs for bf16/fp16 against the reference run in that dtype — plus the
+stricter bound against the exact oracle on the same rounded inputs: fp32 accumulation error plus
+ONE rounding of the result to the output dtype, |got - want| <= A + R*|want| with R the dtype's unit
+roundoff (bf16 2^-8, fp16 2^-11) and A = 1e-3 / 2e-4 / 1e-4 (bf16 / fp16 / fp32).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import workloads
+from cases import CASES, make_inputs
+from minivllm_b200 import reset_context, set_context
+from minivllm_b200.layers.attention import Attention, paged_attention_decode, store_kvcache
+from oracle import c_oracle
+from oracle import paged_attention_oracle as po
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+TOL_EXACT = {torch.float32: (1e-4, 0.0), torch.bfloat16: (1e-3, 2.0 ** -8), torch.float16: (2e-4, 2.0 ** -11)}
+
+
+def _assert_close(got, want, dtype):
+    got, want = np.asarray(got, dtype=np.float64), np.asarray(want, dtype=np.float64)
+    a, r = TOL_EXACT[dtype]
+    excess = np.abs(got - want) - (a + r * np.abs(want))
+    assert excess.max() <= 0, f"max excess {excess.max():.3e}, max abs err {np.abs(got - want).max():.3e}"
+
+
+def _dev(inp, device):
+    return {k: (v.to(device) if isinstance(v, torch.Tensor) else v) for k, v in inp.items()}
+
+
+def _run(inp, **kw):
+    return paged_attention_decode(inp["q"], inp["k_cache"], inp["v_cache"], inp["block_tables"],
+                                  inp["context_lens"], inp["scale"], inp["H"], inp["KVH"], inp["D"],
+                                  inp["BS"], **kw)
+
+
+def _oracle(inp):
+    return c_oracle.paged_decode(inp["q"], inp["k_cache"], inp["v_cache"], inp["block_tables"],
+                                 inp["context_lens"], inp["scale"], inp["H"], inp["KVH"], inp["D"],
+                                 inp["BS"])
+
+
+# ------------------------------------------------------------------ store_kvcache: bit-exact
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("idx", [torch.int64, torch.int32])
+def test_store_bit_exact(cuda_device, dtype, idx):
+    g = torch.Generator().manual_seed(7)
+    NB, BS, KVH, D, N = 40, 16, 8, 128, 300
+    key = torch.randn(N, KVH, D, generator=g).to(dtype)
+    val = torch.randn(N, KVH, D, generator=g).to(dtype)
+    slots = torch.randperm(NB * BS, generator=g)[:N].to(torch.int64)
+    slots[::7] = -1
+    kc = torch.randn(NB, BS, KVH, D, generator=g).to(dtype)
+    vc = torch.randn(NB, BS, KVH, D, generator=g).to(dtype)
+    want_k, want_v = kc.clone(), vc.clone()
+    po.store_kvcache_oracle(key, val, want_k, want_v, slots)
+    dk, dv = kc.to(cuda_device), vc.to(cuda_device)
+    assert store_kvcache(key.to(cuda_device), val.to(cuda_device), dk, dv,
+                         slots.to(cuda_device, idx), BS) is None
+    # whole-cache equality: untouched slots must stay untouched
+    assert torch.equal(dk.cpu().view(torch.uint8), want_k.view(torch.uint8))
+    assert torch.equal(dv.cpu().view(torch.uint8), want_v.view(torch.uint8))
+
+
+def test_store_edge_cases(cuda_device):
+    BS, KVH, D = 256, 2, 64
+    kc = torch.zeros(3, BS, KVH, D, device=cuda_device, dtype=torch.bfloat16)
+    vc = torch.zeros_like(kc)
+    # empty input, all -1, first and last slot of the pool
+    store_kvcache(kc.new_zeros(0, KVH, D), kc.new_zeros(0, KVH, D), kc, vc,
+                  torch.zeros(0, dtype=torch.int64, device=cuda_device), BS)
+    k = torch.randn(3, KVH, D, device=cuda_device).to(torch.bfloat16)
+    v = torch.randn(3, KVH, D, device=cuda_device).to(torch.bfloat16)
+    store_kvcache(k, v, kc, vc, torch.full((3,), -1, dtype=torch.int64, device=cuda_device), BS)
+    assert torch.count_nonzero(kc) == 0 and torch.count_nonzero(vc) == 0
+    store_kvcache(k, v, kc, vc, torch.tensor([0, -1, 3 * BS - 1], device=cuda_device), BS)
+    assert torch.equal(kc[0, 0], k[0]) and torch.equal(vc[2, BS - 1], v[2])
+    assert torch.count_nonzero(kc) == torch.count_nonzero(k[0]) + torch.count_nonzero(k[2])
+    # strided views (k/v slices of a fused qkv projection) are consumed without a copy
+    H = 4
+    qkv = torch.randn(5, (H + 2 * KVH) * D, device=cuda_device).to(torch.bfloat16)
+    k_view = qkv[:, H * D:(H + KVH) * D].view(5, KVH, D)
+    v_view = qkv[:, (H + KVH) * D:].view(5, KVH, D)
+    assert not k_view.is_contiguous()
+    slots = torch.tensor([10, 11, -1, 300, 12], device=cuda_device)
+    kc.zero_(), vc.zero_()
+    store_kvcache(k_view, v_view, kc, vc, slots, BS)
+    flat_k, flat_v = kc.view(-1, KVH, D), vc.view(-1, KVH, D)
+    for t, s in enumerate(slots.tolist()):
+        if s >= 0:
+            assert torch.equal(flat_k[s], k_view[t]) and torch.equal(flat_v[s], v_view[t])
+
+
+# ------------------------------------------------------------------ decode vs reference goldens
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_decode_matches_reference_golden(cuda_device, name):
+    inp = make_inputs(name)
+    z = np.load(os.path.join(GOLD, name + ".npz"))
+    out = _run(_dev(inp, cuda_device))
+    assert out.dtype == inp["q"].dtype and out.shape == inp["q"].shape
+    got = out.float().cpu().numpy()
+    if inp["q"].dtype == torch.float32:
+        assert np.abs(got - z["ref_out"]).max() <= 1e-4          # both sides fp32
+    else:
+        assert np.abs(got - z["ref_out"]).max() <= 2e-2          # reference run in bf16/fp16
+        _assert_close(got, z["ref_out_f32"], inp["q"].dtype)
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+@pytest.mark.parametrize("chunk", [64, 128, 100000])
+def test_decode_split_sizes_agree_with_oracle(cuda_device, name, chunk):
+    inp = make_inputs(name)
+    want = _oracle(inp).numpy()
+    got = _run(_dev(inp, cuda_device), chunk_tokens=chunk).float().cpu().numpy()
+    _assert_close(got, want, inp["q"].dtype)
+
+
+def _random_case(seed, dtype, H, KVH, D, BS, B, max_ctx, ctx_dtype=torch.int64):
+    g = torch.Generator().manual_seed(seed)
+    rng = np.random.RandomState(seed)
+    ctx = rng.randint(1, max_ctx + 1, size=B)
+    nblk = (ctx + BS - 1) // BS
+    total = int(nblk.sum()) + 5
+    perm = rng.permutation(total)
+    tables = np.full((B, int(nblk.max()) + 2), -1, dtype=np.int32)
+    at = 0
+    for b in range(B):
+        tables[b, :nblk[b]] = perm[at:at + nblk[b]]
+        at += nblk[b]
+        # stale garbage beyond the valid range must never be dereferenced (Appendix B-6)
+        tables[b, nblk[b]:] = 2 ** 30
+    return dict(q=torch.randn(B, H, D, generator=g).to(dtype),
+                k_cache=torch.randn(total, BS, KVH, D, generator=g).to(dtype),
+                v_cache=torch.randn(total, BS, KVH, D, generator=g).to(dtype),
+                block_tables=torch.from_numpy(tables), context_lens=torch.from_numpy(ctx).to(ctx_dtype),
+                scale=1.0 / D ** 0.5, H=H, KVH=KVH, D=D, BS=BS)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("H,KVH", [(4, 4), (8, 4), (32, 8), (16, 2), (10, 2), (32, 2), (6, 2)])
+@pytest.mark.parametrize("D,BS", [(128, 16), (64, 16), (128, 256), (64, 8), (128, 4)])
+def test_decode_random_ragged(cuda_device, dtype, H, KVH, D, BS):
+    inp = _random_case(1000 + H * 7 + KVH + D + BS, dtype, H, KVH, D, BS, B=5, max_ctx=600,
+                       ctx_dtype=torch.int32 if BS == 16 else torch.int64)
+    want = _oracle(inp).numpy()
+    got = _run(_dev(inp, cuda_device)).float().cpu().numpy()
+    assert np.isfinite(got).all()
+    _assert_close(got, want, dtype)
+
+
+def test_decode_edge_lengths(cuda_device):
+    # 1, BS-1, BS, BS+1, tile and chunk boundaries, and a zero-length (graph padding) row
+    inp = _random_case(77, torch.bfloat16, 32, 8, 128, 16, B=12, max_ctx=10)
+    ctx = torch.tensor([1, 15, 16, 17, 63, 64, 65, 127, 128, 129, 1024, 1025])
+    BS = 16
+    nblk = (ctx + BS - 1) // BS
+    total = int(nblk.sum())
+    g = torch.Generator().manual_seed(3)
+    tables = torch.full((12, int(nblk.max())), -1, dtype=torch.int32)
+    perm = torch.randperm(total, generator=g).to(torch.int32)
+    at = 0
+    for b in range(12):
+        tables[b, :nblk[b]] = perm[at:at + nblk[b]]
+        at += int(nblk[b])
+    inp.update(k_cache=torch.randn(total, BS, 8, 128, generator=g).to(torch.bfloat16),
+               v_cache=torch.randn(total, BS, 8, 128, generator=g).to(torch.bfloat16),
+               block_tables=tables, context_lens=ctx)
+    want = _oracle(inp).numpy()
+    got = _run(_dev(inp, cuda_device)).float().cpu().numpy()
+    _assert_close(got, want, torch.bfloat16)
+    # ctx == 1 -> output is exactly that token's V row
+    blk = int(tables[0, 0])
+    assert torch.equal(torch.from_numpy(got[0, 5]), inp["v_cache"][blk, 0, 1].float())
+    # zero-length rows give zeros and do not disturb their neighbours
+    inp["context_lens"] = ctx.clone()
+    inp["context_lens"][3] = 0
+    got0 = _run(_dev(inp, cuda_device)).float().cpu().numpy()
+    assert np.abs(got0[3]).max() == 0
+    keep = [i for i in range(12) if i != 3]
+    assert np.array_equal(got0[keep], got[keep])
+
+
+def test_decode_large_scores_are_stable(cuda_device):
+    # a large scale drives scores far apart: exercises the lazy-max refresh and masking
+    inp = _random_case(5, torch.float32, 8, 2, 128, 16, B=3, max_ctx=900)
+    inp["scale"] = 3.0
+    want = _oracle(inp).numpy()
+    got = _run(_dev(inp, cuda_device)).float().cpu().numpy()
+    assert np.isfinite(got).all() and np.abs(got - want).max() <= 1e-4
+
+
+def test_decode_is_deterministic_and_respects_out(cuda_device):
+    inp = _dev(make_inputs("ragged_bf16"), cuda_device)
+    a = _run(inp)
+    buf = torch.full_like(a, 7)
+    b = _run(inp, out=buf)
+    assert b is buf and torch.equal(a, b)
+
+
+# ------------------------------------------------------------------ Attention module + Context
+@pytest.mark.parametrize("block_size", [16, 256])
+def test_attention_forward_decode_step(cuda_device, block_size):
+    """store-then-attend in one forward, as reference attention.py:493-557 (decode branch)."""
+    H, KVH, D, B = 16, 8, 128, 6
+    g = torch.Generator().manual_seed(21)
+    ctx = torch.tensor([5, 16, 17, 300, 256, 257])
+    nblk = (ctx + block_size - 1) // block_size
+    total = int(nblk.sum())
+    tables = torch.full((B, int(nblk.max())), -1, dtype=torch.int32)
+    perm = torch.randperm(total, generator=g).to(torch.int32)
+    at = 0
+    for b in range(B):
+        tables[b, :nblk[b]] = perm[at:at + nblk[b]]
+        at += int(nblk[b])
+    kc = torch.randn(total, block_size, KVH, D, generator=g).to(torch.bfloat16)
+    vc = torch.randn(total, block_size, KVH, D, generator=g).to(torch.bfloat16)
+    q = torch.randn(B, H, D, generator=g).to(torch.bfloat16)
+    k = torch.randn(B, KVH, D, generator=g).to(torch.bfloat16)
+    v = torch.randn(B, KVH, D, generator=g).to(torch.bfloat16)
+    last = ctx - 1
+    slots = tables[torch.arange(B), last // block_size].long() * block_size + last % block_size
+    # oracle: write the new token, then attend over ctx tokens (Appendix B-9)
+    ok, ov = kc.clone(), vc.clone()
+    po.store_kvcache_oracle(k, v, ok, ov, slots)
+    want = c_oracle.paged_decode(q, ok, ov, tables, ctx, 1.0 / D ** 0.5, H, KVH, D, block_size)
+
+    layer = Attention(H, D, scale=1.0, num_kv_heads=KVH)  # block_size left at the default 16
+    layer.k_cache, layer.v_cache = kc.to(cuda_device), vc.to(cuda_device)
+    set_context(False, slot_mapping=slots.to(cuda_device), context_lens=ctx.to(cuda_device),
+                block_tables=tables.to(cuda_device))
+    try:
+        out = layer(q.to(cuda_device).unsqueeze(1), k.to(cuda_device), v.to(cuda_device))
+    finally:
+        reset_context()
+    assert out.shape == (B, H * D) and out.dtype == torch.bfloat16
+    assert torch.equal(layer.k_cache.cpu().view(torch.uint8), ok.view(torch.uint8))
+    assert torch.equal(layer.v_cache.cpu().view(torch.uint8), ov.view(torch.uint8))
+    _assert_close(out.float().cpu().view(B, H, D).numpy(), want.numpy(), torch.bfloat16)
+
+
+def test_bad_arguments_raise(cuda_device):
+    inp = _dev(make_inputs("g1_d64"), cuda_device)
+    with pytest.raises(ValueError):
+        _run(dict(inp, block_tables=inp["block_tables"].long()))
+    with pytest.raises(ValueError):
+        _run(dict(inp, q=inp["q"].double()))
+    with pytest.raises(ValueError):  # head_dim 32 is not built
+        paged_attention_decode(inp["q"][..., :32].contiguous(), inp["k_cache"][..., :32].contiguous(),
+                               inp["v_cache"][..., :32].contiguous(), inp["block_tables"],
+                               inp["context_lens"], 1.0, 4, 4, 32, 16)
+    with pytest.raises(ValueError):  # block size 12 is not a power of two
+        kc = torch.zeros(4, 12, 4, 64, device=cuda_device)
+        paged_attention_decode(inp["q"], kc, kc, inp["block_tables"], inp["context_lens"], 1.0, 4, 4, 64, 12)
+
+
+# ------------------------------------------------------------------ full-size properties (C3 shape)
+def test_c3_full_size_properties(cuda_device):
+    """BASELINE config 3 at full size: sub-batch parity against the oracle, then size-independent
+    properties: split-size invariance, block-permutation invariance, V-linearity, ones-V row sums."""
+    t = workloads.build_tables("c3")
+    w = workloads.materialize(t, cuda_device)
+    args = (w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"], w["H"],
+            w["KVH"], w["D"], w["BS"])
+    out = paged_attention_decode(w["q"], *args)
+    assert torch.isfinite(out.float()).all()
+    # (1) oracle parity on a strided sample of sequences (the oracle needs seconds per sequence)
+    pick = [0, 85, 170, 255]
+    sub_want = c_oracle.paged_decode(w["q"][pick].cpu(), w["k_cache"].cpu(), w["v_cache"].cpu(),
+                                     w["block_tables"][pick].cpu(), w["context_lens"][pick].cpu(),
+                                     w["scale"], w["H"], w["KVH"], w["D"], w["BS"])
+    _assert_close(out[pick].float().cpu().numpy(), sub_want.numpy(), torch.bfloat16)
+    # (2) the split size changes the reduction tree, not the result (beyond fp32 rounding)
+    out_512 = paged_attention_decode(w["q"], *args, chunk_tokens=512)
+    assert (out.float() - out_512.float()).abs().max() <= 2e-2
+    # (3) V == 1 everywhere -> every output element is exactly 1 (softmax rows sum to 1)
+    ones = torch.ones_like(w["v_cache"])
+    o1 = paged_attention_decode(w["q"], w["k_cache"], ones, *args[2:])
+    assert (o1.float() - 1).abs().max() <= 1e-2
+    # (4) permuting physical blocks (cache rows and table entries together) changes nothing
+    perm = torch.randperm(t.num_blocks, device=cuda_device)
+    inv = torch.empty_like(perm)
+    inv[perm] = torch.arange(t.num_blocks, device=cuda_device)
+    bt = w["block_tables"].long()
+    bt2 = torch.where(bt >= 0, inv[bt.clamp(min=0)], bt).to(torch.int32)
+    kc2, vc2 = w["k_cache"][perm], w["v_cache"][perm]
+    out_p = paged_attention_decode(w["q"], kc2, vc2, bt2, *args[3:])
+    assert torch.equal(out_p, out)

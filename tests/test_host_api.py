@@ -1,0 +1,114 @@
+"""CPU: the host-side mirror of the reference interface and the C-ABI surface (no compute calls).
+
+Reference interface being mirrored: src/myvllm/utils/context.py:5-27 and
+src/myvllm/layers/attention.py:67-74, 418-429, 477-484.
+"""
+import ctypes
+import inspect
+import os
+import re
+
+import pytest
+import torch
+
+import minivllm_b200 as pkg
+from minivllm_b200 import _ext
+from minivllm_b200.layers import attention as att
+from minivllm_b200.utils import context as ctxmod
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "mvl_abi.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(mvl_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    names = _declared_symbols()
+    assert "mvl_store_kvcache" in names and "mvl_paged_decode" in names
+    raw = ctypes.CDLL(_ext.LIB_PATH)
+    for name in names:
+        assert hasattr(raw, name), f"{name} declared in mvl_abi.h but not exported"
+    assert sorted(_ext.PROTOTYPES) == names, "ctypes binding and header disagree"
+
+
+def test_abi_version_and_strerror():
+    lib = _ext.lib()
+    assert lib.mvl_abi_version() == _ext.ABI_VERSION
+    assert lib.mvl_strerror(0) == b"ok"
+    for code in range(-7, 0):
+        assert lib.mvl_strerror(code) not in (b"ok", b"unknown mvl_status")
+    assert lib.mvl_strerror(-99) == b"unknown mvl_status"
+
+
+def test_argument_validation_needs_no_gpu():
+    lib = _ext.lib()
+    # num_tokens == 0 is a no-op; bad dtype / shape are rejected before any CUDA call
+    assert lib.mvl_store_kvcache(None, None, None, None, None, 1, 0, 8, 128, 1024, 1024, 64, 2, None) == 0
+    assert lib.mvl_store_kvcache(None, None, None, None, None, 1, 4, 8, 128, 1024, 1024, 64, 9, None) == -2
+    assert lib.mvl_store_kvcache(None, None, None, None, None, 1, 4, 8, 128, 1024, 1024, 64, 2, None) == -1
+    buf = ctypes.create_string_buffer(64)
+    p = ctypes.addressof(buf)
+    p += (-p) % 16
+    assert lib.mvl_store_kvcache(p, p, p, p, p, 1, 4, 8, 128, 8, 1024, 64, 2, None) == -3  # stride < row
+    assert lib.mvl_store_kvcache(p + 2, p, p, p, p, 1, 4, 8, 128, 1024, 1024, 64, 2, None) == -4
+    with pytest.raises(ValueError):
+        _ext.check(-3)
+    with pytest.raises(_ext.MvlError):
+        _ext.check(-5)
+
+
+def test_context_matches_reference_interface():
+    assert [f for f in ctxmod.Context.__dataclass_fields__] == [
+        "is_prefill", "cu_seqlens_q", "cu_seqlens_k", "max_seqlen_q", "max_seqlen_k", "slot_mapping",
+        "context_lens", "block_tables"]
+    assert list(inspect.signature(ctxmod.set_context).parameters) == [
+        "is_prefill", "cu_seqlens_q", "cu_seqlens_k", "max_seqlen_q", "max_seqlen_k", "slot_mapping",
+        "context_lens", "block_tables"]
+    pkg.reset_context()
+    c0 = pkg.get_context()
+    assert c0.is_prefill is False and c0.slot_mapping is None and c0.max_seqlen_k == 0
+    slots = torch.tensor([3, -1])
+    pkg.set_context(False, slot_mapping=slots, context_lens=torch.tensor([4, 9]))
+    c1 = pkg.get_context()
+    assert c1 is not c0 and c1.slot_mapping is slots and c1.block_tables is None
+    pkg.set_context(True)  # replaces wholesale, does not merge
+    assert pkg.get_context().slot_mapping is None and pkg.get_context().is_prefill is True
+    pkg.reset_context()
+    assert pkg.get_context().is_prefill is False
+
+
+def test_operator_signatures_match_reference():
+    assert list(inspect.signature(att.store_kvcache).parameters) == [
+        "key", "value", "k_cache", "v_cache", "slot_mapping", "block_size"]
+    assert list(inspect.signature(att.paged_attention_decode).parameters)[:10] == [
+        "query", "k_cache", "v_cache", "block_tables", "context_lens", "scale", "num_heads",
+        "num_kv_heads", "head_dim", "block_size"]
+    sig = inspect.signature(att.Attention.__init__)
+    assert list(sig.parameters)[1:] == ["num_heads", "head_dim", "scale", "num_kv_heads", "block_size"]
+    assert sig.parameters["scale"].default == 1.0 and sig.parameters["block_size"].default == 16
+    layer = att.Attention(16, 128, num_kv_heads=None)
+    assert layer.num_kv_heads == 16 and layer.k_cache.numel() == 0 and layer.v_cache.numel() == 0
+    assert hasattr(layer, "k_cache") and hasattr(layer, "v_cache")  # the runner's duck-typing hook
+
+
+def test_no_cpu_fallback():
+    q = torch.zeros(2, 4, 64)
+    kc = torch.zeros(3, 16, 2, 64)
+    bt = torch.zeros(2, 1, dtype=torch.int32)
+    cl = torch.ones(2, dtype=torch.int32)
+    with pytest.raises(ValueError, match="CUDA"):
+        att.paged_attention_decode(q, kc, kc, bt, cl, 1.0, 4, 2, 64, 16)
+    with pytest.raises(ValueError, match="CUDA"):
+        att.store_kvcache(torch.zeros(2, 2, 64), torch.zeros(2, 2, 64), kc, kc.clone(),
+                          torch.zeros(2, dtype=torch.int64), 16)
+
+
+def test_product_does_not_import_the_oracle():
+    pat = re.compile(r"^\s*(from|import)\s+oracle\b|oracle/|paged_oracle|c_oracle", re.M)
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "minivllm_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                assert not pat.search(open(os.path.join(dirpath, f)).read()), f"{f} uses the oracle"

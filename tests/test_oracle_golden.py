@@ -1,0 +1,106 @@
+"""CPU: the oracles against the golden vectors written by the reference's own function.
+
+Golden outputs come from reference benchmark_decoding.py:136-189 (decode_torch_optimized), run by
+tests/golden/make_golden.py.  Tolerances: fp32 1e-5 abs (same math, different summation order);
+16-bit dtypes 2e-2 abs for the in-dtype port (BASELINE.json north_star), 1e-5 for the exact
+oracles against the reference fed fp32-upcast inputs.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from cases import CASES, input_digest, make_inputs
+from oracle import c_oracle
+from oracle import paged_attention_oracle as po
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _load(name):
+    z = np.load(os.path.join(GOLD, name + ".npz"))
+    return z["ref_out"], z["ref_out_f32"], float(z["naive_maxdiff"]), str(z["digest"])
+
+
+def _args(inp):
+    return (inp["q"], inp["k_cache"], inp["v_cache"], inp["block_tables"], inp["context_lens"],
+            inp["scale"], inp["H"], inp["KVH"], inp["D"], inp["BS"])
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_inputs_reproduce(name):
+    inp = make_inputs(name)
+    assert input_digest(inp) == _load(name)[3], "seeded input generator drifted from the goldens"
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_reference_variants_agree(name):
+    assert _load(name)[2] <= 1e-6  # decode_torch_optimized vs naive_decode_attention
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_padded_port_matches_reference(name):
+    inp = make_inputs(name)
+    ref_out, ref_f32, _, _ = _load(name)
+    got = po.decode_attention_padded(*_args(inp)).float().numpy()
+    tol = 1e-5 if CASES[name]["dtype"] == "f32" else 2e-2
+    assert np.abs(got - ref_out).max() <= tol
+    up = dict(inp, q=inp["q"].float(), k_cache=inp["k_cache"].float(), v_cache=inp["v_cache"].float())
+    got32 = po.decode_attention_padded(*_args(up)).numpy()
+    assert np.abs(got32 - ref_f32).max() <= 1e-5
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_exact_oracles_match_reference(name):
+    inp = make_inputs(name)
+    ref_f32 = _load(name)[1]
+    exact = po.decode_attention_exact(*_args(inp))
+    assert np.abs(exact - ref_f32).max() <= 1e-5
+    c_out = c_oracle.paged_decode(*_args(inp)).numpy()
+    assert np.abs(c_out - ref_f32).max() <= 1e-5
+    assert np.abs(c_out - exact).max() <= 2e-6
+
+
+def test_context_len_zero_is_zero_row():
+    inp = make_inputs("g1_d64")
+    inp["context_lens"] = inp["context_lens"].clone()
+    inp["context_lens"][1] = 0
+    out = c_oracle.paged_decode(*_args(inp))
+    assert torch.count_nonzero(out[1]) == 0
+    assert np.abs(po.decode_attention_exact(*_args(inp))[1]).max() == 0
+
+
+def test_context_len_one_returns_value_row():
+    inp = make_inputs("ragged_g4")  # sequence 0 has one token
+    out = c_oracle.paged_decode(*_args(inp))
+    blk = int(inp["block_tables"][0, 0])
+    group = inp["H"] // inp["KVH"]
+    for h in range(inp["H"]):
+        assert torch.equal(out[0, h], inp["v_cache"][blk, 0, h // group].float())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+def test_store_oracles_follow_kernel_index_math(dtype):
+    # reference attention.py:33-34,52-56: block = slot // BS, offset = slot % BS
+    g = torch.Generator().manual_seed(5)
+    NB, BS, KVH, D, N = 7, 16, 2, 64, 9
+    key = torch.randn(N, KVH, D, generator=g).to(dtype)
+    val = torch.randn(N, KVH, D, generator=g).to(dtype)
+    slots = torch.tensor([3, -1, 111, 0, 16, -1, 15, 64, 90], dtype=torch.int64)
+    base_k = torch.randn(NB, BS, KVH, D, generator=g).to(dtype)
+    base_v = torch.randn(NB, BS, KVH, D, generator=g).to(dtype)
+    want_k, want_v = base_k.clone(), base_v.clone()
+    for t, s in enumerate(slots.tolist()):
+        if s == -1:
+            continue
+        want_k[s // BS, s % BS] = key[t]
+        want_v[s // BS, s % BS] = val[t]
+    k1, v1 = base_k.clone(), base_v.clone()
+    po.store_kvcache_oracle(key, val, k1, v1, slots)
+    assert torch.equal(k1.view(torch.uint8), want_k.view(torch.uint8))
+    assert torch.equal(v1.view(torch.uint8), want_v.view(torch.uint8))
+    k2, v2 = base_k.clone(), base_v.clone()
+    c_oracle.store_kvcache(key, val, k2, v2, slots)
+    assert torch.equal(k2.view(torch.uint8), want_k.view(torch.uint8))
+    assert torch.equal(v2.view(torch.uint8), want_v.view(torch.uint8))
