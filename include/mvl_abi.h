@@ -140,6 +140,45 @@ int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_h
                          float scale, int elem_dtype, void* workspace, size_t workspace_bytes,
                          int chunk_tokens, void* stream);
 
+/*
+ * mvl_paged_decode_static — mvl_paged_decode for callers that cannot allocate device memory.
+ * This entry point has no counterpart in the reference (its Triton kernel needs no scratch).
+ *
+ * Same arguments and result as mvl_paged_decode, minus the workspace: the split-KV partials go
+ * into an array of MVL_STATIC_SCRATCH_BYTES that is part of this library's device image.  Use it
+ * when your side of the boundary has nothing to allocate from — all free HBM already belongs to
+ * the KV cache, your binding holds raw pointers but no allocator, or your loop cannot take the
+ * device-wide synchronisation a cudaMalloc implies.  The call itself performs no cudaMalloc,
+ * cudaFree or any other allocating call.
+ *
+ *   - Cost: every GPU on which the library is loaded keeps those MVL_STATIC_SCRATCH_BYTES resident
+ *     until the process exits, whether or not this function is ever called.
+ *   - Limit: if mvl_paged_decode_workspace_bytes(...) for the given sizes exceeds
+ *     MVL_STATIC_SCRATCH_BYTES the call returns MVL_ERR_LIMIT and launches nothing;
+ *     mvl_static_last_error() then says how many bytes were needed.  A larger chunk_tokens
+ *     (fewer chunks per sequence) or a smaller batch shrinks the need.
+ *   - First call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ *     that device current).  Make that first call outside any stream capture.
+ *   - All calls on a device share the one array and it keeps whatever the previous call left;
+ *     nothing in it needs to start at zero, so nothing is cleared.  Two calls that may run at the
+ *     same time on one GPU (different streams, or different host threads) race on it: keep calls
+ *     ordered on one stream, or order the streams with events.
+ */
+#define MVL_STATIC_SCRATCH_BYTES (16u << 20) /* 16 MiB */
+
+int mvl_paged_decode_static(void* out, const void* query, const void* k_cache, const void* v_cache,
+                            const int32_t* block_tables, const void* context_lens, int ctx_is_i64,
+                            int64_t batch, int64_t max_num_blocks, int64_t block_table_stride,
+                            int num_heads, int num_kv_heads, int head_dim, int block_size,
+                            int64_t num_blocks, float scale, int elem_dtype, int chunk_tokens,
+                            void* stream);
+
+/* MVL_STATIC_SCRATCH_BYTES as seen by the built library. */
+size_t mvl_static_scratch_bytes(void);
+
+/* Text explaining the last failure of mvl_paged_decode_static on the calling thread ("" if none). */
+const char* mvl_static_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif

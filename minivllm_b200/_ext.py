@@ -33,6 +33,10 @@ PROTOTYPES = {
                               _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
     "mvl_decode_step_host": (_i, [_vp] * 16 + [_i, _i64, _i64, _i, _i, _i, _i, _i64, _f, _i, _vp,
                                                _sz, _i, _vp]),
+    "mvl_paged_decode_static": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i64, _i64, _i64, _i, _i, _i,
+                                     _i, _i64, _f, _i, _i, _vp]),
+    "mvl_static_scratch_bytes": (_sz, []),
+    "mvl_static_last_error": (C.c_char_p, []),
 }
 
 _lib = None
