@@ -30,6 +30,11 @@ __device__ __forceinline__ u64 fmul2(u64 a, u64 b) {
   asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
   return d;
 }
+__device__ __forceinline__ u64 fadd2(u64 a, u64 b) {
+  u64 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
 __device__ __forceinline__ float hsum2(u64 v) {
   float lo, hi;
   unpack2(v, lo, hi);
@@ -66,6 +71,20 @@ __device__ __forceinline__ void sts64(uint32_t a, uint2 v) {
 }
 __device__ __forceinline__ void sts32(uint32_t a, uint32_t v) {
   asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v));
+}
+
+// base + row * pitch as one IMAD.WIDE.U32 (row and pitch are 32-bit, the sum is a 64-bit address).
+__device__ __forceinline__ const char* row_ptr(const char* base, uint32_t row, uint32_t pitch) {
+  u64 r;
+  asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(row), "r"(pitch), "l"(base));
+  return reinterpret_cast<const char*>(r);
+}
+// a ^ imm, volatile so the compiler recomputes it where it is used instead of hoisting a family of
+// loop-invariant swizzled addresses into (spilled) registers.
+__device__ __forceinline__ uint32_t xor_imm(uint32_t a, uint32_t imm) {
+  uint32_t r;
+  asm volatile("xor.b32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(imm));
+  return r;
 }
 
 // ---------------------------------------------------------------- cp.async (SASS: LDGSTS)

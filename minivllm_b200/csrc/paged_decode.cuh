@@ -158,25 +158,40 @@ paged_decode_split_kernel(const DecodeParams p) {
   // ---- this warp's tiles: tile = warp, warp + NW, ...
   const int ntiles = (end - start + TR - 1) / TR;
   const int my_nt = (warp < ntiles) ? (ntiles - warp + NW - 1) / NW : 0;
-  const long long row_pitch = (long long)p.KVH * ROWB;  // bytes between consecutive slots
+  const uint32_t row_pitch = (uint32_t)p.KVH * ROWB;  // bytes between consecutive slots
   const int bs_mask = (1 << p.bs_shift) - 1;
   const int32_t* bt_row = p.bt + (long long)b * p.bt_stride;
   const char* kbase = reinterpret_cast<const char*>(p.kc) + (long long)kvh * ROWB + c * 16;
   const char* vbase = reinterpret_cast<const char*>(p.vc) + (long long)kvh * ROWB + c * 16;
+  const uint32_t lane_off = h * ROWB + c * 16;  // this lane's byte inside a tile pass
 
-  // Issue the n-th half tile (even: K of tile n/2, odd: V) into ring slot n % RING; always commits.
-  auto issue = [&](int n) {
+  // Block-table entries are fetched one tile ahead of the cp.async that needs them, so the
+  // table load's latency never sits in front of an issue.  blk_a: entry of the tile whose half
+  // tiles are issued next; blk_b: entry of the tile after it.
+  auto table_entry = [&](int i) -> uint32_t {
+    return (UNIFORM && i < my_nt)
+               ? (uint32_t)__ldg(bt_row + ((start + (warp + i * NW) * TR) >> p.bs_shift))
+               : 0u;
+  };
+  uint32_t blk_a = table_entry(0), blk_b = table_entry(1);
+
+  // Issue the n-th half tile (even: K of tile n/2, odd: V) into ring slot `slot`; always commits.
+  auto issue = [&](int n, int slot) {
     if (n < 2 * my_nt) {
       const int tstart = start + (warp + (n >> 1) * NW) * TR;
       const char* base = (n & 1) ? vbase : kbase;
-      const uint32_t dst = ring + (n % RING) * TILEB + h * ROWB + c * 16;
+      const uint32_t dst = ring + slot * TILEB + lane_off;
       if (UNIFORM) {
-        const long long blk = __ldg(bt_row + (tstart >> p.bs_shift));
-        const char* src = base + ((blk << p.bs_shift) + (tstart & bs_mask) + h) * row_pitch;
+        const uint32_t row0 = (blk_a << p.bs_shift) + (tstart & bs_mask) + h;
+        if (tstart + TR <= end) {  // whole tile valid: no per-row predicate
 #pragma unroll
-        for (int j = 0; j < R; ++j) {
-          const bool valid = tstart + j * RPP + h < end;
-          cp_async16(dst + j * RPP * ROWB, src + (long long)(j * RPP) * row_pitch, valid ? 16u : 0u);
+          for (int j = 0; j < R; ++j)
+            cp_async16(dst + j * RPP * ROWB, row_ptr(base, row0 + j * RPP, row_pitch), 16u);
+        } else {
+#pragma unroll
+          for (int j = 0; j < R; ++j)
+            cp_async16(dst + j * RPP * ROWB, row_ptr(base, row0 + j * RPP, row_pitch),
+                       (tstart + j * RPP + h < end) ? 16u : 0u);
         }
       } else {
 #pragma unroll
@@ -184,17 +199,21 @@ paged_decode_split_kernel(const DecodeParams p) {
           const int t = tstart + j * RPP + h;
           const bool valid = t < end;
           const int tt = valid ? t : end - 1;
-          const long long blk = __ldg(bt_row + (tt >> p.bs_shift));
-          const char* src = base + ((blk << p.bs_shift) + (tt & bs_mask)) * row_pitch;
-          cp_async16(dst + j * RPP * ROWB, src, valid ? 16u : 0u);
+          const uint32_t blk = (uint32_t)__ldg(bt_row + (tt >> p.bs_shift));
+          cp_async16(dst + j * RPP * ROWB,
+                     row_ptr(base, (blk << p.bs_shift) + (tt & bs_mask), row_pitch), valid ? 16u : 0u);
         }
       }
     }
     cp_async_commit();
+    if (UNIFORM && (n & 1)) {  // both halves of tile n/2 issued: advance the table prefetch
+      blk_a = blk_b;
+      blk_b = table_entry((n >> 1) + 2);
+    }
   };
 
-#pragma unroll
-  for (int n = 0; n < RING - 1; ++n) issue(n);
+#pragma unroll 1
+  for (int n = 0; n < RING - 1; ++n) issue(n, n);
 
   float m_all[GT];
   u64 o2[GT][NP];
@@ -211,121 +230,148 @@ paged_decode_split_kernel(const DecodeParams p) {
     l_slot[i] = 0.f;
   }
 
-  for (int it = 0; it < my_nt; ++it) {
-    const int tstart = start + (warp + it * NW) * TR;
-    // ================================================================ K: scores
+  // loop-invariant shared-memory addresses, kept to a handful of registers
+  const uint32_t xw = xbuf + lane * (NV * 4) + (xb_key<NQ>(lane) << 4);     // writer: xw ^ (k << 4)
+  const uint32_t xr = xbuf + h * (LPR * NV * 4) + ((idx0 >> 2) << 4) + (idx0 & 3) * 4;  // reader
+  const uint32_t pw = pbuf + (h * NV + idx0) * 8;                           // my (p,p) pairs
+  const uint32_t pr = pbuf + h * NV * 8;                                    // pairs of my row group
+
+  int slot_c = 0;  // ring slot of the half tile being consumed
+#pragma unroll 1
+  for (int n = 0; n < 2 * my_nt; ++n) {
     cp_async_wait<RING - 2>();
     __syncwarp();
-    issue(2 * it + RING - 1);
-    {
-      const uint32_t ks = ring + ((2 * it) % RING) * TILEB + h * ROWB + c * 16;
-      float sv[NV];
-      const int key = xb_key<NQ>(lane);
-      const uint32_t xrow = xbuf + lane * (NV * 4);
+    issue(n + RING - 1, slot_c == 0 ? RING - 1 : slot_c - 1);
+    const uint32_t tile = ring + slot_c * TILEB + lane_off;
+    slot_c = (slot_c + 1 == RING) ? 0 : slot_c + 1;
+    if (!(n & 1)) {
+      // ================================================================ K: scores
+      const int tstart = start + (warp + (n >> 1) * NW) * TR;
+      {
+        float sv[NV];
 #pragma unroll
-      for (int j = 0; j < R; ++j) {
-        u64 k2[NP];
-        Chunk<T>::widen(lds128(ks + j * RPP * ROWB), k2);
+        for (int j = 0; j < R; ++j) {
+          u64 k2[NP];
+          Chunk<T>::widen(lds128(tile + j * RPP * ROWB), k2);
 #pragma unroll
-        for (int g = 0; g < GT; ++g) {
-          u64 acc = 0ull;
+          for (int g = 0; g < GT; ++g) {
+            u64 acc = 0ull;
 #pragma unroll
-          for (int e = 0; e < NP; ++e) acc = ffma2(q2[g][e], k2[e], acc);
-          sv[j * GT + g] = hsum2(acc);
-        }
-        // publish the quads of partial scores completed by this pass (keeps few of them live)
+            for (int e = 0; e < NP; ++e) acc = ffma2(q2[g][e], k2[e], acc);
+            sv[j * GT + g] = hsum2(acc);
+          }
+          // publish the quads of partial scores completed by this pass (keeps few of them live)
 #pragma unroll
-        for (int k = (j * GT) / 4; k < ((j + 1) * GT) / 4; ++k) {
-          uint4 v = make_uint4(__float_as_uint(sv[4 * k]), __float_as_uint(sv[4 * k + 1]),
-                               __float_as_uint(sv[4 * k + 2]), __float_as_uint(sv[4 * k + 3]));
-          sts128(xrow + ((k ^ key) << 4), v);
+          for (int k = (j * GT) / 4; k < ((j + 1) * GT) / 4; ++k)
+            sts128(xor_imm(xw, k << 4),
+                   make_uint4(__float_as_uint(sv[4 * k]), __float_as_uint(sv[4 * k + 1]),
+                              __float_as_uint(sv[4 * k + 2]), __float_as_uint(sv[4 * k + 3])));
         }
       }
-    }
-    __syncwarp();
-    float sc[VPL];
+      __syncwarp();
+      // gather: lane (h,c) sums the LPR partials of its VPL scores (source lane h*LPR+cc, whose
+      // swizzle key depends only on cc & 7)
+      float sc[VPL];
+      {
+        u64 acc2 = 0ull;
+        float acc1 = 0.f;
+        u64 acc4[2] = {0ull, 0ull};
+        constexpr int NK = (NQ >= 8) ? 8 : NQ;       // distinct swizzle keys
+        constexpr int KSH = (NQ >= 8) ? 0 : (NQ == 4 ? 1 : 2);  // key(cc) = (cc >> KSH) & (NK-1)
 #pragma unroll
-    for (int i = 0; i < VPL; ++i) sc[i] = 0.f;
-    {
-      const int quad = idx0 >> 2, w = idx0 & 3;
+        for (int kk = 0; kk < NK; ++kk) {
+          const uint32_t a = xor_imm(xr, kk << 4);
 #pragma unroll
-      for (int cc = 0; cc < LPR; ++cc) {
-        // source lane L' = h*LPR + cc; its key depends only on cc (see xb_key and LPR >= 8)
-        const uint32_t a = xbuf + (h * LPR + cc) * (NV * 4) + ((quad ^ xb_key<NQ>(cc)) << 4) + w * 4;
+          for (int cc = 0; cc < LPR; ++cc) {
+            if (((cc >> KSH) & (NK - 1)) != kk) continue;
+            const uint32_t at = a + cc * (NV * 4);
+            if (VPL == 1) {
+              acc1 += __uint_as_float(lds32(at));
+            } else if (VPL == 2) {
+              uint2 v = lds64(at);
+              acc2 = fadd2(acc2, pack2(__uint_as_float(v.x), __uint_as_float(v.y)));
+            } else {
+              uint4 v = lds128(at);
+              acc4[0] = fadd2(acc4[0], pack2(__uint_as_float(v.x), __uint_as_float(v.y)));
+              acc4[1] = fadd2(acc4[1], pack2(__uint_as_float(v.z), __uint_as_float(v.w)));
+            }
+          }
+        }
         if (VPL == 1) {
-          sc[0] += __uint_as_float(lds32(a));
+          sc[0] = acc1;
         } else if (VPL == 2) {
-          uint2 v = lds64(a);
-          sc[0] += __uint_as_float(v.x);
-          sc[1 % VPL] += __uint_as_float(v.y);
+          unpack2(acc2, sc[0], sc[1 % VPL]);
         } else {
-          uint4 v = lds128(a);
-          sc[0] += __uint_as_float(v.x);
-          sc[1 % VPL] += __uint_as_float(v.y);
-          sc[2 % VPL] += __uint_as_float(v.z);
-          sc[3 % VPL] += __uint_as_float(v.w);
+          unpack2(acc4[0], sc[0], sc[1 % VPL]);
+          unpack2(acc4[1], sc[2 % VPL], sc[3 % VPL]);
         }
       }
-    }
-    // ---- online softmax with a lazily refreshed maximum
-    bool need = false;
+      // ---- online softmax with a lazily refreshed maximum
+      bool need = false;
 #pragma unroll
-    for (int i = 0; i < VPL; ++i) {
-      const bool valid = ok_s[i] && (tstart + rr_s[i] < end);
-      sc[i] = valid ? sc[i] : -INFINITY;
-      need |= sc[i] > m_slot[i] + 8.f;
-    }
-    if (__any_sync(0xffffffffu, need)) {
-      __syncwarp();
-#pragma unroll
-      for (int i = 0; i < VPL; ++i)
-        if (ok_s[i]) sts32(pbuf + (rr_s[i] * GT + g_s[i]) * 4, __float_as_uint(sc[i]));
-      __syncwarp();
-      float mx[GT];
-#pragma unroll
-      for (int g = 0; g < GT; ++g) mx[g] = m_all[g];
-#pragma unroll
-      for (int qd = 0; qd < TR * GT / 4; ++qd) {
-        uint4 v = lds128(pbuf + qd * 16);
-        mx[(4 * qd + 0) % GT] = fmaxf(mx[(4 * qd + 0) % GT], __uint_as_float(v.x));
-        mx[(4 * qd + 1) % GT] = fmaxf(mx[(4 * qd + 1) % GT], __uint_as_float(v.y));
-        mx[(4 * qd + 2) % GT] = fmaxf(mx[(4 * qd + 2) % GT], __uint_as_float(v.z));
-        mx[(4 * qd + 3) % GT] = fmaxf(mx[(4 * qd + 3) % GT], __uint_as_float(v.w));
+      for (int i = 0; i < VPL; ++i) {
+        const bool valid = ok_s[i] && (tstart + rr_s[i] < end);
+        sc[i] = valid ? sc[i] : -INFINITY;
+        need |= sc[i] > m_slot[i] + 8.f;
       }
-#pragma unroll
-      for (int g = 0; g < GT; ++g) {
-        const float alpha = fast_exp2(m_all[g] - mx[g]);  // m_all = -inf -> 0
-        const u64 a2 = pack2(alpha, alpha);
-#pragma unroll
-        for (int e = 0; e < NP; ++e) o2[g][e] = fmul2(o2[g][e], a2);
+      if (__any_sync(0xffffffffu, need)) {
+        // rare: publish raw scores as [row][head], every lane takes the per-head maxima
 #pragma unroll
         for (int i = 0; i < VPL; ++i)
-          if (g_s[i] == g) {
-            l_slot[i] *= alpha;
-            m_slot[i] = mx[g];
-          }
-        m_all[g] = mx[g];
-      }
-      __syncwarp();
-    }
+          if (ok_s[i]) sts32(pbuf + (rr_s[i] * GT + g_s[i]) * 4, __float_as_uint(sc[i]));
+        __syncwarp();
+        float mx[GT];
 #pragma unroll
-    for (int i = 0; i < VPL; ++i) {
-      const float pr = fast_exp2(sc[i] - m_slot[i]);  // masked rows: exp2(-inf) = 0
-      l_slot[i] += pr;
-      if (ok_s[i])
-        sts64(pbuf + (rr_s[i] * GT + g_s[i]) * 8, make_uint2(__float_as_uint(pr), __float_as_uint(pr)));
-    }
-    // ================================================================ V: accumulate P.V
-    cp_async_wait<RING - 2>();
-    __syncwarp();
-    issue(2 * it + RING);
-    {
-      const uint32_t vs = ring + ((2 * it + 1) % RING) * TILEB + h * ROWB + c * 16;
+        for (int g = 0; g < GT; ++g) mx[g] = m_all[g];
+#pragma unroll
+        for (int qd = 0; qd < TR * GT / 4; ++qd) {
+          uint4 v = lds128(pbuf + qd * 16);
+          mx[(4 * qd + 0) % GT] = fmaxf(mx[(4 * qd + 0) % GT], __uint_as_float(v.x));
+          mx[(4 * qd + 1) % GT] = fmaxf(mx[(4 * qd + 1) % GT], __uint_as_float(v.y));
+          mx[(4 * qd + 2) % GT] = fmaxf(mx[(4 * qd + 2) % GT], __uint_as_float(v.z));
+          mx[(4 * qd + 3) % GT] = fmaxf(mx[(4 * qd + 3) % GT], __uint_as_float(v.w));
+        }
+#pragma unroll
+        for (int g = 0; g < GT; ++g) {
+          const float alpha = fast_exp2(m_all[g] - mx[g]);  // m_all = -inf -> 0
+          const u64 a2 = pack2(alpha, alpha);
+#pragma unroll
+          for (int e = 0; e < NP; ++e) o2[g][e] = fmul2(o2[g][e], a2);
+#pragma unroll
+          for (int i = 0; i < VPL; ++i)
+            if (g_s[i] == g) {
+              l_slot[i] *= alpha;
+              m_slot[i] = mx[g];
+            }
+          m_all[g] = mx[g];
+        }
+        __syncwarp();
+      }
+      float pr_v[VPL];
+#pragma unroll
+      for (int i = 0; i < VPL; ++i) {
+        pr_v[i] = fast_exp2(sc[i] - m_slot[i]);  // masked rows: exp2(-inf) = 0
+        l_slot[i] += pr_v[i];
+      }
+      // (p,p) pairs, lane-contiguous: [row group h][idx = pass*GT + head] -> conflict-free stores
+      if (c * VPL < NV) {
+        if (VPL == 1) {
+          sts64(pw, make_uint2(__float_as_uint(pr_v[0]), __float_as_uint(pr_v[0])));
+        } else {
+#pragma unroll
+          for (int i = 0; i < VPL; i += 2)
+            sts128(pw + i * 8, make_uint4(__float_as_uint(pr_v[i]), __float_as_uint(pr_v[i]),
+                                          __float_as_uint(pr_v[(i + 1) % VPL]),
+                                          __float_as_uint(pr_v[(i + 1) % VPL])));
+        }
+      }
+    } else {
+      // ================================================================ V: accumulate P.V
 #pragma unroll
       for (int j = 0; j < R; ++j) {
         u64 v2[NP];
-        Chunk<T>::widen(lds128(vs + j * RPP * ROWB), v2);
-        const uint32_t pa = pbuf + (j * RPP + h) * GT * 8;
+        Chunk<T>::widen(lds128(tile + j * RPP * ROWB), v2);
+        const uint32_t pa = pr + j * GT * 8;
         if (GT == 1) {
           uint2 pp = lds64(pa);
           const u64 p2 = pack2(__uint_as_float(pp.x), __uint_as_float(pp.y));
@@ -346,7 +392,6 @@ paged_decode_split_kernel(const DecodeParams p) {
         }
       }
     }
-    __syncwarp();
   }
   cp_async_wait<0>();
   __syncwarp();
