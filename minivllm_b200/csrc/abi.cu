@@ -76,7 +76,7 @@ struct Plan {
 };
 
 constexpr int kWarps = 4;
-constexpr int kMaxChunk = 1024;
+constexpr int kMaxChunk = 4096;
 
 // Shape checks shared by the planning entry points and mvl_paged_decode.
 int make_plan(long long batch, int H, int KVH, int D, long long max_num_blocks, int block_size,
@@ -100,11 +100,18 @@ int make_plan(long long batch, int H, int KVH, int D, long long max_num_blocks, 
   if (chunk_req > 0) {
     chunk = ((chunk_req + cta_rows - 1) / cta_rows) * cta_rows;
   } else {
-    // Aim for >= 6 CTAs per SM over the worst-case token count, within [cta_rows, kMaxChunk].
+    // Largest power-of-two multiple of cta_rows (<= kMaxChunk) that still leaves the grid about
+    // 16 full waves of resident CTAs (3 per SM) at the worst-case context length.  Measured on
+    // B200 (scripts/sweep_chunks.sh): large chunks win while the grid stays deep (C3: 1024 ->
+    // 93.9 %, 2048 -> 95-96 %, 4096 -> 94 % of peak); mid-size problems want 256-512-token chunks
+    // (C2: 1024 -> 83.6 %, 512 -> 90.8 %, 256 -> 90.3 %) but not less while 256 still fills a wave.
     const double units = (double)(batch > 0 ? batch : 1) * KVH * pl->n_gt;
-    const double want = units * (double)max_ctx / ((double)num_sms * 6.0);
+    const double wave = (double)num_sms * 3.0;
+    auto ctas = [&](long long c) { return units * (double)((max_ctx + c - 1) / c); };
     chunk = cta_rows;
-    while (chunk < kMaxChunk && chunk < want) chunk *= 2;
+    while (chunk * 2 <= kMaxChunk && ctas(chunk * 2) >= 16.0 * wave) chunk *= 2;
+    const int c256 = ((256 + cta_rows - 1) / cta_rows) * cta_rows;
+    if (chunk < c256 && ctas(c256) >= wave) chunk = c256;
   }
   if ((long long)chunk > ((max_ctx + cta_rows - 1) / cta_rows) * cta_rows)
     chunk = (int)(((max_ctx + cta_rows - 1) / cta_rows) * cta_rows);

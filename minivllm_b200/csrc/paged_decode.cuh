@@ -59,7 +59,7 @@ struct DecodeCfg {
   static constexpr int NP = Chunk<T>::NP;       // fp32 pairs per chunk
   static constexpr int LPR = D / VEC;           // lanes per row
   static constexpr int RPP = 32 / LPR;          // rows per pass
-  static constexpr int R = (GT_ >= 8) ? 4 : 8;   // passes per tile
+  static constexpr int R = 8;                   // passes per tile
   static constexpr int TR = R * RPP;            // rows per warp tile
   static constexpr int ROWB = D * ES;           // bytes per row of one kv head
   static constexpr int TILEB = TR * ROWB;       // bytes per K (or V) tile = R * 512
@@ -68,13 +68,14 @@ struct DecodeCfg {
   static constexpr int VPL = (NV / LPR) > 0 ? (NV / LPR) : 1;  // complete scores per lane
   static constexpr int XB_BYTES = 32 * NV * 4;  // transpose buffer
   static constexpr int PB_BYTES = TR * GT * 8;  // (p,p) pairs
-  static constexpr int RING = (GT_ >= 8) ? 5 : 3;  // ring slots; RING-1 half tiles in flight
+  static constexpr int RING = 3;                // ring slots; RING-1 half tiles in flight
   static constexpr int WARP_SMEM = RING * TILEB + XB_BYTES + PB_BYTES;
   static constexpr int SMEM = NW * WARP_SMEM;
   static constexpr int MRG_BYTES = RPP * GT * D * 4 + GT * 8;  // merge area, aliases the ring
   static_assert(LPR >= 8 && LPR <= 32, "head_dim / dtype combination not supported");
   static_assert(MRG_BYTES <= RING * TILEB, "merge area must fit in the ring");
   static_assert(NV % 4 == 0 && NQ >= 2, "NV must be a multiple of 8");
+  static_assert(VPL == 1 || VPL == 2 || VPL == 4 || VPL == 8, "unsupported scores-per-lane");
 };
 
 // XOR swizzle of the transpose buffer: lane L stores quad k at quad (k ^ key(L)).
@@ -273,9 +274,11 @@ paged_decode_split_kernel(const DecodeParams p) {
       // swizzle key depends only on cc & 7)
       float sc[VPL];
       {
-        u64 acc2 = 0ull;
+        constexpr int NPAIR = (VPL + 1) / 2;
+        u64 accp[NPAIR];
         float acc1 = 0.f;
-        u64 acc4[2] = {0ull, 0ull};
+#pragma unroll
+        for (int i = 0; i < NPAIR; ++i) accp[i] = 0ull;
         constexpr int NK = (NQ >= 8) ? 8 : NQ;       // distinct swizzle keys
         constexpr int KSH = (NQ >= 8) ? 0 : (NQ == 4 ? 1 : 2);  // key(cc) = (cc >> KSH) & (NK-1)
 #pragma unroll
@@ -289,21 +292,26 @@ paged_decode_split_kernel(const DecodeParams p) {
               acc1 += __uint_as_float(lds32(at));
             } else if (VPL == 2) {
               uint2 v = lds64(at);
-              acc2 = fadd2(acc2, pack2(__uint_as_float(v.x), __uint_as_float(v.y)));
+              accp[0] = fadd2(accp[0], pack2(__uint_as_float(v.x), __uint_as_float(v.y)));
             } else {
-              uint4 v = lds128(at);
-              acc4[0] = fadd2(acc4[0], pack2(__uint_as_float(v.x), __uint_as_float(v.y)));
-              acc4[1] = fadd2(acc4[1], pack2(__uint_as_float(v.z), __uint_as_float(v.w)));
+              // VPL = 4 or 8: consecutive quads; the swizzle flips quad bits, so quad q4 of this
+              // lane's run sits at (at ^ (q4 << 4)) (the run starts at an even multiple of VPL/4)
+#pragma unroll
+              for (int q4 = 0; q4 < VPL / 4; ++q4) {
+                uint4 v = lds128(at ^ (q4 << 4));
+                accp[(2 * q4) % NPAIR] = fadd2(accp[(2 * q4) % NPAIR],
+                                              pack2(__uint_as_float(v.x), __uint_as_float(v.y)));
+                accp[(2 * q4 + 1) % NPAIR] = fadd2(accp[(2 * q4 + 1) % NPAIR],
+                                                  pack2(__uint_as_float(v.z), __uint_as_float(v.w)));
+              }
             }
           }
         }
         if (VPL == 1) {
           sc[0] = acc1;
-        } else if (VPL == 2) {
-          unpack2(acc2, sc[0], sc[1 % VPL]);
         } else {
-          unpack2(acc4[0], sc[0], sc[1 % VPL]);
-          unpack2(acc4[1], sc[2 % VPL], sc[3 % VPL]);
+#pragma unroll
+          for (int i = 0; i < NPAIR; ++i) unpack2(accp[i], sc[(2 * i) % VPL], sc[(2 * i + 1) % VPL]);
         }
       }
       // ---- online softmax with a lazily refreshed maximum

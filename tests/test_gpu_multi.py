@@ -1,0 +1,84 @@
+"""GPU (-m gpu): KV-head sharding.  The concatenation of per-rank outputs must equal the unsharded
+run BIT FOR BIT (same reduction order per head).  With one GPU the ranks run one
+after the other on it; with >= 2 GPUs a second test runs real ranks over NCCL and checks
+``gather_heads`` on every rank.
+"""
+import os
+import sys
+
+import pytest
+import torch
+
+from cases import make_inputs
+from minivllm_b200.head_shard import shard_plan
+from minivllm_b200.layers.attention import paged_attention_decode, store_kvcache
+
+pytestmark = pytest.mark.gpu
+
+
+def _local_decode(inp, sh, dev):
+    q = inp["q"][:, sh.q_heads].contiguous().to(dev)
+    kc = inp["k_cache"][:, :, sh.kv_heads].contiguous().to(dev)
+    vc = inp["v_cache"][:, :, sh.kv_heads].contiguous().to(dev)
+    return paged_attention_decode(q, kc, vc, inp["block_tables"].to(dev), inp["context_lens"].to(dev),
+                                  inp["scale"], sh.num_heads, sh.num_kv_heads, inp["D"], inp["BS"])
+
+
+@pytest.mark.parametrize("name,world", [("ragged_bf16", 2), ("ragged_bf16", 4), ("ragged_bf16", 8),
+                                        ("long_split", 2), ("g8_ragged", 2)])
+def test_sharded_equals_unsharded_bitwise(cuda_device, name, world):
+    inp = make_inputs(name)
+    full = _local_decode(inp, shard_plan(inp["H"], inp["KVH"], 1, 0), cuda_device)
+    parts = [_local_decode(inp, shard_plan(inp["H"], inp["KVH"], world, r), cuda_device)
+             for r in range(world)]
+    assert torch.equal(torch.cat(parts, dim=1), full)
+
+
+def test_sharded_store_is_a_slice_of_the_full_store(cuda_device):
+    inp = make_inputs("ragged_bf16")
+    KVH, D, BS = inp["KVH"], inp["D"], inp["BS"]
+    g = torch.Generator().manual_seed(9)
+    k = torch.randn(8, KVH, D, generator=g).to(torch.bfloat16)
+    v = torch.randn(8, KVH, D, generator=g).to(torch.bfloat16)
+    slots = torch.tensor([5, -1, 77, 300, 2, 19, 640, 1])
+    kc, vc = inp["k_cache"].to(cuda_device), inp["v_cache"].to(cuda_device)
+    store_kvcache(k.to(cuda_device), v.to(cuda_device), kc, vc, slots.to(cuda_device), BS)
+    for r in range(4):
+        sh = shard_plan(inp["H"], KVH, 4, r)
+        kc_r = inp["k_cache"][:, :, sh.kv_heads].contiguous().to(cuda_device)
+        vc_r = inp["v_cache"][:, :, sh.kv_heads].contiguous().to(cuda_device)
+        store_kvcache(k[:, sh.kv_heads].to(cuda_device), v[:, sh.kv_heads].to(cuda_device), kc_r, vc_r,
+                      slots.to(cuda_device), BS)
+        assert torch.equal(kc_r, kc[:, :, sh.kv_heads]) and torch.equal(vc_r, vc[:, :, sh.kv_heads])
+
+
+def _nccl_worker(rank, world, port, ret):
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    from minivllm_b200.head_shard import gather_heads
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dev = torch.device("cuda", rank)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        inp = make_inputs("ragged_bf16")
+        full = _local_decode(inp, shard_plan(inp["H"], inp["KVH"], 1, 0), dev)
+        local = _local_decode(inp, shard_plan(inp["H"], inp["KVH"], world, rank), dev)
+        got = gather_heads(local)
+        torch.cuda.synchronize()
+        ret[rank] = bool(torch.equal(got, full))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_nccl_gather_on_real_ranks(cuda_device):
+    world = min(torch.cuda.device_count(), 8)
+    world = 1 << (world.bit_length() - 1)
+    if world < 2:
+        pytest.skip("needs >= 2 GPUs (covered on CPU over gloo by tests/test_head_shard_gloo.py)")
+    import torch.multiprocessing as mp
+    port = 29500 + os.getpid() % 2000
+    with mp.Manager() as mgr:
+        ret = mgr.dict()
+        mp.spawn(_nccl_worker, args=(world, port, ret), nprocs=world, join=True)
+        assert dict(ret) == {r: True for r in range(world)}

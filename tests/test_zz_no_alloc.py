@@ -98,8 +98,8 @@ def test_static_entry_matches_workspace_entry_twice_in_a_row(cuda_device):
 
 def test_static_entry_refuses_what_does_not_fit(cuda_device):
     lib = _ext.lib()
-    # 256 sequences x 32 heads x 8 chunks of partials (the C3 bench shape) need ~34 MB > 16 MiB
-    B, H, KVH, D, BS, W = 256, 32, 8, 128, 16, 512
+    # 256 sequences x 32 heads x 16 chunks of partials (64k-token tables) need ~68 MB > 16 MiB
+    B, H, KVH, D, BS, W = 256, 32, 8, 128, 16, 4096
     q = torch.zeros(B, H, D, dtype=torch.bfloat16, device=cuda_device)
     kc = torch.zeros(4, BS, KVH, D, dtype=torch.bfloat16, device=cuda_device)
     inp = dict(q=q, k_cache=kc, v_cache=kc, H=H, KVH=KVH, D=D, BS=BS, scale=1.0,
