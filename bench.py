@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--cpu-seqs", type=int, default=8, help="sequences in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                    help="N>1: how the per-rank heads are gathered (fused peer stores, or NCCL)")
     return ap.parse_args()
 
 
@@ -201,6 +203,20 @@ def run_ours(args, rank, world, local_rank):
     B = w["B"]
     out = torch.empty_like(w["q"])
     staging = torch.empty((world, B, w["H"], w["D"]), dtype=out.dtype, device=dev) if world > 1 else None
+    fused, gather_kind = None, "none"
+    if world > 1 and args.gather == "peer":
+        try:
+            from minivllm_b200.head_shard import PeerGatheredDecode
+            fused = PeerGatheredDecode(sh, B, sp.H, sp.D, out.dtype, dev)
+            gather_kind = "peer stores from the decode kernels (mvl_paged_decode_peers) + barrier"
+        except Exception as exc:  # symmetric memory unavailable on this box: say so, use NCCL
+            gather_kind = f"NCCL all-gather (peer-memory setup failed: {type(exc).__name__})"
+        ok = torch.tensor([1 if fused is not None else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok) == 0:
+            fused = None
+    elif world > 1:
+        gather_kind = "NCCL all-gather + permute copy"
     dec_args = (w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"], w["H"],
                 w["KVH"], w["D"], w["BS"])
     lib = _ext.lib()
@@ -213,6 +229,16 @@ def run_ours(args, rank, world, local_rank):
         store_kvcache(w["k"], w["v"], w["k_cache"], w["v_cache"], w["slot_mapping"], w["BS"])
         if ev is not None:
             ev[0].record()
+        if fused is not None:
+            fargs = (w["q"], w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"],
+                     w["scale"], w["BS"])
+            fused(*fargs, chunk_tokens=args.chunk, flags=_ext.DECODE_SKIP_COMBINE, barrier=False)
+            if ev is not None:
+                ev[1].record()
+            if multi_split:
+                fused(*fargs, chunk_tokens=args.chunk, flags=_ext.DECODE_ONLY_COMBINE, barrier=False)
+            fused.barrier()
+            return fused.out
         paged_attention_decode(w["q"], *dec_args, out=out, chunk_tokens=args.chunk,
                                flags=_ext.DECODE_SKIP_COMBINE)
         if ev is not None:
@@ -319,7 +345,7 @@ def run_ours(args, rank, world, local_rank):
         "config": {"workload": args.workload, "shape": f"{sp.H}Q/{sp.KVH}KV/D{sp.D}", "batch": B,
                    "block_size": sp.BS, "context_tokens": int(t.ctx.sum()),
                    "context_range": [int(t.ctx.min()), int(t.ctx.max())], "chunk_tokens": int(chunk),
-                   "parallelism": f"kv-head-shard x{world}" + (" + NCCL all-gather" if world > 1 else ""),
+                   "parallelism": f"kv-head-shard x{world}", "gather": gather_kind,
                    "l2": "inputs larger than L2 (KV bytes per step >> 126 MB); no flush needed"
                          if alg_unique > 4 * 126e6 else "KV fits in L2: number is L2-assisted"},
         "hbm_gbs_step": alg_unique / (ms_step * 1e-3) / 1e9,

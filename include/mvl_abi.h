@@ -122,6 +122,26 @@ int mvl_paged_decode(void* out, const void* query, const void* k_cache, const vo
                      size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream);
 
 /*
+ * mvl_paged_decode_peers — mvl_paged_decode whose result stores also perform the all-gather of a
+ * KV-head-sharded run.  Rank r of N computes num_heads = total_heads / N local heads and writes
+ * them at head offset head_offset into EVERY destination out_peers[0..num_peers): each is a
+ * (batch, total_heads, head_dim) tensor, normally the peer-mapped (NVLink P2P) result buffer of
+ * one rank of the node, so after the kernels of all ranks have run and the ranks have met in a
+ * barrier every rank holds all heads — no separate collective, no head-major -> batch-major copy.
+ * The reference has no such step (attention is followed by row-parallel o_proj + all-reduce,
+ * linear.py:216-221); this is the "all-gather where o_proj needs full heads" of BASELINE.json's
+ * north_star, fused into the producing kernels.  num_peers <= 8.  With num_peers = 1,
+ * total_heads = num_heads, head_offset = 0 it is exactly mvl_paged_decode.
+ */
+int mvl_paged_decode_peers(void* const* out_peers, int num_peers, int total_heads, int head_offset,
+                           const void* query, const void* k_cache, const void* v_cache,
+                           const int32_t* block_tables, const void* context_lens, int ctx_is_i64,
+                           int64_t batch, int64_t max_num_blocks, int64_t block_table_stride,
+                           int num_heads, int num_kv_heads, int head_dim, int block_size,
+                           int64_t num_blocks, float scale, int elem_dtype, void* workspace,
+                           size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream);
+
+/*
  * mvl_decode_step_host — one decode-attention step of a layer driven from HOST buffers:
  * async H2D of the step's inputs (pinned host memory recommended) into caller-provided device
  * staging buffers, mvl_store_kvcache, mvl_paged_decode, async D2H of the result.  The caller

@@ -31,6 +31,8 @@ PROTOTYPES = {
     "mvl_paged_decode_workspace_bytes": (_sz, [_i64, _i, _i, _i, _i64, _i, _i, _i]),
     "mvl_paged_decode": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i64, _i64, _i64, _i, _i, _i, _i,
                               _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
+    "mvl_paged_decode_peers": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _i64, _i64, _i64, _i,
+                                    _i, _i, _i, _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
     "mvl_decode_step_host": (_i, [_vp] * 16 + [_i, _i64, _i64, _i, _i, _i, _i, _i64, _f, _i, _vp,
                                                _sz, _i, _vp]),
     "mvl_paged_decode_static": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i64, _i64, _i64, _i, _i, _i,

@@ -204,7 +204,8 @@ size_t mvl_paged_decode_workspace_bytes(int64_t batch, int num_heads, int num_kv
   return plan_workspace(pl, batch, num_heads, head_dim);
 }
 
-int mvl_paged_decode(void* out, const void* query, const void* k_cache, const void* v_cache,
+static int decode_impl(void* const* outs, int n_out, int h_out, int head_off, const void* query,
+                       const void* k_cache, const void* v_cache,
                      const int32_t* block_tables, const void* context_lens, int ctx_is_i64,
                      int64_t batch, int64_t max_num_blocks, int64_t block_table_stride,
                      int num_heads, int num_kv_heads, int head_dim, int block_size,
@@ -219,9 +220,15 @@ int mvl_paged_decode(void* out, const void* query, const void* k_cache, const vo
   if (st != MVL_OK) return st;
   if (batch == 0) return MVL_OK;
   if (num_blocks <= 0 || block_table_stride < max_num_blocks) return MVL_ERR_SHAPE;
-  if (!out || !query || !k_cache || !v_cache || !block_tables || !context_lens)
+  if (!outs || !query || !k_cache || !v_cache || !block_tables || !context_lens)
     return MVL_ERR_NULL_POINTER;
-  if (!aligned16(out) || !aligned16(query) || !aligned16(k_cache) || !aligned16(v_cache) ||
+  if (n_out < 1 || n_out > 8) return MVL_ERR_LIMIT;
+  if (head_off < 0 || head_off + num_heads > h_out) return MVL_ERR_SHAPE;
+  for (int r = 0; r < n_out; ++r) {
+    if (!outs[r]) return MVL_ERR_NULL_POINTER;
+    if (!aligned16(outs[r])) return MVL_ERR_ALIGNMENT;
+  }
+  if (!aligned16(query) || !aligned16(k_cache) || !aligned16(v_cache) ||
       (reinterpret_cast<uintptr_t>(block_tables) & 3u) ||
       (reinterpret_cast<uintptr_t>(context_lens) & (ctx_is_i64 ? 7u : 3u)))
     return MVL_ERR_ALIGNMENT;
@@ -231,7 +238,10 @@ int mvl_paged_decode(void* out, const void* query, const void* k_cache, const vo
 
   mvl::DecodeParams p;
   memset(&p, 0, sizeof(p));
-  p.out = out;
+  for (int r = 0; r < n_out; ++r) p.outs[r] = outs[r];
+  p.n_out = n_out;
+  p.H_out = h_out;
+  p.head_off = head_off;
   p.q = query;
   p.kc = k_cache;
   p.vc = v_cache;
@@ -256,7 +266,7 @@ int mvl_paged_decode(void* out, const void* query, const void* k_cache, const vo
 
   cudaStream_t s = (cudaStream_t)stream;
   if (!(flags & MVL_DECODE_ONLY_COMBINE)) {
-    dim3 grid((unsigned)(num_kv_heads * pl.n_gt), (unsigned)pl.max_splits, (unsigned)batch);
+    dim3 grid((unsigned)(num_kv_heads * pl.n_gt), (unsigned)batch, (unsigned)pl.max_splits);
     int e = -1000;
     switch (elem_dtype) {
       case MVL_DTYPE_F32: e = mvl::launch_decode_split<float>(p, head_dim, pl.gt, grid, s); break;
@@ -280,6 +290,32 @@ int mvl_paged_decode(void* out, const void* query, const void* k_cache, const vo
     if (e != 0) return cuda_fail((cudaError_t)e, "paged_decode_combine launch");
   }
   return MVL_OK;
+}
+
+int mvl_paged_decode(void* out, const void* query, const void* k_cache, const void* v_cache,
+                     const int32_t* block_tables, const void* context_lens, int ctx_is_i64,
+                     int64_t batch, int64_t max_num_blocks, int64_t block_table_stride,
+                     int num_heads, int num_kv_heads, int head_dim, int block_size,
+                     int64_t num_blocks, float scale, int elem_dtype, void* workspace,
+                     size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream) {
+  void* outs[1] = {out};
+  return decode_impl(outs, 1, num_heads, 0, query, k_cache, v_cache, block_tables, context_lens,
+                     ctx_is_i64, batch, max_num_blocks, block_table_stride, num_heads, num_kv_heads,
+                     head_dim, block_size, num_blocks, scale, elem_dtype, workspace, workspace_bytes,
+                     chunk_tokens, flags, stream);
+}
+
+int mvl_paged_decode_peers(void* const* out_peers, int num_peers, int total_heads, int head_offset,
+                           const void* query, const void* k_cache, const void* v_cache,
+                           const int32_t* block_tables, const void* context_lens, int ctx_is_i64,
+                           int64_t batch, int64_t max_num_blocks, int64_t block_table_stride,
+                           int num_heads, int num_kv_heads, int head_dim, int block_size,
+                           int64_t num_blocks, float scale, int elem_dtype, void* workspace,
+                           size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream) {
+  return decode_impl(out_peers, num_peers, total_heads, head_offset, query, k_cache, v_cache,
+                     block_tables, context_lens, ctx_is_i64, batch, max_num_blocks,
+                     block_table_stride, num_heads, num_kv_heads, head_dim, block_size, num_blocks,
+                     scale, elem_dtype, workspace, workspace_bytes, chunk_tokens, flags, stream);
 }
 
 int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_host,

@@ -4,7 +4,7 @@
 // (reference src/myvllm/layers/attention.py:283-415): same math, different machine mapping.
 //
 // Work decomposition
-//   grid = (num_kv_heads * head_tiles, max_splits, batch).  One CTA owns the tokens
+//   grid = (num_kv_heads * head_tiles, batch, max_splits).  One CTA owns the tokens
 //   [split*chunk, min(ctx, (split+1)*chunk)) of one sequence for ONE kv head and ALL query heads of
 //   its GQA group (GT heads per tile), so every K/V byte is fetched from HBM once per group instead
 //   of once per query head (the reference's grid (batch, num_heads) re-reads it G times,
@@ -30,7 +30,12 @@
 namespace mvl {
 
 struct DecodeParams {
-  void* out;
+  // Result destinations: outs[0..n_out) are (batch, H_out, D) tensors; this launch's heads land at
+  // head offset head_off in each.  n_out = 1, H_out = H, head_off = 0 is the plain single-GPU case;
+  // with head sharding outs[] are the peer-mapped full-head buffers of all ranks, so the result is
+  // all-gathered by the stores themselves (NVLink P2P) instead of by a separate collective.
+  void* outs[8];
+  int n_out, H_out, head_off;
   const void* q;
   const void* kc;
   const void* vc;
@@ -48,6 +53,22 @@ struct DecodeParams {
   int max_splits;
   float qscale;      // scale * log2(e)
 };
+
+// Store 4 consecutive result elements of (sequence b, local head) to every destination.
+template <typename T, int D>
+__device__ __forceinline__ void store_out4(const DecodeParams& p, long long b, int head, int d0,
+                                           float a, float b1, float c, float d) {
+  const long long off = (b * p.H_out + p.head_off + head) * D + d0;
+#pragma unroll 1
+  for (int r = 0; r < p.n_out; ++r) store4<T>(reinterpret_cast<T*>(p.outs[r]) + off, a, b1, c, d);
+}
+template <typename T, int D>
+__device__ __forceinline__ void store_out2(const DecodeParams& p, long long b, int head, int d0,
+                                           float a, float b1) {
+  const long long off = (b * p.H_out + p.head_off + head) * D + d0;
+#pragma unroll 1
+  for (int r = 0; r < p.n_out; ++r) store2<T>(reinterpret_cast<T*>(p.outs[r]) + off, a, b1);
+}
 
 template <typename T, int D_, int GT_>
 struct DecodeCfg {
@@ -100,7 +121,10 @@ paged_decode_split_kernel(const DecodeParams p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int h = lane / LPR, c = lane % LPR;
   const int kvh = blockIdx.x / p.n_gt, gt = blockIdx.x % p.n_gt;
-  const int split = blockIdx.y, b = blockIdx.z;
+  // y = sequence, z = chunk: CTAs of the same chunk index of all sequences are scheduled together,
+  // so sequences whose block tables alias (shared prefixes) read the same pages at about the same
+  // time and all but the first reader hit L2.
+  const int b = blockIdx.y, split = blockIdx.z;
   const int head0 = kvh * p.G + gt * GT;
   const int g_valid = min(GT, p.G - gt * GT);
 
@@ -108,13 +132,12 @@ paged_decode_split_kernel(const DecodeParams p) {
                                   : (long long)reinterpret_cast<const int*>(p.ctx)[b];
   if (ctx_ll > p.max_ctx) ctx_ll = p.max_ctx;
   const int ctx = (int)ctx_ll;
-  T* out = reinterpret_cast<T*>(p.out);
 
   if (ctx <= 0) {  // graph-padding row: defined as zeros (reference gives 0/0)
     if (split == 0)
       for (int i = threadIdx.x; i < g_valid * (D / 4); i += NW * 32) {
         const int g = i / (D / 4), dq = i % (D / 4);
-        store4<T>(out + ((long long)b * p.H + head0 + g) * D + dq * 4, 0.f, 0.f, 0.f, 0.f);
+        store_out4<T, D>(p, b, head0 + g, dq * 4, 0.f, 0.f, 0.f, 0.f);
       }
     return;
   }
@@ -470,7 +493,7 @@ paged_decode_split_kernel(const DecodeParams p) {
     const long long bh = (long long)b * p.H + head0 + g;
     if (n_act == 1) {
       const float inv = 1.f / Lsum;
-      store4<T>(out + bh * D + dq * 4, a0 * inv, a1 * inv, a2 * inv, a3 * inv);
+      store_out4<T, D>(p, b, head0 + g, dq * 4, a0 * inv, a1 * inv, a2 * inv, a3 * inv);
     } else {
       const long long pi = bh * p.max_splits + split;
       *reinterpret_cast<float4*>(p.part_o + pi * D + dq * 4) = make_float4(a0, a1, a2, a3);
@@ -535,11 +558,12 @@ __global__ void __launch_bounds__(128) paged_decode_combine_kernel(const DecodeP
     for (int e = 0; e < EPL; ++e) acc[e] += w * po[(long long)s * D + e];
   }
   const float inv = 1.f / Lsum;
-  T* dst = reinterpret_cast<T*>(p.out) + bh * D + lane * EPL;
+  const int head = (int)(bh - b * p.H);
   if (EPL == 4) {
-    store4<T>(dst, acc[0] * inv, acc[1] * inv, acc[2 % EPL] * inv, acc[3 % EPL] * inv);
+    store_out4<T, D>(p, b, head, lane * EPL, acc[0] * inv, acc[1] * inv, acc[2 % EPL] * inv,
+                     acc[3 % EPL] * inv);
   } else {
-    store2<T>(dst, acc[0] * inv, acc[1] * inv);
+    store_out2<T, D>(p, b, head, lane * EPL, acc[0] * inv, acc[1] * inv);
   }
 }
 

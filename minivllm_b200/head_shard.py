@@ -67,3 +67,66 @@ def gather_heads(o_local: torch.Tensor, group: Optional[dist.ProcessGroup] = Non
         staging = torch.empty((world, B, h, D), dtype=o_local.dtype, device=o_local.device)
     dist.all_gather_into_tensor(staging.view(world * B, h, D), o_local.contiguous(), group=group)
     return staging.permute(1, 0, 2, 3).reshape(B, world * h, D)
+
+
+class PeerGatheredDecode:
+    """Head-sharded decode whose result stores ARE the all-gather (``mvl_paged_decode_peers``).
+
+    Every rank owns a (batch, total_heads, head_dim) result buffer in symmetric (peer-mapped)
+    memory.  A rank's decode kernels write its heads straight into all ranks' buffers over NVLink
+    P2P; one barrier on the symmetric-memory signal pads then makes every buffer complete.  Compared
+    with ``gather_heads`` this removes the NCCL all-gather launch and the (N,B,h,D)->(B,H,D)
+    permute copy from the step.  ``torch.distributed._symmetric_memory`` is used for the plumbing
+    only (allocation, handle exchange, barrier); the data path is our kernels' stores.
+    """
+
+    def __init__(self, shard: HeadShard, batch: int, total_heads: int, head_dim: int,
+                 dtype: torch.dtype, device: torch.device, group: Optional[dist.ProcessGroup] = None):
+        import ctypes
+
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.shard, self.batch, self.total_heads, self.head_dim = shard, batch, total_heads, head_dim
+        self.group = group if group is not None else dist.group.WORLD
+        self.out = symm_mem.empty((batch, total_heads, head_dim), dtype=dtype, device=device)
+        self.handle = symm_mem.rendezvous(self.out, self.group)
+        ptrs = list(self.handle.buffer_ptrs)
+        if len(ptrs) != shard.world_size:
+            raise RuntimeError("symmetric-memory rendezvous returned the wrong number of peers")
+        self._ptr_array = (ctypes.c_void_p * len(ptrs))(*ptrs)
+        self.device = device
+
+    def __call__(self, query, k_cache, v_cache, block_tables, context_lens, scale, block_size,
+                 chunk_tokens: int = 0, flags: int = 0, barrier: bool = True) -> torch.Tensor:
+        """Decode this rank's heads into every rank's buffer; returns this rank's full
+        (batch, total_heads, head_dim) buffer (complete after the barrier)."""
+        import ctypes
+
+        from . import _ext
+        from .layers import attention as att
+
+        sh = self.shard
+        batch, max_blocks = query.shape[0], block_tables.shape[1]
+        code = att._dtype_code(query)
+        lib = _ext.lib()
+        with att._on_device(self.device):
+            nbytes = lib.mvl_paged_decode_workspace_bytes(batch, sh.num_heads, sh.num_kv_heads,
+                                                          self.head_dim, max_blocks, block_size, code,
+                                                          chunk_tokens)
+            ws = att.workspace_for(self.device, nbytes)
+            _ext.check(lib.mvl_paged_decode_peers(
+                ctypes.cast(self._ptr_array, ctypes.c_void_p), sh.world_size, self.total_heads,
+                sh.q_heads.start, query.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+                block_tables.data_ptr(), context_lens.data_ptr(),
+                att._index_flag("context_lens", context_lens), batch, max_blocks, block_tables.stride(0),
+                sh.num_heads, sh.num_kv_heads, self.head_dim, block_size, k_cache.shape[0],
+                float(scale), code, ws.data_ptr() if ws is not None else None,
+                ws.numel() if ws is not None else 0, chunk_tokens, flags,
+                att._stream_ptr(self.device)))
+            if barrier:
+                self.barrier()
+        return self.out
+
+    def barrier(self) -> None:
+        """All ranks' stores issued before this point are visible in every buffer after it."""
+        self.handle.barrier(channel=0)

@@ -60,6 +60,29 @@ def _stream_ptr(dev: torch.device) -> int:
     return torch.cuda.current_stream(dev).cuda_stream
 
 
+class _on_device:
+    """``with torch.cuda.device(dev)`` only when ``dev`` is not already current (saves ~10 us/call)."""
+
+    __slots__ = ("dev", "ctx")
+
+    def __init__(self, dev: torch.device):
+        self.dev, self.ctx = dev, None
+
+    def __enter__(self):
+        if torch.cuda.current_device() != self.dev.index:
+            self.ctx = torch.cuda.device(self.dev)
+            self.ctx.__enter__()
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+
+
+# (batch, H, KVH, D, max_blocks, BS, dtype code, chunk, device) -> workspace bytes; the plan is a
+# pure function of these, so it is asked of the library once per shape.
+_plan_cache: dict = {}
+
+
 def workspace_for(dev: torch.device, nbytes: int) -> Optional[torch.Tensor]:
     """Scratch for the split-KV partials on torch's current stream of ``dev`` (None if nbytes == 0)."""
     if nbytes == 0:
@@ -104,7 +127,7 @@ def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor,
     key, value = rows(key), rows(value)
     slot_mapping = slot_mapping.contiguous()
     dense_stride = num_kv_heads * head_dim
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         _ext.check(_ext.lib().mvl_store_kvcache(
             key.data_ptr(), value.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
             slot_mapping.data_ptr(), _index_flag("slot_mapping", slot_mapping), num_tokens,
@@ -160,9 +183,13 @@ def paged_attention_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: 
         return out.zero_() if max_num_blocks == 0 else out
     code = _dtype_code(query)
     handle = _ext.lib()
-    with torch.cuda.device(dev):
-        nbytes = handle.mvl_paged_decode_workspace_bytes(
-            batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, code, chunk_tokens)
+    with _on_device(dev):
+        key = (batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, code, chunk_tokens,
+               dev.index)
+        nbytes = _plan_cache.get(key)
+        if nbytes is None:
+            nbytes = _plan_cache[key] = handle.mvl_paged_decode_workspace_bytes(
+                batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, code, chunk_tokens)
         ws = workspace_for(dev, nbytes)
         _ext.check(handle.mvl_paged_decode(
             out.data_ptr(), query.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),

@@ -52,6 +52,43 @@ def test_sharded_store_is_a_slice_of_the_full_store(cuda_device):
         assert torch.equal(kc_r, kc[:, :, sh.kv_heads]) and torch.equal(vc_r, vc[:, :, sh.kv_heads])
 
 
+@pytest.mark.parametrize("name,world", [("ragged_bf16", 2), ("long_split", 2), ("ragged_bf16", 8)])
+def test_peer_stores_gather_on_one_gpu(cuda_device, name, world):
+    """mvl_paged_decode_peers with every "peer" buffer on this GPU: each emulated rank writes its
+    heads at its head offset into all destination buffers; all buffers must end up equal to the
+    unsharded result (includes a zero-length row, written by the zero-fill path)."""
+    import ctypes
+
+    from minivllm_b200 import _ext
+    from minivllm_b200.layers import attention as att
+    inp = make_inputs(name)
+    inp["context_lens"] = inp["context_lens"].clone()
+    inp["context_lens"][1] = 0
+    full = _local_decode(inp, shard_plan(inp["H"], inp["KVH"], 1, 0), cuda_device)
+    B, H, D = inp["q"].shape
+    bufs = [torch.full((B, H, D), float("nan"), dtype=inp["q"].dtype, device=cuda_device)
+            for _ in range(world)]
+    ptrs = (ctypes.c_void_p * world)(*[t.data_ptr() for t in bufs])
+    bt, cl = inp["block_tables"].to(cuda_device), inp["context_lens"].to(cuda_device)
+    lib = _ext.lib()
+    for r in range(world):
+        sh = shard_plan(H, inp["KVH"], world, r)
+        q = inp["q"][:, sh.q_heads].contiguous().to(cuda_device)
+        kc = inp["k_cache"][:, :, sh.kv_heads].contiguous().to(cuda_device)
+        vc = inp["v_cache"][:, :, sh.kv_heads].contiguous().to(cuda_device)
+        nbytes = lib.mvl_paged_decode_workspace_bytes(B, sh.num_heads, sh.num_kv_heads, D, bt.shape[1],
+                                                      inp["BS"], att._dtype_code(q), 0)
+        ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=cuda_device)
+        _ext.check(lib.mvl_paged_decode_peers(
+            ctypes.cast(ptrs, ctypes.c_void_p), world, H, sh.q_heads.start, q.data_ptr(), kc.data_ptr(),
+            vc.data_ptr(), bt.data_ptr(), cl.data_ptr(), int(cl.dtype == torch.int64), B, bt.shape[1],
+            bt.stride(0), sh.num_heads, sh.num_kv_heads, D, inp["BS"], kc.shape[0], float(inp["scale"]),
+            att._dtype_code(q), ws.data_ptr(), nbytes, 0, 0, torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    for buf in bufs:
+        assert torch.equal(buf, full)
+
+
 def _nccl_worker(rank, world, port, ret):
     import torch.distributed as dist
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
@@ -66,7 +103,23 @@ def _nccl_worker(rank, world, port, ret):
         local = _local_decode(inp, shard_plan(inp["H"], inp["KVH"], world, rank), dev)
         got = gather_heads(local)
         torch.cuda.synchronize()
-        ret[rank] = bool(torch.equal(got, full))
+        ok = bool(torch.equal(got, full))
+        # the same gather done by the decode kernels' own stores into peer-mapped buffers
+        from minivllm_b200.head_shard import PeerGatheredDecode
+        sh = shard_plan(inp["H"], inp["KVH"], world, rank)
+        fused = PeerGatheredDecode(sh, inp["q"].shape[0], inp["H"], inp["D"], inp["q"].dtype, dev)
+        q = inp["q"][:, sh.q_heads].contiguous().to(dev)
+        kc = inp["k_cache"][:, :, sh.kv_heads].contiguous().to(dev)
+        vc = inp["v_cache"][:, :, sh.kv_heads].contiguous().to(dev)
+        bt, cl = inp["block_tables"].to(dev), inp["context_lens"].to(dev)
+        for _ in range(3):  # repeated steps reuse the buffers
+            fused.out.fill_(float("nan"))
+            fused.barrier()
+            res = fused(q, kc, vc, bt, cl, inp["scale"], inp["BS"])
+            torch.cuda.synchronize()
+            ok = ok and bool(torch.equal(res, full))
+            fused.barrier()
+        ret[rank] = ok
     finally:
         dist.destroy_process_group()
 
