@@ -43,7 +43,12 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--workload", default="c3", choices=sorted(workloads.SPECS))
+    ap.add_argument("--workload", default="c3", choices=sorted(workloads.SPECS) + ["c2e"],
+                    help="c1..c5: one attention call per step; c2e: 28-layer engine-shaped decode "
+                         "loop of config 2 under CUDA-graph replay")
+    ap.add_argument("--eager", action="store_true", help="c2e: no CUDA graphs")
+    ap.add_argument("--shard-of", type=int, default=1,
+                    help="tuning aid: run rank 0's KV-head shard of an N-way split on ONE GPU, no gather")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--chunk", type=int, default=0, help="split size override (tokens)")
     ap.add_argument("--cpu-seqs", type=int, default=8, help="sequences in the CPU-baseline sample")
@@ -199,6 +204,8 @@ def run_ours(args, rank, world, local_rank):
     t = workloads.build_tables(args.workload)
     sp = t.spec
     sh = shard_plan(sp.H, sp.KVH, world, rank)
+    if world == 1 and args.shard_of > 1:
+        sh = shard_plan(sp.H, sp.KVH, args.shard_of, 0)
     w = workloads.materialize(t, dev, kv_heads=sh.kv_heads, seed_offset=rank)
     B = w["B"]
     out = torch.empty_like(w["q"])
@@ -345,7 +352,9 @@ def run_ours(args, rank, world, local_rank):
         "config": {"workload": args.workload, "shape": f"{sp.H}Q/{sp.KVH}KV/D{sp.D}", "batch": B,
                    "block_size": sp.BS, "context_tokens": int(t.ctx.sum()),
                    "context_range": [int(t.ctx.min()), int(t.ctx.max())], "chunk_tokens": int(chunk),
-                   "parallelism": f"kv-head-shard x{world}", "gather": gather_kind,
+                   "parallelism": f"kv-head-shard x{world}" if args.shard_of == 1 else
+                   f"rank 0's shard of a {args.shard_of}-way head split, alone on one GPU",
+                   "gather": gather_kind,
                    "l2": "inputs larger than L2 (KV bytes per step >> 126 MB); no flush needed"
                          if alg_unique > 4 * 126e6 else "KV fits in L2: number is L2-assisted"},
         "hbm_gbs_step": alg_unique / (ms_step * 1e-3) / 1e9,
@@ -358,11 +367,93 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_engine(args):
+    """BASELINE.json configs[1] at the attention-path level: Qwen3-0.6B shape (16Q/8KV/D128, 28
+    layers, bf16), batch 64, context 2k growing by one token per step, block_size 256 (main.py:19),
+    driven like the reference engine: pool.append -> prepare_decode (host prep + H2D) -> graph replay
+    of 28 x (store, split, combine).  tokens/s = batch / step time (llm_engine.py:58,79-83)."""
+    from minivllm_b200.engine import BlockPool, DecodeRunner, SeqState
+
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    Lyr, H, KVH, D, BS, B, CTX = 28, 16, 8, 128, 256, 64, 2048
+    warm = max(args.warmup, 3)
+    K = args.steps
+    max_len = ((CTX + warm + K + 8 + BS - 1) // BS) * BS
+    nb = B * (max_len // BS)
+    runner = DecodeRunner(Lyr, H, KVH, D, BS, nb, B, max_len, torch.bfloat16, dev, enforce_eager=args.eager)
+    runner.kv_cache.normal_()
+    runner.q.normal_(), runner.k.normal_(), runner.v.normal_()
+    if not args.eager:
+        runner.capture_cudagraph([B])
+    pool = BlockPool(nb, BS, seed=2)
+    seqs = [SeqState() for _ in range(B)]
+    for s in seqs:
+        pool.allocate(s, CTX)
+
+    def step():
+        for s in seqs:
+            pool.append_token(s)
+        runner.prepare_decode(seqs)
+        return runner.run()
+
+    for _ in range(warm):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ctx_start = seqs[0].num_tokens
+    with ClockSampler(0) as clocks:
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(K):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+    ms_step = e0.elapsed_time(e1) / K
+    ctx_mean = (ctx_start + seqs[0].num_tokens) / 2 + 0.5
+    es = 2
+    alg = Lyr * (B * ctx_mean * KVH * D * 2 * es + 2 * B * H * D * es + 4 * B * np.ceil(ctx_mean / BS) + 8 * B
+                 + 4 * B * KVH * D * es + 8 * B)
+    peak, peak_src = measured_peaks()
+    achieved = alg / (ms_step * 1e-3) / 1e9
+    value = B / (ms_step * 1e-3)
+    line = {
+        "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": 1, "steps": K, "warmup": warm,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "c2e: 28-layer engine-shaped decode loop, attention path only "
+                               "(projections/MLP/sampler out of scope)", "shape": "16Q/8KV/D128",
+                   "layers": Lyr, "batch": B, "block_size": BS, "context": [ctx_start, seqs[0].num_tokens],
+                   "cuda_graph": not args.eager,
+                   "l2": "KV bytes per step (15 GB) >> L2; no flush needed"},
+        "roofline": {"bound": "hbm", "kernel": "whole step: CUDA graph of 28 x (store_kvcache, "
+                     "paged_decode_split, paged_decode_combine) + host prep", "achieved": achieved,
+                     "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": alg},
+        "cpu_baseline": None,
+        "e2e": {"value": B / (wall / K), "unit": "tokens/s", "h2d_bytes_per_step": int(runner.h2d_bytes_per_step),
+                "d2h_bytes_per_step": 0, "api": "DecodeRunner.prepare_decode + run (wall clock, "
+                "metadata H2D every step; activations stay on the device as in the reference engine)"},
+        "gpu_launches": K * Lyr * 3, "clocks": clocks.summary(),
+    }
+    print(json.dumps(line), flush=True)
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload == "c2e":
+        if args.impl == "reference":
+            args.workload = "c2"   # the CPU arm times one layer of the same shape
+        elif world == 1:
+            run_engine(args)
+            return
+        else:
+            raise SystemExit("c2e is a single-GPU workload")
     if args.impl == "reference":
         run_reference(args, rank)
         return

@@ -100,18 +100,20 @@ int make_plan(long long batch, int H, int KVH, int D, long long max_num_blocks, 
   if (chunk_req > 0) {
     chunk = ((chunk_req + cta_rows - 1) / cta_rows) * cta_rows;
   } else {
-    // Largest power-of-two multiple of cta_rows (<= kMaxChunk) that still leaves the grid about
-    // 16 full waves of resident CTAs (3 per SM) at the worst-case context length.  Measured on
-    // B200 (scripts/sweep_chunks.sh): large chunks win while the grid stays deep (C3: 1024 ->
-    // 93.9 %, 2048 -> 95-96 %, 4096 -> 94 % of peak); mid-size problems want 256-512-token chunks
-    // (C2: 1024 -> 83.6 %, 512 -> 90.8 %, 256 -> 90.3 %) but not less while 256 still fills a wave.
+    // A CTA pays ~2 us to start (q, table entry, first tile) and the last CTAs to finish leave the
+    // chip partly idle for about half a CTA lifetime; the total is smallest when the lifetime is
+    // sqrt(2 * 2 us * T), T = the kernel's duration at streaming rate for the worst-case context
+    // length.  One SM streams ~44 KB/us (6.5 TB/s / 148) shared by its 3 resident CTAs.
+    // Reproduces the measured optima (scripts/sweep_chunks.sh, scripts/sweep_shard.sh): C3 2048,
+    // C3 sharded 4- and 8-way 1024, C2 512, C4/C5 4096.
     const double units = (double)(batch > 0 ? batch : 1) * KVH * pl->n_gt;
-    const double wave = (double)num_sms * 3.0;
-    auto ctas = [&](long long c) { return units * (double)((max_ctx + c - 1) / c); };
+    const double tok_bytes = 2.0 * D * elem_size(dtype);
+    const double rate_sm = 44000.0;  // bytes per microsecond per SM
+    const double t_est_us = units * (double)max_ctx * tok_bytes / (rate_sm * num_sms);
+    const double life_us = sqrt(4.0 * t_est_us);
+    const double want = life_us * rate_sm / (3.0 * tok_bytes);
     chunk = cta_rows;
-    while (chunk * 2 <= kMaxChunk && ctas(chunk * 2) >= 16.0 * wave) chunk *= 2;
-    const int c256 = ((256 + cta_rows - 1) / cta_rows) * cta_rows;
-    if (chunk < c256 && ctas(c256) >= wave) chunk = c256;
+    while (chunk * 2 <= kMaxChunk && (double)chunk * 1.41421356 < want) chunk *= 2;
   }
   if ((long long)chunk > ((max_ctx + cta_rows - 1) / cta_rows) * cta_rows)
     chunk = (int)(((max_ctx + cta_rows - 1) / cta_rows) * cta_rows);

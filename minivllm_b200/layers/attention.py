@@ -227,7 +227,10 @@ class Attention(nn.Module):
             return self.k_cache.shape[1]
         return self.block_size
 
-    def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
+    def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *,
+                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``out`` (keyword-only, optional): a preallocated (batch, num_heads, head_dim) result
+        buffer, for callers that run under CUDA-graph capture with static buffers."""
         context = get_context()
         k_cache, v_cache = self.k_cache, self.v_cache
         block_size = self._effective_block_size()
@@ -247,7 +250,7 @@ class Attention(nn.Module):
             q = q.squeeze(1)
         o = paged_attention_decode(q, k_cache, v_cache, context.block_tables, context.context_lens,
                                    scale, self.num_heads, self.num_kv_heads, self.head_dim,
-                                   block_size)
+                                   block_size, out=out)
         return o.reshape(o.shape[0], self.num_heads * self.head_dim)
 
 

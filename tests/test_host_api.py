@@ -112,3 +112,20 @@ def test_product_does_not_import_the_oracle():
         for f in files:
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 assert not pat.search(open(os.path.join(dirpath, f)).read()), f"{f} uses the oracle"
+
+
+def test_block_pool_bookkeeping():
+    from minivllm_b200.engine import BlockPool, SeqState
+    pool = BlockPool(8, 16)
+    s = SeqState()
+    pool.allocate(s, 16)
+    assert len(s.block_table) == 1 and len(s) == 16
+    pool.append_token(s)                 # token 17 starts page 2
+    assert len(s.block_table) == 2 and len(s) == 17
+    for _ in range(15):
+        pool.append_token(s)
+    assert len(s.block_table) == 2 and len(s) == 32
+    pool.deallocate(s)
+    assert len(pool.free) == 8 and len(s) == 0
+    with pytest.raises(MemoryError):
+        pool.allocate(s, 16 * 9)
