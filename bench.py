@@ -47,6 +47,8 @@ def parse_args():
                     help="c1..c5: one attention call per step; c2e: 28-layer engine-shaped decode "
                          "loop of config 2 under CUDA-graph replay")
     ap.add_argument("--eager", action="store_true", help="c2e: no CUDA graphs")
+    ap.add_argument("--unfused", action="store_true",
+                    help="three launches per step (store, split, combine) instead of the fused one")
     ap.add_argument("--shard-of", type=int, default=1,
                     help="tuning aid: run rank 0's KV-head shard of an N-way split on ONE GPU, no gather")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
@@ -195,7 +197,8 @@ def run_ours(args, rank, world, local_rank):
 
     from minivllm_b200 import _ext
     from minivllm_b200.head_shard import gather_heads, shard_plan
-    from minivllm_b200.layers.attention import HostDecodeStep, paged_attention_decode, store_kvcache
+    from minivllm_b200.layers.attention import (HostDecodeStep, decode_step, paged_attention_decode,
+                                                store_kvcache)
 
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
@@ -232,27 +235,43 @@ def run_ours(args, rank, world, local_rank):
                                                              t.tables.shape[1], w["BS"], code)
     multi_split = t.tables.shape[1] * sp.BS > chunk
 
+    fargs = (w["q"], w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"], w["BS"])
+    new_kv = (w["k"], w["v"], w["slot_mapping"])
+
     def step(ev=None):
-        store_kvcache(w["k"], w["v"], w["k_cache"], w["v_cache"], w["slot_mapping"], w["BS"])
-        if ev is not None:
-            ev[0].record()
-        if fused is not None:
-            fargs = (w["q"], w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"],
-                     w["scale"], w["BS"])
-            fused(*fargs, chunk_tokens=args.chunk, flags=_ext.DECODE_SKIP_COMBINE, barrier=False)
+        """One decode step of a layer.  Default: ONE launch (store + split + combine fused,
+        mvl_decode_step).  --unfused: the three separate launches, for profiling comparisons."""
+        if args.unfused:
+            store_kvcache(w["k"], w["v"], w["k_cache"], w["v_cache"], w["slot_mapping"], w["BS"])
+            if ev is not None:
+                ev[0].record()
+            if fused is not None:
+                fused(*fargs, chunk_tokens=args.chunk, flags=_ext.DECODE_SKIP_COMBINE, barrier=False)
+            else:
+                paged_attention_decode(w["q"], *dec_args, out=out, chunk_tokens=args.chunk,
+                                       flags=_ext.DECODE_SKIP_COMBINE)
             if ev is not None:
                 ev[1].record()
             if multi_split:
-                fused(*fargs, chunk_tokens=args.chunk, flags=_ext.DECODE_ONLY_COMBINE, barrier=False)
+                if fused is not None:
+                    fused(*fargs, chunk_tokens=args.chunk, flags=_ext.DECODE_ONLY_COMBINE, barrier=False)
+                else:
+                    paged_attention_decode(w["q"], *dec_args, out=out, chunk_tokens=args.chunk,
+                                           flags=_ext.DECODE_ONLY_COMBINE)
+        else:
+            if ev is not None:
+                ev[0].record()
+            if fused is not None:
+                fused(*fargs, chunk_tokens=args.chunk, barrier=False, store=new_kv)
+            else:
+                decode_step(w["q"], w["k"], w["v"], w["k_cache"], w["v_cache"], w["slot_mapping"],
+                            w["block_tables"], w["context_lens"], w["scale"], w["H"], w["KVH"], w["D"],
+                            w["BS"], out=out, chunk_tokens=args.chunk)
+            if ev is not None:
+                ev[1].record()
+        if fused is not None:
             fused.barrier()
             return fused.out
-        paged_attention_decode(w["q"], *dec_args, out=out, chunk_tokens=args.chunk,
-                               flags=_ext.DECODE_SKIP_COMBINE)
-        if ev is not None:
-            ev[1].record()
-        if multi_split:
-            paged_attention_decode(w["q"], *dec_args, out=out, chunk_tokens=args.chunk,
-                                   flags=_ext.DECODE_ONLY_COMBINE)
         if world > 1:
             return gather_heads(out, staging=staging)
         return out
@@ -323,7 +342,8 @@ def run_ours(args, rank, world, local_rank):
     alg = workloads.algorithmic_bytes(t, kvh_local=w["KVH"], h_local=w["H"])
     alg_unique = workloads.algorithmic_bytes(t, kvh_local=w["KVH"], h_local=w["H"], unique=True)
     achieved = alg_unique / (kern_ms * 1e-3) / 1e9
-    roof = {"bound": "hbm", "kernel": "paged_decode_split_kernel", "achieved": achieved, "peak": peak,
+    roof = {"bound": "hbm", "kernel": "paged_decode_split_kernel" + (
+                "" if args.unfused else " (store and combine fused in)"), "achieved": achieved, "peak": peak,
             "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": alg_unique, "logical_bytes_per_launch": alg,
             "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / ms_step,
@@ -359,7 +379,7 @@ def run_ours(args, rank, world, local_rank):
                          if alg_unique > 4 * 126e6 else "KV fits in L2: number is L2-assisted"},
         "hbm_gbs_step": alg_unique / (ms_step * 1e-3) / 1e9,
         "roofline": roof, "cpu_baseline": cpu, "e2e": e2e,
-        "gpu_launches": K * (3 if multi_split else 2),
+        "gpu_launches": K * ((3 if multi_split else 2) if args.unfused else 1),
         "clocks": clocks.summary(),
     }
     print(json.dumps(line), flush=True)

@@ -51,6 +51,11 @@ typedef enum mvl_dtype {
 /* Flags for mvl_paged_decode (bit mask). */
 #define MVL_DECODE_SKIP_COMBINE 1u /* profiling only: launch the split kernel, not the combine */
 #define MVL_DECODE_ONLY_COMBINE 2u /* profiling only: launch the combine kernel alone */
+#define MVL_DECODE_FUSED_COMBINE 4u /* merge the chunks inside the split kernel (last CTA to arrive
+                                       per sequence and head tile does it): no combine launch.
+                                       Needs the first 256 KiB of the workspace to be zero on first
+                                       use; every call leaves them zero.  Ignored (separate combine
+                                       kernel) when batch * kv-head tiles > 65536. */
 
 /* Library / ABI identification.  No reference counterpart (the reference has no native layer). */
 int mvl_abi_version(void);
@@ -142,6 +147,37 @@ int mvl_paged_decode_peers(void* const* out_peers, int num_peers, int total_head
                            size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream);
 
 /*
+ * mvl_decode_step — store + decode of one decode step in ONE kernel launch (plus the combine unless
+ * MVL_DECODE_FUSED_COMBINE): what reference Attention.forward does with two Triton launches
+ * (attention.py:498-510 store_kvcache, then :544-555 paged_attention_decode).  key/value are the
+ * step's new rows, (batch, num_kv_heads, head_dim) with token strides in elements; slot_mapping[b]
+ * must be the slot of token context_lens[b]-1 of sequence b (what reference
+ * model_runner.py:238-239 produces) or -1.  The CTA that streams the chunk holding that token
+ * writes the row first, so no separate store kernel runs; rows with context_lens[b] <= 0 store
+ * nothing.  slot_mapping and context_lens share one index dtype.  Other arguments as
+ * mvl_paged_decode.
+ */
+int mvl_decode_step(void* out, const void* query, const void* key, const void* value, void* k_cache,
+                    void* v_cache, const void* slot_mapping, const int32_t* block_tables,
+                    const void* context_lens, int idx_is_i64, int64_t batch, int64_t max_num_blocks,
+                    int64_t block_table_stride, int64_t key_token_stride, int64_t value_token_stride,
+                    int num_heads, int num_kv_heads, int head_dim, int block_size,
+                    int64_t num_blocks, float scale, int elem_dtype, void* workspace,
+                    size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream);
+
+/* mvl_decode_step with the result stores of mvl_paged_decode_peers (head-sharded step whose stores
+ * perform the all-gather).  No reference counterpart. */
+int mvl_decode_step_peers(void* const* out_peers, int num_peers, int total_heads, int head_offset,
+                          const void* query, const void* key, const void* value, void* k_cache,
+                          void* v_cache, const void* slot_mapping, const int32_t* block_tables,
+                          const void* context_lens, int idx_is_i64, int64_t batch,
+                          int64_t max_num_blocks, int64_t block_table_stride,
+                          int64_t key_token_stride, int64_t value_token_stride, int num_heads,
+                          int num_kv_heads, int head_dim, int block_size, int64_t num_blocks,
+                          float scale, int elem_dtype, void* workspace, size_t workspace_bytes,
+                          int chunk_tokens, unsigned flags, void* stream);
+
+/*
  * mvl_decode_step_host — one decode-attention step of a layer driven from HOST buffers:
  * async H2D of the step's inputs (pinned host memory recommended) into caller-provided device
  * staging buffers, mvl_store_kvcache, mvl_paged_decode, async D2H of the result.  The caller
@@ -149,6 +185,8 @@ int mvl_paged_decode_peers(void* const* out_peers, int num_peers, int total_head
  * model_runner.py:231-256 (prepare_decode's H2D copies) + attention.py:493-557
  * (Attention.forward decode branch) do per layer.  slot_mapping/context_lens are int64 when
  * idx_is_i64 != 0 else int32.  Staging buffers must hold at least the host arrays' bytes.
+ * Runs mvl_decode_step with MVL_DECODE_FUSED_COMBINE: the first 256 KiB of the workspace must be
+ * zero before the first call.
  */
 int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_host,
                          const void* slot_mapping_host, const void* context_lens_host,

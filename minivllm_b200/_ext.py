@@ -17,7 +17,7 @@ ABI_VERSION = 1
 # mvl_dtype
 F32, F16, BF16 = 0, 1, 2
 # flags of mvl_paged_decode
-DECODE_SKIP_COMBINE, DECODE_ONLY_COMBINE = 1, 2
+DECODE_SKIP_COMBINE, DECODE_ONLY_COMBINE, DECODE_FUSED_COMBINE = 1, 2, 4
 
 _vp, _i, _i64, _sz, _f, _u = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float, C.c_uint
 
@@ -33,6 +33,10 @@ PROTOTYPES = {
                               _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
     "mvl_paged_decode_peers": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _i64, _i64, _i64, _i,
                                     _i, _i, _i, _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
+    "mvl_decode_step": (_i, [_vp] * 9 + [_i, _i64, _i64, _i64, _i64, _i64, _i, _i, _i, _i, _i64, _f, _i,
+                              _vp, _sz, _i, _u, _vp]),
+    "mvl_decode_step_peers": (_i, [_vp, _i, _i, _i] + [_vp] * 8 + [_i, _i64, _i64, _i64, _i64, _i64, _i,
+                                   _i, _i, _i, _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
     "mvl_decode_step_host": (_i, [_vp] * 16 + [_i, _i64, _i64, _i, _i, _i, _i, _i64, _f, _i, _vp,
                                                _sz, _i, _vp]),
     "mvl_paged_decode_static": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i64, _i64, _i64, _i, _i, _i,

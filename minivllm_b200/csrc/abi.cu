@@ -124,11 +124,24 @@ int make_plan(long long batch, int H, int KVH, int D, long long max_num_blocks, 
   return MVL_OK;
 }
 
+// Workspace layout: [arrival counters, fixed kCounterBytes][part_o fp32][part_ml float2].
+// The counter region has a fixed size and position so that it never overlaps another call's
+// partials, whatever the shapes: it only ever holds counters, which every call leaves at zero.
+constexpr size_t kCounterBytes = 256u << 10;  // 65536 counters
+
 size_t plan_workspace(const Plan& pl, long long batch, int H, int D) {
   if (pl.max_splits <= 1) return 0;
   const size_t rows = (size_t)batch * H * pl.max_splits;
-  return rows * D * sizeof(float) + rows * sizeof(float2);
+  return kCounterBytes + rows * D * sizeof(float) + rows * sizeof(float2);
 }
+
+struct StoreArgs {  // the step's new K/V rows for the fused store (mvl_decode_step)
+  const void* key;
+  const void* value;
+  const void* slot_mapping;
+  int slot_is_i64;
+  long long key_token_stride, value_token_stride;  // elements
+};
 
 }  // namespace
 
@@ -206,7 +219,8 @@ size_t mvl_paged_decode_workspace_bytes(int64_t batch, int num_heads, int num_kv
   return plan_workspace(pl, batch, num_heads, head_dim);
 }
 
-static int decode_impl(void* const* outs, int n_out, int h_out, int head_off, const void* query,
+static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, int h_out, int head_off,
+                       const void* query,
                        const void* k_cache, const void* v_cache,
                      const int32_t* block_tables, const void* context_lens, int ctx_is_i64,
                      int64_t batch, int64_t max_num_blocks, int64_t block_table_stride,
@@ -250,10 +264,31 @@ static int decode_impl(void* const* outs, int n_out, int h_out, int head_off, co
   p.bt = block_tables;
   p.ctx = context_lens;
   const size_t rows = (size_t)batch * num_heads * pl.max_splits;
-  p.part_o = reinterpret_cast<float*>(workspace);
-  p.part_ml = need ? reinterpret_cast<float2*>(reinterpret_cast<char*>(workspace) +
-                                               rows * head_dim * sizeof(float))
-                   : nullptr;
+  if (need) {
+    char* base = reinterpret_cast<char*>(workspace);
+    p.part_o = reinterpret_cast<float*>(base + kCounterBytes);
+    p.part_ml = reinterpret_cast<float2*>(base + kCounterBytes + rows * head_dim * sizeof(float));
+    const size_t n_counters = (size_t)batch * num_kv_heads * pl.n_gt;
+    if ((flags & MVL_DECODE_FUSED_COMBINE) && n_counters * sizeof(int) <= kCounterBytes &&
+        !(flags & (MVL_DECODE_SKIP_COMBINE | MVL_DECODE_ONLY_COMBINE)))
+      p.counters = reinterpret_cast<int*>(base);
+  }
+  if (st_args) {
+    const int es = elem_size(elem_dtype);
+    if (!st_args->key || !st_args->value || !st_args->slot_mapping) return MVL_ERR_NULL_POINTER;
+    const long long dense = (long long)num_kv_heads * head_dim;
+    if (st_args->key_token_stride < dense || st_args->value_token_stride < dense) return MVL_ERR_SHAPE;
+    if ((st_args->key_token_stride * es) % 16 || (st_args->value_token_stride * es) % 16 ||
+        !aligned16(st_args->key) || !aligned16(st_args->value))
+      return MVL_ERR_ALIGNMENT;
+    p.k_new = st_args->key;
+    p.v_new = st_args->value;
+    p.slot_map = st_args->slot_mapping;
+    p.slot_is_i64 = st_args->slot_is_i64 ? 1 : 0;
+    p.k_new_stride = st_args->key_token_stride * es;
+    p.v_new_stride = st_args->value_token_stride * es;
+    p.num_slots = num_blocks * (long long)block_size;
+  }
   p.bt_stride = block_table_stride;
   p.max_ctx = pl.max_ctx;
   p.ctx_is_i64 = ctx_is_i64 ? 1 : 0;
@@ -280,7 +315,7 @@ static int decode_impl(void* const* outs, int n_out, int h_out, int head_off, co
     if (e == -1000) return MVL_ERR_SHAPE;
     if (e != 0) return cuda_fail((cudaError_t)e, "paged_decode_split launch");
   }
-  if (pl.max_splits > 1 && !(flags & MVL_DECODE_SKIP_COMBINE)) {
+  if (pl.max_splits > 1 && !(flags & MVL_DECODE_SKIP_COMBINE) && p.counters == nullptr) {
     const long long bh = (long long)batch * num_heads;
     int e = -1000;
     switch (elem_dtype) {
@@ -301,7 +336,7 @@ int mvl_paged_decode(void* out, const void* query, const void* k_cache, const vo
                      int64_t num_blocks, float scale, int elem_dtype, void* workspace,
                      size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream) {
   void* outs[1] = {out};
-  return decode_impl(outs, 1, num_heads, 0, query, k_cache, v_cache, block_tables, context_lens,
+  return decode_impl(nullptr, outs, 1, num_heads, 0, query, k_cache, v_cache, block_tables, context_lens,
                      ctx_is_i64, batch, max_num_blocks, block_table_stride, num_heads, num_kv_heads,
                      head_dim, block_size, num_blocks, scale, elem_dtype, workspace, workspace_bytes,
                      chunk_tokens, flags, stream);
@@ -314,8 +349,39 @@ int mvl_paged_decode_peers(void* const* out_peers, int num_peers, int total_head
                            int num_heads, int num_kv_heads, int head_dim, int block_size,
                            int64_t num_blocks, float scale, int elem_dtype, void* workspace,
                            size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream) {
-  return decode_impl(out_peers, num_peers, total_heads, head_offset, query, k_cache, v_cache,
+  return decode_impl(nullptr, out_peers, num_peers, total_heads, head_offset, query, k_cache, v_cache,
                      block_tables, context_lens, ctx_is_i64, batch, max_num_blocks,
+                     block_table_stride, num_heads, num_kv_heads, head_dim, block_size, num_blocks,
+                     scale, elem_dtype, workspace, workspace_bytes, chunk_tokens, flags, stream);
+}
+
+int mvl_decode_step(void* out, const void* query, const void* key, const void* value, void* k_cache,
+                    void* v_cache, const void* slot_mapping, const int32_t* block_tables,
+                    const void* context_lens, int idx_is_i64, int64_t batch, int64_t max_num_blocks,
+                    int64_t block_table_stride, int64_t key_token_stride, int64_t value_token_stride,
+                    int num_heads, int num_kv_heads, int head_dim, int block_size,
+                    int64_t num_blocks, float scale, int elem_dtype, void* workspace,
+                    size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream) {
+  StoreArgs st{key, value, slot_mapping, idx_is_i64, key_token_stride, value_token_stride};
+  void* outs[1] = {out};
+  return decode_impl(&st, outs, 1, num_heads, 0, query, k_cache, v_cache, block_tables, context_lens,
+                     idx_is_i64, batch, max_num_blocks, block_table_stride, num_heads, num_kv_heads,
+                     head_dim, block_size, num_blocks, scale, elem_dtype, workspace, workspace_bytes,
+                     chunk_tokens, flags, stream);
+}
+
+int mvl_decode_step_peers(void* const* out_peers, int num_peers, int total_heads, int head_offset,
+                          const void* query, const void* key, const void* value, void* k_cache,
+                          void* v_cache, const void* slot_mapping, const int32_t* block_tables,
+                          const void* context_lens, int idx_is_i64, int64_t batch,
+                          int64_t max_num_blocks, int64_t block_table_stride,
+                          int64_t key_token_stride, int64_t value_token_stride, int num_heads,
+                          int num_kv_heads, int head_dim, int block_size, int64_t num_blocks,
+                          float scale, int elem_dtype, void* workspace, size_t workspace_bytes,
+                          int chunk_tokens, unsigned flags, void* stream) {
+  StoreArgs st{key, value, slot_mapping, idx_is_i64, key_token_stride, value_token_stride};
+  return decode_impl(&st, out_peers, num_peers, total_heads, head_offset, query, k_cache, v_cache,
+                     block_tables, context_lens, idx_is_i64, batch, max_num_blocks,
                      block_table_stride, num_heads, num_kv_heads, head_dim, block_size, num_blocks,
                      scale, elem_dtype, workspace, workspace_bytes, chunk_tokens, flags, stream);
 }
@@ -354,15 +420,12 @@ int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_h
   MVL_H2D(context_lens_dev, context_lens_host, ib);
   MVL_H2D(block_tables_dev, block_tables_host, tb);
 #undef MVL_H2D
-  int st = mvl_store_kvcache(k_dev, v_dev, k_cache, v_cache, slot_mapping_dev, idx_is_i64, batch,
-                             num_kv_heads, head_dim, (int64_t)num_kv_heads * head_dim,
-                             (int64_t)num_kv_heads * head_dim, num_blocks * block_size, elem_dtype,
-                             stream);
-  if (st != MVL_OK) return st;
-  st = mvl_paged_decode(out_dev, q_dev, k_cache, v_cache, block_tables_dev, context_lens_dev,
-                        idx_is_i64, batch, max_num_blocks, max_num_blocks, num_heads, num_kv_heads,
-                        head_dim, block_size, num_blocks, scale, elem_dtype, workspace,
-                        workspace_bytes, chunk_tokens, 0u, stream);
+  const int st = mvl_decode_step(out_dev, q_dev, k_dev, v_dev, k_cache, v_cache, slot_mapping_dev,
+                                 block_tables_dev, context_lens_dev, idx_is_i64, batch, max_num_blocks,
+                                 max_num_blocks, (int64_t)num_kv_heads * head_dim,
+                                 (int64_t)num_kv_heads * head_dim, num_heads, num_kv_heads, head_dim,
+                                 block_size, num_blocks, scale, elem_dtype, workspace, workspace_bytes,
+                                 chunk_tokens, MVL_DECODE_FUSED_COMBINE, stream);
   if (st != MVL_OK) return st;
   e = cudaMemcpyAsync(out_host, out_dev, qb, cudaMemcpyDeviceToHost, s);
   if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync D2H out");

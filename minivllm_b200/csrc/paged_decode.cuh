@@ -36,6 +36,16 @@ struct DecodeParams {
   // all-gathered by the stores themselves (NVLink P2P) instead of by a separate collective.
   void* outs[8];
   int n_out, H_out, head_off;
+  // Optional fusion of the step's KV-cache write (store_kvcache of the sequence's newest token):
+  // the CTA whose chunk holds token ctx-1 writes that row for its kv head before it streams it.
+  const void* k_new;        // (batch, KVH, D), token strides in bytes; nullptr = no fused store
+  const void* v_new;
+  const void* slot_map;     // (batch,) int32/int64, slot of token ctx-1 (or -1)
+  long long k_new_stride, v_new_stride, num_slots;
+  int slot_is_i64;
+  // Optional fusion of the combine: per (sequence, head tile) arrival counters (zero before the
+  // call, left zero after it); the last chunk's CTA to arrive merges the partials itself.
+  int* counters;            // nullptr = separate combine kernel
   const void* q;
   const void* kc;
   const void* vc;
@@ -88,7 +98,7 @@ struct DecodeCfg {
   static constexpr int NQ = NV / 4;             // ... in 16-byte quads
   static constexpr int VPL = (NV / LPR) > 0 ? (NV / LPR) : 1;  // complete scores per lane
   static constexpr int XB_BYTES = 32 * NV * 4;  // transpose buffer
-  static constexpr int PB_BYTES = TR * GT * 8;  // (p,p) pairs
+  static constexpr int PB_BYTES = ((TR * GT * 8 + 255) / 256) * 256;  // (p,p) pairs, 256-B granular
   static constexpr int RING = 3;                // ring slots; RING-1 half tiles in flight
   static constexpr int WARP_SMEM = RING * TILEB + XB_BYTES + PB_BYTES;
   static constexpr int SMEM = NW * WARP_SMEM;
@@ -97,6 +107,9 @@ struct DecodeCfg {
   static_assert(MRG_BYTES <= RING * TILEB, "merge area must fit in the ring");
   static_assert(NV % 4 == 0 && NQ >= 2, "NV must be a multiple of 8");
   static_assert(VPL == 1 || VPL == 2 || VPL == 4 || VPL == 8, "unsupported scores-per-lane");
+  // the XOR swizzle of the transpose buffer needs rows aligned to their size (<= 256 B): every
+  // region size is a multiple of 256 and the kernel uses no static shared memory
+  static_assert((RING * TILEB) % 256 == 0 && XB_BYTES % 256 == 0 && WARP_SMEM % 256 == 0, "alignment");
 };
 
 // XOR swizzle of the transpose buffer: lane L stores quad k at quad (k ^ key(L)).
@@ -116,7 +129,7 @@ paged_decode_split_kernel(const DecodeParams p) {
   constexpr int NP = C::NP, R = C::R, RPP = C::RPP, LPR = C::LPR, TR = C::TR, NV = C::NV,
                 NQ = C::NQ, VPL = C::VPL, NW = C::NW, ROWB = C::ROWB, TILEB = C::TILEB,
                 RING = C::RING;
-  extern __shared__ __align__(128) unsigned char smem[];
+  extern __shared__ __align__(1024) unsigned char smem[];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int h = lane / LPR, c = lane % LPR;
@@ -145,6 +158,24 @@ paged_decode_split_kernel(const DecodeParams p) {
   if (start >= ctx) return;
   const int end = min(ctx, start + p.chunk);
   const int n_act = (ctx + p.chunk - 1) / p.chunk;
+
+  if (p.k_new != nullptr && ctx - 1 >= start && ctx - 1 < end) {  // CTA-uniform
+    const long long slot = p.slot_is_i64 ? reinterpret_cast<const long long*>(p.slot_map)[b]
+                                         : (long long)reinterpret_cast<const int*>(p.slot_map)[b];
+    if (slot >= 0 && slot < p.num_slots) {
+      constexpr int CPR = C::ROWB / 16;  // 16-byte chunks per row of one kv head
+      if (threadIdx.x < 2 * CPR) {
+        const int isv = threadIdx.x / CPR, ch = threadIdx.x % CPR;
+        const char* src = reinterpret_cast<const char*>(isv ? p.v_new : p.k_new) +
+                          b * (isv ? p.v_new_stride : p.k_new_stride) + (long long)kvh * C::ROWB + ch * 16;
+        char* dst = reinterpret_cast<char*>(const_cast<void*>(isv ? p.vc : p.kc)) +
+                    (slot * p.KVH + kvh) * C::ROWB + ch * 16;
+        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+      }
+      __threadfence();  // the row is read back below through cp.async (L2)
+    }
+    __syncthreads();
+  }
 
   const uint32_t wbase = smem_u32(smem) + warp * C::WARP_SMEM;
   const uint32_t ring = wbase;
@@ -499,6 +530,47 @@ paged_decode_split_kernel(const DecodeParams p) {
       *reinterpret_cast<float4*>(p.part_o + pi * D + dq * 4) = make_float4(a0, a1, a2, a3);
       if (dq == 0) p.part_ml[pi] = make_float2(M, Lsum);
     }
+  }
+  if (n_act == 1 || p.counters == nullptr) return;
+
+  // ---- fused combine: the last of this (sequence, head tile)'s n_act CTAs to arrive merges them.
+  // The flag lives in dynamic shared memory (warp 0's probability buffer, idle by now): a static
+  // __shared__ variable would shift the dynamic base and break the transpose buffer's alignment.
+  const uint32_t flag = sbase + C::RING * TILEB + C::XB_BYTES;
+  __syncthreads();  // every thread's partial stores are issued
+  if (threadIdx.x == 0) {
+    __threadfence();  // release: the CTA's partials (ordered by the barrier) before the count
+    int* cnt = p.counters + (long long)b * gridDim.x + blockIdx.x;
+    const int prev = atomicAdd(cnt, 1);
+    const int last = (prev == n_act - 1);
+    if (last) {
+      *cnt = 0;         // leave the counter ready for the next call
+      __threadfence();  // acquire: the other CTAs' partials after the count
+    }
+    sts32(flag, (uint32_t)last);
+  }
+  __syncthreads();
+  const bool s_last = lds32(flag) != 0;
+  if (!s_last) return;
+  for (int item = threadIdx.x; item < GT * (D / 4); item += NW * 32) {
+    const int g = item / (D / 4), dq = item % (D / 4);
+    if (g >= g_valid) continue;
+    const long long pi0 = ((long long)b * p.H + head0 + g) * p.max_splits;
+    float M = -INFINITY, Lsum = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    for (int s = 0; s < n_act; ++s) {
+      const float2 ml = __ldcg(p.part_ml + pi0 + s);
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(p.part_o + (pi0 + s) * D + dq * 4));
+      const float Mn = fmaxf(M, ml.x);
+      const float so = fast_exp2(M - Mn), sn = fast_exp2(ml.x - Mn);  // first: exp2(-inf) = 0
+      Lsum = Lsum * so + ml.y * sn;
+      a0 = a0 * so + v.x * sn;
+      a1 = a1 * so + v.y * sn;
+      a2 = a2 * so + v.z * sn;
+      a3 = a3 * so + v.w * sn;
+      M = Mn;
+    }
+    const float inv = 1.f / Lsum;
+    store_out4<T, D>(p, b, head0 + g, dq * 4, a0 * inv, a1 * inv, a2 * inv, a3 * inv);
   }
 }
 

@@ -97,15 +97,19 @@ class PeerGatheredDecode:
         self.device = device
 
     def __call__(self, query, k_cache, v_cache, block_tables, context_lens, scale, block_size,
-                 chunk_tokens: int = 0, flags: int = 0, barrier: bool = True) -> torch.Tensor:
+                 chunk_tokens: int = 0, flags: Optional[int] = None, barrier: bool = True,
+                 store=None) -> torch.Tensor:
         """Decode this rank's heads into every rank's buffer; returns this rank's full
-        (batch, total_heads, head_dim) buffer (complete after the barrier)."""
+        (batch, total_heads, head_dim) buffer (complete after the barrier).  ``store=(key, value,
+        slot_mapping)`` fuses the step's KV-cache write into the same launch (mvl_decode_step_peers)."""
         import ctypes
 
         from . import _ext
         from .layers import attention as att
 
         sh = self.shard
+        if flags is None:
+            flags = _ext.DECODE_FUSED_COMBINE
         batch, max_blocks = query.shape[0], block_tables.shape[1]
         code = att._dtype_code(query)
         lib = _ext.lib()
@@ -114,15 +118,25 @@ class PeerGatheredDecode:
                                                           self.head_dim, max_blocks, block_size, code,
                                                           chunk_tokens)
             ws = att.workspace_for(self.device, nbytes)
-            _ext.check(lib.mvl_paged_decode_peers(
-                ctypes.cast(self._ptr_array, ctypes.c_void_p), sh.world_size, self.total_heads,
-                sh.q_heads.start, query.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
-                block_tables.data_ptr(), context_lens.data_ptr(),
-                att._index_flag("context_lens", context_lens), batch, max_blocks, block_tables.stride(0),
-                sh.num_heads, sh.num_kv_heads, self.head_dim, block_size, k_cache.shape[0],
-                float(scale), code, ws.data_ptr() if ws is not None else None,
-                ws.numel() if ws is not None else 0, chunk_tokens, flags,
-                att._stream_ptr(self.device)))
+            peers = ctypes.cast(self._ptr_array, ctypes.c_void_p)
+            wsp, wsn = (ws.data_ptr(), ws.numel()) if ws is not None else (None, 0)
+            idx = att._index_flag("context_lens", context_lens)
+            if store is None:
+                _ext.check(lib.mvl_paged_decode_peers(
+                    peers, sh.world_size, self.total_heads, sh.q_heads.start, query.data_ptr(),
+                    k_cache.data_ptr(), v_cache.data_ptr(), block_tables.data_ptr(),
+                    context_lens.data_ptr(), idx, batch, max_blocks, block_tables.stride(0),
+                    sh.num_heads, sh.num_kv_heads, self.head_dim, block_size, k_cache.shape[0],
+                    float(scale), code, wsp, wsn, chunk_tokens, flags, att._stream_ptr(self.device)))
+            else:
+                key, value, slots = store
+                _ext.check(lib.mvl_decode_step_peers(
+                    peers, sh.world_size, self.total_heads, sh.q_heads.start, query.data_ptr(),
+                    key.data_ptr(), value.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+                    slots.data_ptr(), block_tables.data_ptr(), context_lens.data_ptr(), idx, batch,
+                    max_blocks, block_tables.stride(0), key.stride(0), value.stride(0), sh.num_heads,
+                    sh.num_kv_heads, self.head_dim, block_size, k_cache.shape[0], float(scale), code,
+                    wsp, wsn, chunk_tokens, flags, att._stream_ptr(self.device)))
             if barrier:
                 self.barrier()
         return self.out

@@ -90,7 +90,9 @@ def workspace_for(dev: torch.device, nbytes: int) -> Optional[torch.Tensor]:
     key = (dev.index, _stream_ptr(dev))
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
-        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=dev)
+        # zero-filled: its first 256 KiB are the arrival counters of the fused combine, which every
+        # call leaves at zero (include/mvl_abi.h, MVL_DECODE_FUSED_COMBINE)
+        ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=dev)
         _workspaces[key] = ws
     return ws
 
@@ -141,16 +143,18 @@ def paged_attention_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: 
                            block_tables: torch.Tensor, context_lens: torch.Tensor, scale: float,
                            num_heads: int, num_kv_heads: int, head_dim: int, block_size: int,
                            *, out: Optional[torch.Tensor] = None, chunk_tokens: int = 0,
-                           flags: int = 0) -> torch.Tensor:
+                           flags: Optional[int] = None, _store=None) -> torch.Tensor:
     """Decode attention of one query per sequence over the paged KV cache.
 
     query: (batch, num_heads, head_dim); caches as in ``store_kvcache``; block_tables:
     (batch, max_num_blocks) int32, padded with -1; context_lens: (batch,) int32/int64.
     Returns a new (batch, num_heads, head_dim) tensor in query's dtype (reference
     attention.py:418-473).  ``out``, ``chunk_tokens`` and ``flags`` are keyword-only additions
-    (preallocated output, split size override, profiling flags); defaults reproduce the
-    reference call.
+    (preallocated output, split size override, ABI flags); defaults reproduce the reference call
+    and merge the chunks inside the split kernel (MVL_DECODE_FUSED_COMBINE).
     """
+    if flags is None:
+        flags = _ext.DECODE_FUSED_COMBINE
     dev = _need_cuda(query=query, k_cache=k_cache, v_cache=v_cache, block_tables=block_tables,
                      context_lens=context_lens)
     if query.dim() != 3 or query.shape[1] != num_heads or query.shape[2] != head_dim:
@@ -191,14 +195,55 @@ def paged_attention_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: 
             nbytes = _plan_cache[key] = handle.mvl_paged_decode_workspace_bytes(
                 batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, code, chunk_tokens)
         ws = workspace_for(dev, nbytes)
-        _ext.check(handle.mvl_paged_decode(
-            out.data_ptr(), query.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
-            block_tables.data_ptr(), context_lens.data_ptr(), _index_flag("context_lens", context_lens),
-            batch, max_num_blocks, block_tables.stride(0), num_heads, num_kv_heads, head_dim,
-            block_size, k_cache.shape[0], float(scale), code,
-            ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0,
-            chunk_tokens, flags, _stream_ptr(dev)))
+        wsp, wsn = (ws.data_ptr(), ws.numel()) if ws is not None else (None, 0)
+        if _store is None:
+            _ext.check(handle.mvl_paged_decode(
+                out.data_ptr(), query.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+                block_tables.data_ptr(), context_lens.data_ptr(),
+                _index_flag("context_lens", context_lens), batch, max_num_blocks,
+                block_tables.stride(0), num_heads, num_kv_heads, head_dim, block_size,
+                k_cache.shape[0], float(scale), code, wsp, wsn, chunk_tokens, flags, _stream_ptr(dev)))
+        else:
+            key, value, slots = _store
+            _ext.check(handle.mvl_decode_step(
+                out.data_ptr(), query.data_ptr(), key.data_ptr(), value.data_ptr(), k_cache.data_ptr(),
+                v_cache.data_ptr(), slots.data_ptr(), block_tables.data_ptr(), context_lens.data_ptr(),
+                _index_flag("context_lens", context_lens), batch, max_num_blocks,
+                block_tables.stride(0), key.stride(0), value.stride(0), num_heads, num_kv_heads,
+                head_dim, block_size, k_cache.shape[0], float(scale), code, wsp, wsn, chunk_tokens,
+                flags, _stream_ptr(dev)))
     return out
+
+
+def decode_step(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor,
+                v_cache: torch.Tensor, slot_mapping: torch.Tensor, block_tables: torch.Tensor,
+                context_lens: torch.Tensor, scale: float, num_heads: int, num_kv_heads: int,
+                head_dim: int, block_size: int, *, out: Optional[torch.Tensor] = None,
+                chunk_tokens: int = 0) -> torch.Tensor:
+    """``store_kvcache`` then ``paged_attention_decode`` of one decode step in ONE kernel launch
+    (``mvl_decode_step``).  ``key``/``value`` are the step's new rows (batch, num_kv_heads,
+    head_dim); ``slot_mapping[b]`` is the slot of token ``context_lens[b] - 1`` (or -1), as the
+    reference's ``prepare_decode`` produces (model_runner.py:238-239).  Same result and same cache
+    contents as the two separate calls."""
+    _need_cuda(key=key, value=value, slot_mapping=slot_mapping)
+    batch = query.shape[0]
+    if key.shape != (batch, num_kv_heads, head_dim) or value.shape != key.shape:
+        raise ValueError("key/value must be (batch, num_kv_heads, head_dim) for a decode step")
+    if key.dtype != k_cache.dtype or value.dtype != k_cache.dtype:
+        raise ValueError("key, value and the caches must share one dtype")
+    if slot_mapping.numel() != batch or slot_mapping.dtype != context_lens.dtype:
+        raise ValueError("slot_mapping must be (batch,) with context_lens' integer dtype")
+
+    def rows(x: torch.Tensor) -> torch.Tensor:
+        dense = x.stride(2) == 1 and x.stride(1) == head_dim and (
+            batch <= 1 or x.stride(0) >= num_kv_heads * head_dim)
+        x = x if dense else x.contiguous()
+        return x if batch > 1 else x.reshape(1, num_kv_heads, head_dim).contiguous()
+
+    return paged_attention_decode(query, k_cache, v_cache, block_tables, context_lens, scale, num_heads,
+                                  num_kv_heads, head_dim, block_size, out=out,
+                                  chunk_tokens=chunk_tokens,
+                                  _store=(rows(key), rows(value), slot_mapping.contiguous()))
 
 
 class Attention(nn.Module):
@@ -235,22 +280,32 @@ class Attention(nn.Module):
         k_cache, v_cache = self.k_cache, self.v_cache
         block_size = self._effective_block_size()
 
-        if k_cache.numel() > 0 and v_cache.numel() > 0 and context.slot_mapping is not None:
-            if k.dim() == 4:  # (B, N, KVH, D) -> (B*N, KVH, D)
-                k = k.reshape(-1, k.shape[-2], k.shape[-1])
-                v = v.reshape(-1, v.shape[-2], v.shape[-1])
-            store_kvcache(k, v, k_cache, v_cache, context.slot_mapping, block_size)
-
+        has_cache = k_cache.numel() > 0 and v_cache.numel() > 0 and context.slot_mapping is not None
+        if has_cache and k.dim() == 4:  # (B, N, KVH, D) -> (B*N, KVH, D)
+            k = k.reshape(-1, k.shape[-2], k.shape[-1])
+            v = v.reshape(-1, v.shape[-2], v.shape[-1])
         scale = self.scale / (self.head_dim ** 0.5)
 
         if context.is_prefill:
+            if has_cache:
+                store_kvcache(k, v, k_cache, v_cache, context.slot_mapping, block_size)
             raise NotImplementedError(
                 "prefill attention is outside the B200 decode path (SURVEY.md §8(f) N3)")
         if q.dim() == 4:  # (B, 1, H, D) -> (B, H, D)
             q = q.squeeze(1)
-        o = paged_attention_decode(q, k_cache, v_cache, context.block_tables, context.context_lens,
-                                   scale, self.num_heads, self.num_kv_heads, self.head_dim,
-                                   block_size, out=out)
+        one_token_each = (has_cache and k.shape[0] == q.shape[0]
+                          and context.slot_mapping.dtype == context.context_lens.dtype)
+        if one_token_each:
+            # the reference's decode step: one new token per sequence -> store fused into decode
+            o = decode_step(q, k, v, k_cache, v_cache, context.slot_mapping, context.block_tables,
+                            context.context_lens, scale, self.num_heads, self.num_kv_heads,
+                            self.head_dim, block_size, out=out)
+        else:
+            if has_cache:
+                store_kvcache(k, v, k_cache, v_cache, context.slot_mapping, block_size)
+            o = paged_attention_decode(q, k_cache, v_cache, context.block_tables, context.context_lens,
+                                       scale, self.num_heads, self.num_kv_heads, self.head_dim,
+                                       block_size, out=out)
         return o.reshape(o.shape[0], self.num_heads * self.head_dim)
 
 
@@ -296,7 +351,7 @@ class HostDecodeStep:
             nbytes = _ext.lib().mvl_paged_decode_workspace_bytes(
                 batch, num_heads, self.num_kv_heads, self.head_dim, max_num_blocks, self.block_size,
                 self.code, chunk_tokens)
-        self.ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+        self.ws = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device=dev)  # counters start at zero
         self.ws_bytes = nbytes
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in
                              (self.q_h, self.k_h, self.v_h, self.slot_h, self.ctx_h, self.bt_h))

@@ -87,12 +87,13 @@ def test_peer_stores_gather_on_one_gpu(cuda_device, name, world):
         vc = inp["v_cache"][:, :, sh.kv_heads].contiguous().to(cuda_device)
         nbytes = lib.mvl_paged_decode_workspace_bytes(B, sh.num_heads, sh.num_kv_heads, D, bt.shape[1],
                                                       inp["BS"], att._dtype_code(q), CHUNK)
-        ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=cuda_device)
+        ws = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device=cuda_device)  # counters at zero
         _ext.check(lib.mvl_paged_decode_peers(
             ctypes.cast(ptrs, ctypes.c_void_p), world, H, sh.q_heads.start, q.data_ptr(), kc.data_ptr(),
             vc.data_ptr(), bt.data_ptr(), cl.data_ptr(), int(cl.dtype == torch.int64), B, bt.shape[1],
             bt.stride(0), sh.num_heads, sh.num_kv_heads, D, inp["BS"], kc.shape[0], float(inp["scale"]),
-            att._dtype_code(q), ws.data_ptr(), nbytes, CHUNK, 0, torch.cuda.current_stream().cuda_stream))
+            att._dtype_code(q), ws.data_ptr(), nbytes, CHUNK, _ext.DECODE_FUSED_COMBINE,
+            torch.cuda.current_stream().cuda_stream))
     torch.cuda.synchronize()
     for buf in bufs:
         assert torch.equal(buf, full)

@@ -292,3 +292,53 @@ def test_c3_full_size_properties(cuda_device):
     kc2, vc2 = w["k_cache"][perm], w["v_cache"][perm]
     out_p = paged_attention_decode(w["q"], kc2, vc2, bt2, *args[3:])
     assert torch.equal(out_p, out)
+
+
+# ------------------------------------------------------------------ fused step (one launch)
+@pytest.mark.parametrize("name", ["ragged_bf16", "long_split", "bs256_bf16", "g8_ragged", "g5_d64"])
+def test_fused_step_equals_separate_launches(cuda_device, name):
+    """mvl_decode_step (store + split + combine in one launch) against the three separate launches
+    (store_kvcache, split kernel, combine kernel): identical cache, same output to fp32 rounding;
+    three fused calls in a row (arrival counters must return to zero) give identical results."""
+    from minivllm_b200 import _ext
+    from minivllm_b200.layers.attention import decode_step
+    inp = make_inputs(name)
+    B, KVH, D, BS = inp["q"].shape[0], inp["KVH"], inp["D"], inp["BS"]
+    g = torch.Generator().manual_seed(123)
+    k = torch.randn(B, KVH, D, generator=g).to(inp["q"].dtype)
+    v = torch.randn(B, KVH, D, generator=g).to(inp["q"].dtype)
+    last = inp["context_lens"].long() - 1
+    slots = (inp["block_tables"][torch.arange(B), last // BS].long() * BS + last % BS).to(inp["context_lens"].dtype)
+    dev = _dev(inp, cuda_device)
+    kc_a, vc_a = dev["k_cache"].clone(), dev["v_cache"].clone()
+    store_kvcache(k.to(cuda_device), v.to(cuda_device), kc_a, vc_a, slots.to(cuda_device), BS)
+    want = paged_attention_decode(dev["q"], kc_a, vc_a, dev["block_tables"], dev["context_lens"],
+                                  inp["scale"], inp["H"], KVH, D, BS, flags=0)
+    outs = []
+    kc_b, vc_b = dev["k_cache"].clone(), dev["v_cache"].clone()
+    for _ in range(3):
+        outs.append(decode_step(dev["q"], k.to(cuda_device), v.to(cuda_device), kc_b, vc_b,
+                                slots.to(cuda_device), dev["block_tables"], dev["context_lens"],
+                                inp["scale"], inp["H"], KVH, D, BS).clone())
+    assert torch.equal(kc_a, kc_b) and torch.equal(vc_a, vc_b)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])
+    a, r = TOL_EXACT[inp["q"].dtype]
+    diff = (outs[0].float() - want.float()).abs() - (a + r * want.float().abs())
+    assert diff.max() <= 0
+    # oracle on the updated cache
+    ref = c_oracle.paged_decode(inp["q"], kc_a.cpu(), vc_a.cpu(), inp["block_tables"], inp["context_lens"],
+                                inp["scale"], inp["H"], KVH, D, BS)
+    _assert_close(outs[0].float().cpu().numpy(), ref.numpy(), inp["q"].dtype)
+
+
+def test_fused_step_skips_rows_without_a_slot(cuda_device):
+    from minivllm_b200.layers.attention import decode_step
+    inp = _dev(make_inputs("ragged_bf16"), cuda_device)
+    B, KVH, D, BS = inp["q"].shape[0], inp["KVH"], inp["D"], inp["BS"]
+    k = torch.randn(B, KVH, D, device=cuda_device).to(torch.bfloat16)
+    slots = torch.full((B,), -1, dtype=inp["context_lens"].dtype, device=cuda_device)
+    kc, vc = inp["k_cache"].clone(), inp["v_cache"].clone()
+    out = decode_step(inp["q"], k, k, kc, vc, slots, inp["block_tables"], inp["context_lens"],
+                      inp["scale"], inp["H"], KVH, D, BS)
+    assert torch.equal(kc, inp["k_cache"]) and torch.equal(vc, inp["v_cache"])
+    assert torch.equal(out, _run(inp))
