@@ -39,6 +39,9 @@ SPECS = {
     "c3": Spec("c3", 32, 8, 128, 16, "bf16", 3, 256),
     "c4": Spec("c4", 64, 8, 128, 16, "bf16", 4, 512),
     "c5": Spec("c5", 32, 8, 128, 16, "bf16", 5, 32),
+    # experiment: same bytes as c3 but ONE kv head (pages fully contiguous, 4 KB): isolates the
+    # effect of the 2 KB row pitch of the 8-head layout on DRAM efficiency
+    "c3x": Spec("c3x", 4, 1, 128, 16, "bf16", 3, 2048),
 }
 
 
@@ -61,7 +64,7 @@ def build_tables(name: str, batch: Optional[int] = None) -> Tables:
         ctx = np.full(B, 512, dtype=np.int64)
     elif name == "c2":
         ctx = np.full(B, 2048, dtype=np.int64)
-    elif name == "c3":
+    elif name in ("c3", "c3x"):
         ctx = rng.randint(1024, 8192 + 1, size=B).astype(np.int64)
     elif name == "c4":
         ctx = rng.randint(8192, 16384 + 1, size=B).astype(np.int64)
