@@ -94,19 +94,29 @@ struct DecodeCfg {
   static constexpr int TR = R * RPP;            // rows per warp tile
   static constexpr int ROWB = D * ES;           // bytes per row of one kv head
   static constexpr int TILEB = TR * ROWB;       // bytes per K (or V) tile = R * 512
-  static constexpr int NV = R * GT;             // partial scores per lane and tile
+  // Score phase granularity: the GT heads are scored GK at a time (NSUB sub-phases, q from shared
+  // memory when NSUB > 1); the P.V phase always carries all GT heads.  GK = 4 for 8-head tiles fits
+  // 3 CTAs per SM (167 registers) but measured SLOWER on B200 than scoring all 8 heads at once with
+  // 2 CTAs per SM (C4: 6.54 ms vs 6.12 ms): the re-read and re-conversion of K and the second
+  // transpose cost more issue slots than the extra warps recover.  So GK = GT.
+  static constexpr int GK = GT_;
+  static constexpr int NSUB = GT_ / GK;
+  static constexpr int NV = R * GK;             // partial scores per lane, tile and sub-phase
   static constexpr int NQ = NV / 4;             // ... in 16-byte quads
-  static constexpr int VPL = (NV / LPR) > 0 ? (NV / LPR) : 1;  // complete scores per lane
+  static constexpr int VPL = (NV / LPR) > 0 ? (NV / LPR) : 1;  // complete scores per lane and sub-phase
+  static constexpr int NSLOT = VPL * NSUB;      // complete scores per lane and tile
   static constexpr int XB_BYTES = 32 * NV * 4;  // transpose buffer
   static constexpr int PB_BYTES = ((TR * GT * 8 + 255) / 256) * 256;  // (p,p) pairs, 256-B granular
   static constexpr int RING = 3;                // ring slots; RING-1 half tiles in flight
   static constexpr int WARP_SMEM = RING * TILEB + XB_BYTES + PB_BYTES;
-  static constexpr int SMEM = NW * WARP_SMEM;
+  static constexpr int QB_BYTES = (NSUB > 1) ? GT * D * 4 : 0;  // CTA-wide pre-scaled q (fp32)
+  static constexpr int SMEM = NW * WARP_SMEM + QB_BYTES;
   static constexpr int MRG_BYTES = RPP * GT * D * 4 + GT * 8;  // merge area, aliases the ring
   static_assert(LPR >= 8 && LPR <= 32, "head_dim / dtype combination not supported");
   static_assert(MRG_BYTES <= RING * TILEB, "merge area must fit in the ring");
   static_assert(NV % 4 == 0 && NQ >= 2, "NV must be a multiple of 8");
-  static_assert(VPL == 1 || VPL == 2 || VPL == 4 || VPL == 8, "unsupported scores-per-lane");
+  static_assert(VPL == 1 || VPL == 2 || VPL == 4, "unsupported scores-per-lane");
+  static_assert(VPL <= GK, "a lane's scores of one sub-phase must belong to one row");
   // the XOR swizzle of the transpose buffer needs rows aligned to their size (<= 256 B): every
   // region size is a multiple of 256 and the kernel uses no static shared memory
   static_assert((RING * TILEB) % 256 == 0 && XB_BYTES % 256 == 0 && WARP_SMEM % 256 == 0, "alignment");
@@ -123,12 +133,12 @@ __device__ __forceinline__ int xb_key(int L) {
 // UNIFORM: every warp tile lies inside one page (block_size % TR == 0), so one block-table entry
 // addresses the whole tile; otherwise each row looks up its own page.
 template <typename T, int D, int GT, bool UNIFORM>
-__global__ void __launch_bounds__(DecodeCfg<T, D, GT>::NW * 32, (GT >= 8 ? 2 : 3))
+__global__ void __launch_bounds__(DecodeCfg<T, D, GT>::NW * 32, (DecodeCfg<T, D, GT>::GK >= 8 ? 2 : 3))
 paged_decode_split_kernel(const DecodeParams p) {
   using C = DecodeCfg<T, D, GT>;
   constexpr int NP = C::NP, R = C::R, RPP = C::RPP, LPR = C::LPR, TR = C::TR, NV = C::NV,
                 NQ = C::NQ, VPL = C::VPL, NW = C::NW, ROWB = C::ROWB, TILEB = C::TILEB,
-                RING = C::RING;
+                RING = C::RING, GK = C::GK, NSUB = C::NSUB, NSLOT = C::NSLOT;
   extern __shared__ __align__(1024) unsigned char smem[];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -182,31 +192,55 @@ paged_decode_split_kernel(const DecodeParams p) {
   const uint32_t xbuf = wbase + C::RING * TILEB;
   const uint32_t pbuf = xbuf + C::XB_BYTES;
 
-  // ---- q for the GT heads of this tile, as packed fp32 pairs scaled by scale*log2(e)
-  u64 q2[GT][NP];
+  // ---- q for the GT heads of this tile, as packed fp32 pairs scaled by scale*log2(e):
+  // in registers when all heads are scored at once, else in shared memory (qbuf, [head][D] fp32)
+  u64 q2[GK][NP];
+  const uint32_t qbuf = smem_u32(smem) + NW * C::WARP_SMEM;
   {
     const u64 qs = pack2(p.qscale, p.qscale);
+    if (NSUB == 1) {
 #pragma unroll
-    for (int g = 0; g < GT; ++g) {
-      uint4 raw = make_uint4(0, 0, 0, 0);
-      if (g < g_valid)
-        raw = *reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.q) +
-                                              ((long long)b * p.H + head0 + g) * D + c * C::VEC);
-      Chunk<T>::widen(raw, q2[g]);
+      for (int g = 0; g < GK; ++g) {
+        uint4 raw = make_uint4(0, 0, 0, 0);
+        if (g < g_valid)
+          raw = *reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.q) +
+                                                ((long long)b * p.H + head0 + g) * D + c * C::VEC);
+        Chunk<T>::widen(raw, q2[g]);
 #pragma unroll
-      for (int e = 0; e < NP; ++e) q2[g][e] = fmul2(q2[g][e], qs);
+        for (int e = 0; e < NP; ++e) q2[g][e] = fmul2(q2[g][e], qs);
+      }
+    } else {
+      for (int i = threadIdx.x; i < GT * LPR; i += NW * 32) {  // one 16-byte chunk of q each
+        const int g = i / LPR, cc = i % LPR;
+        uint4 raw = make_uint4(0, 0, 0, 0);
+        if (g < g_valid)
+          raw = *reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.q) +
+                                                ((long long)b * p.H + head0 + g) * D + cc * C::VEC);
+        u64 w2[NP];
+        Chunk<T>::widen(raw, w2);
+#pragma unroll
+        for (int e = 0; e < NP; e += 2) {
+          float a0, a1, a2, a3;
+          unpack2(fmul2(w2[e], qs), a0, a1);
+          unpack2(fmul2(w2[e + 1], qs), a2, a3);
+          sts128(qbuf + (g * D + cc * C::VEC + e * 2) * 4,
+                 make_uint4(__float_as_uint(a0), __float_as_uint(a1), __float_as_uint(a2),
+                            __float_as_uint(a3)));
+        }
+      }
+      __syncthreads();
     }
   }
 
-  // ---- per-lane ownership of complete scores: slot i <-> (pass j_i, head g_i), row rr_i
-  int rr_s[VPL], g_s[VPL];
-  bool ok_s[VPL];
+  // ---- per-lane ownership of complete scores: slot s = sub*VPL + i <-> (pass j, head g), row rr
+  int rr_s[NSLOT], g_s[NSLOT];
+  bool ok_s[NSLOT];
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    const int idx = c * VPL + i;
-    ok_s[i] = idx < NV;
-    g_s[i] = idx % GT;
-    rr_s[i] = (idx / GT) * RPP + h;
+  for (int s = 0; s < NSLOT; ++s) {
+    const int idx = c * VPL + (s % VPL);
+    ok_s[s] = idx < NV;
+    g_s[s] = (s / VPL) * GK + idx % GK;
+    rr_s[s] = (idx / GK) * RPP + h;
   }
   const int idx0 = (c * VPL < NV) ? c * VPL : 0;  // first owned score (clamped for idle lanes)
 
@@ -272,7 +306,7 @@ paged_decode_split_kernel(const DecodeParams p) {
 
   float m_all[GT];
   u64 o2[GT][NP];
-  float m_slot[VPL], l_slot[VPL];
+  float m_slot[NSLOT], l_slot[NSLOT];
 #pragma unroll
   for (int g = 0; g < GT; ++g) {
     m_all[g] = -INFINITY;
@@ -280,7 +314,7 @@ paged_decode_split_kernel(const DecodeParams p) {
     for (int e = 0; e < NP; ++e) o2[g][e] = 0ull;
   }
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
+  for (int i = 0; i < NSLOT; ++i) {
     m_slot[i] = -INFINITY;
     l_slot[i] = 0.f;
   }
@@ -288,8 +322,10 @@ paged_decode_split_kernel(const DecodeParams p) {
   // loop-invariant shared-memory addresses, kept to a handful of registers
   const uint32_t xw = xbuf + lane * (NV * 4) + (xb_key<NQ>(lane) << 4);     // writer: xw ^ (k << 4)
   const uint32_t xr = xbuf + h * (LPR * NV * 4) + ((idx0 >> 2) << 4) + (idx0 & 3) * 4;  // reader
-  const uint32_t pw = pbuf + (h * NV + idx0) * 8;                           // my (p,p) pairs
-  const uint32_t pr = pbuf + h * NV * 8;                                    // pairs of my row group
+  // (p,p) pairs live as [row group h][pass j][head g]; a lane's VPL scores of one sub-phase are
+  // consecutive heads of one pass, so they are stored with one or two 16-byte stores
+  const uint32_t pw = pbuf + (h * R * GT + (idx0 / GK) * GT + idx0 % GK) * 8;
+  const uint32_t pr = pbuf + h * R * GT * 8;                                // pairs of my row group
 
   int slot_c = 0;  // ring slot of the half tile being consumed
 #pragma unroll 1
@@ -302,76 +338,84 @@ paged_decode_split_kernel(const DecodeParams p) {
     if (!(n & 1)) {
       // ================================================================ K: scores
       const int tstart = start + (warp + (n >> 1) * NW) * TR;
-      {
-        float sv[NV];
+      float sc[NSLOT];
 #pragma unroll
-        for (int j = 0; j < R; ++j) {
-          u64 k2[NP];
-          Chunk<T>::widen(lds128(tile + j * RPP * ROWB), k2);
+      for (int sub = 0; sub < NSUB; ++sub) {
+        if (NSUB > 1) {
+          if (sub > 0) __syncwarp();  // the previous sub-phase's gather has read the transpose buffer
 #pragma unroll
-          for (int g = 0; g < GT; ++g) {
-            u64 acc = 0ull;
+          for (int g = 0; g < GK; ++g)
 #pragma unroll
-            for (int e = 0; e < NP; ++e) acc = ffma2(q2[g][e], k2[e], acc);
-            sv[j * GT + g] = hsum2(acc);
-          }
-          // publish the quads of partial scores completed by this pass (keeps few of them live)
-#pragma unroll
-          for (int k = (j * GT) / 4; k < ((j + 1) * GT) / 4; ++k)
-            sts128(xor_imm(xw, k << 4),
-                   make_uint4(__float_as_uint(sv[4 * k]), __float_as_uint(sv[4 * k + 1]),
-                              __float_as_uint(sv[4 * k + 2]), __float_as_uint(sv[4 * k + 3])));
+            for (int e = 0; e < NP; e += 2) {
+              uint4 v = lds128(qbuf + ((sub * GK + g) * D + c * C::VEC + e * 2) * 4);
+              q2[g][e] = pack2(__uint_as_float(v.x), __uint_as_float(v.y));
+              q2[g][e + 1] = pack2(__uint_as_float(v.z), __uint_as_float(v.w));
+            }
         }
-      }
-      __syncwarp();
-      // gather: lane (h,c) sums the LPR partials of its VPL scores (source lane h*LPR+cc, whose
-      // swizzle key depends only on cc & 7)
-      float sc[VPL];
-      {
-        constexpr int NPAIR = (VPL + 1) / 2;
-        u64 accp[NPAIR];
-        float acc1 = 0.f;
+        {
+          float sv[NV];
 #pragma unroll
-        for (int i = 0; i < NPAIR; ++i) accp[i] = 0ull;
-        constexpr int NK = (NQ >= 8) ? 8 : NQ;       // distinct swizzle keys
-        constexpr int KSH = (NQ >= 8) ? 0 : (NQ == 4 ? 1 : 2);  // key(cc) = (cc >> KSH) & (NK-1)
+          for (int j = 0; j < R; ++j) {
+            u64 k2[NP];
+            Chunk<T>::widen(lds128(tile + j * RPP * ROWB), k2);
 #pragma unroll
-        for (int kk = 0; kk < NK; ++kk) {
-          const uint32_t a = xor_imm(xr, kk << 4);
+            for (int g = 0; g < GK; ++g) {
+              u64 acc = 0ull;
 #pragma unroll
-          for (int cc = 0; cc < LPR; ++cc) {
-            if (((cc >> KSH) & (NK - 1)) != kk) continue;
-            const uint32_t at = a + cc * (NV * 4);
-            if (VPL == 1) {
-              acc1 += __uint_as_float(lds32(at));
-            } else if (VPL == 2) {
-              uint2 v = lds64(at);
-              accp[0] = fadd2(accp[0], pack2(__uint_as_float(v.x), __uint_as_float(v.y)));
-            } else {
-              // VPL = 4 or 8: consecutive quads; the swizzle flips quad bits, so quad q4 of this
-              // lane's run sits at (at ^ (q4 << 4)) (the run starts at an even multiple of VPL/4)
+              for (int e = 0; e < NP; ++e) acc = ffma2(q2[g][e], k2[e], acc);
+              sv[j * GK + g] = hsum2(acc);
+            }
+            // publish the quads of partial scores completed by this pass (keeps few of them live)
 #pragma unroll
-              for (int q4 = 0; q4 < VPL / 4; ++q4) {
-                uint4 v = lds128(at ^ (q4 << 4));
-                accp[(2 * q4) % NPAIR] = fadd2(accp[(2 * q4) % NPAIR],
-                                              pack2(__uint_as_float(v.x), __uint_as_float(v.y)));
-                accp[(2 * q4 + 1) % NPAIR] = fadd2(accp[(2 * q4 + 1) % NPAIR],
-                                                  pack2(__uint_as_float(v.z), __uint_as_float(v.w)));
+            for (int k = (j * GK) / 4; k < ((j + 1) * GK) / 4; ++k)
+              sts128(xor_imm(xw, k << 4),
+                     make_uint4(__float_as_uint(sv[4 * k]), __float_as_uint(sv[4 * k + 1]),
+                                __float_as_uint(sv[4 * k + 2]), __float_as_uint(sv[4 * k + 3])));
+          }
+        }
+        __syncwarp();
+        // gather: lane (h,c) sums the LPR partials of its VPL scores (source lane h*LPR+cc, whose
+        // swizzle key depends only on cc)
+        {
+          constexpr int NPAIR = (VPL + 1) / 2;
+          u64 accp[NPAIR];
+          float acc1 = 0.f;
+#pragma unroll
+          for (int i = 0; i < NPAIR; ++i) accp[i] = 0ull;
+          constexpr int NK = (NQ >= 8) ? 8 : NQ;       // distinct swizzle keys
+          constexpr int KSH = (NQ >= 8) ? 0 : (NQ == 4 ? 1 : 2);  // key(cc) = (cc >> KSH) & (NK-1)
+#pragma unroll
+          for (int kk = 0; kk < NK; ++kk) {
+            const uint32_t a = xor_imm(xr, kk << 4);
+#pragma unroll
+            for (int cc = 0; cc < LPR; ++cc) {
+              if (((cc >> KSH) & (NK - 1)) != kk) continue;
+              const uint32_t at = a + cc * (NV * 4);
+              if (VPL == 1) {
+                acc1 += __uint_as_float(lds32(at));
+              } else if (VPL == 2) {
+                uint2 v = lds64(at);
+                accp[0] = fadd2(accp[0], pack2(__uint_as_float(v.x), __uint_as_float(v.y)));
+              } else {
+                uint4 v = lds128(at);
+                accp[0] = fadd2(accp[0], pack2(__uint_as_float(v.x), __uint_as_float(v.y)));
+                accp[1 % NPAIR] = fadd2(accp[1 % NPAIR], pack2(__uint_as_float(v.z), __uint_as_float(v.w)));
               }
             }
           }
-        }
-        if (VPL == 1) {
-          sc[0] = acc1;
-        } else {
+          if (VPL == 1) {
+            sc[sub * VPL] = acc1;
+          } else {
 #pragma unroll
-          for (int i = 0; i < NPAIR; ++i) unpack2(accp[i], sc[(2 * i) % VPL], sc[(2 * i + 1) % VPL]);
+            for (int i = 0; i < NPAIR; ++i)
+              unpack2(accp[i], sc[sub * VPL + (2 * i) % VPL], sc[sub * VPL + (2 * i + 1) % VPL]);
+          }
         }
       }
       // ---- online softmax with a lazily refreshed maximum
       bool need = false;
 #pragma unroll
-      for (int i = 0; i < VPL; ++i) {
+      for (int i = 0; i < NSLOT; ++i) {
         const bool valid = ok_s[i] && (tstart + rr_s[i] < end);
         sc[i] = valid ? sc[i] : -INFINITY;
         need |= sc[i] > m_slot[i] + 8.f;
@@ -379,7 +423,7 @@ paged_decode_split_kernel(const DecodeParams p) {
       if (__any_sync(0xffffffffu, need)) {
         // rare: publish raw scores as [row][head], every lane takes the per-head maxima
 #pragma unroll
-        for (int i = 0; i < VPL; ++i)
+        for (int i = 0; i < NSLOT; ++i)
           if (ok_s[i]) sts32(pbuf + (rr_s[i] * GT + g_s[i]) * 4, __float_as_uint(sc[i]));
         __syncwarp();
         float mx[GT];
@@ -400,7 +444,7 @@ paged_decode_split_kernel(const DecodeParams p) {
 #pragma unroll
           for (int e = 0; e < NP; ++e) o2[g][e] = fmul2(o2[g][e], a2);
 #pragma unroll
-          for (int i = 0; i < VPL; ++i)
+          for (int i = 0; i < NSLOT; ++i)
             if (g_s[i] == g) {
               l_slot[i] *= alpha;
               m_slot[i] = mx[g];
@@ -409,22 +453,27 @@ paged_decode_split_kernel(const DecodeParams p) {
         }
         __syncwarp();
       }
-      float pr_v[VPL];
+      float pr_v[NSLOT];
 #pragma unroll
-      for (int i = 0; i < VPL; ++i) {
+      for (int i = 0; i < NSLOT; ++i) {
         pr_v[i] = fast_exp2(sc[i] - m_slot[i]);  // masked rows: exp2(-inf) = 0
         l_slot[i] += pr_v[i];
       }
-      // (p,p) pairs, lane-contiguous: [row group h][idx = pass*GT + head] -> conflict-free stores
+      // publish the (p,p) pairs: per sub-phase VPL consecutive heads of one pass
       if (c * VPL < NV) {
-        if (VPL == 1) {
-          sts64(pw, make_uint2(__float_as_uint(pr_v[0]), __float_as_uint(pr_v[0])));
-        } else {
 #pragma unroll
-          for (int i = 0; i < VPL; i += 2)
-            sts128(pw + i * 8, make_uint4(__float_as_uint(pr_v[i]), __float_as_uint(pr_v[i]),
-                                          __float_as_uint(pr_v[(i + 1) % VPL]),
-                                          __float_as_uint(pr_v[(i + 1) % VPL])));
+        for (int sub = 0; sub < NSUB; ++sub) {
+          const uint32_t pa = pw + sub * GK * 8;
+          if (VPL == 1) {
+            sts64(pa, make_uint2(__float_as_uint(pr_v[sub]), __float_as_uint(pr_v[sub])));
+          } else {
+#pragma unroll
+            for (int i = 0; i < VPL; i += 2)
+              sts128(pa + i * 8,
+                     make_uint4(__float_as_uint(pr_v[sub * VPL + i]), __float_as_uint(pr_v[sub * VPL + i]),
+                                __float_as_uint(pr_v[sub * VPL + (i + 1) % VPL]),
+                                __float_as_uint(pr_v[sub * VPL + (i + 1) % VPL])));
+          }
         }
       }
     } else {
@@ -464,7 +513,7 @@ paged_decode_split_kernel(const DecodeParams p) {
   {
     // l per head: gather every lane's slot sums through the transpose buffer
 #pragma unroll
-    for (int i = 0; i < VPL; ++i) sts32(xbuf + (lane * VPL + i) * 4, __float_as_uint(l_slot[i]));
+    for (int i = 0; i < NSLOT; ++i) sts32(xbuf + (lane * NSLOT + i) * 4, __float_as_uint(l_slot[i]));
     __syncwarp();
     float lsum[GT];
 #pragma unroll
@@ -472,9 +521,10 @@ paged_decode_split_kernel(const DecodeParams p) {
 #pragma unroll
     for (int L = 0; L < 32; ++L)
 #pragma unroll
-      for (int i = 0; i < VPL; ++i) {
-        const int idx = (L % LPR) * VPL + i;
-        if (idx < NV) lsum[idx % GT] += __uint_as_float(lds32(xbuf + (L * VPL + i) * 4));
+      for (int i = 0; i < NSLOT; ++i) {
+        const int idx = (L % LPR) * VPL + i % VPL;
+        if (idx < NV)
+          lsum[(i / VPL) * GK + idx % GK] += __uint_as_float(lds32(xbuf + (L * NSLOT + i) * 4));
       }
 #pragma unroll
     for (int g = 0; g < GT; ++g) {
@@ -536,7 +586,7 @@ paged_decode_split_kernel(const DecodeParams p) {
   // ---- fused combine: the last of this (sequence, head tile)'s n_act CTAs to arrive merges them.
   // The flag lives in dynamic shared memory (warp 0's probability buffer, idle by now): a static
   // __shared__ variable would shift the dynamic base and break the transpose buffer's alignment.
-  const uint32_t flag = sbase + C::RING * TILEB + C::XB_BYTES;
+  const uint32_t flag = sbase + C::RING * TILEB + C::XB_BYTES;  // warp 0's probability buffer
   __syncthreads();  // every thread's partial stores are issued
   if (threadIdx.x == 0) {
     __threadfence();  // release: the CTA's partials (ordered by the barrier) before the count
