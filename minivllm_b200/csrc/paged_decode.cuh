@@ -99,7 +99,8 @@ struct DecodeCfg {
   // 3 CTAs per SM (167 registers) but measured SLOWER on B200 than scoring all 8 heads at once with
   // 2 CTAs per SM (C4: 6.54 ms vs 6.12 ms): the re-read and re-conversion of K and the second
   // transpose cost more issue slots than the extra warps recover.  So GK = GT.
-  static constexpr int GK = GT_;
+  // (The one exception: 16-bit head_dim 64 would own 8 scores per lane; it uses two sub-phases.)
+  static constexpr int GK = (GT_ >= 8 && LPR == 8) ? 4 : GT_;
   static constexpr int NSUB = GT_ / GK;
   static constexpr int NV = R * GK;             // partial scores per lane, tile and sub-phase
   static constexpr int NQ = NV / 4;             // ... in 16-byte quads
