@@ -57,6 +57,11 @@ typedef enum mvl_dtype {
                                        use; every call leaves them zero.  Ignored (separate combine
                                        kernel) when batch * kv-head tiles > 65536. */
 
+#define MVL_DECODE_LOAD_TMA 8u /* fetch K/V tiles with tensor-map TMA (cp.async.bulk.tensor, one
+                                  instruction per tile, mbarrier completion) instead of cp.async.
+                                  Used when block_size is a multiple of the 16-row (bf16/fp16,
+                                  head_dim 128) warp tile; otherwise the cp.async path runs. */
+
 /* Library / ABI identification.  No reference counterpart (the reference has no native layer). */
 int mvl_abi_version(void);
 

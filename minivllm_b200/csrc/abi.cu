@@ -135,6 +135,41 @@ size_t plan_workspace(const Plan& pl, long long batch, int H, int D) {
   return kCounterBytes + rows * D * sizeof(float) + rows * sizeof(float2);
 }
 
+// ---- tensor maps for the TMA load path: [num_slots][KVH][D] with a [tile_rows][1][D] box
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {  // from the driver, no link-time dependency on libcuda
+  static EncodeTiledFn fn = [] {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      ptr = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(ptr);
+  }();
+  return fn;
+}
+
+bool make_cache_map(CUtensorMap* map, const void* cache, int dtype, int D, int KVH, long long num_slots,
+                    int tile_rows) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc) return false;
+  const CUtensorMapDataType dt = dtype == MVL_DTYPE_F32    ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                 : dtype == MVL_DTYPE_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                                          : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  const cuuint64_t es = elem_size(dtype);
+  const cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)KVH, (cuuint64_t)num_slots};
+  const cuuint64_t strides[2] = {(cuuint64_t)D * es, (cuuint64_t)KVH * D * es};  // bytes, dims 1..2
+  const cuuint32_t box[3] = {(cuuint32_t)D, 1u, (cuuint32_t)tile_rows};
+  const cuuint32_t estr[3] = {1u, 1u, 1u};
+  return enc(map, dt, 3, const_cast<void*>(cache), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 struct StoreArgs {  // the step's new K/V rows for the fused store (mvl_decode_step)
   const void* key;
   const void* value;
@@ -304,12 +339,20 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
   cudaStream_t s = (cudaStream_t)stream;
   if (!(flags & MVL_DECODE_ONLY_COMBINE)) {
     dim3 grid((unsigned)(num_kv_heads * pl.n_gt), (unsigned)batch, (unsigned)pl.max_splits);
+    CUtensorMap maps[2];
+    const CUtensorMap* use_maps = nullptr;
+    if ((flags & MVL_DECODE_LOAD_TMA) && block_size % pl.tr == 0) {
+      const long long slots = num_blocks * (long long)block_size;
+      if (make_cache_map(&maps[0], k_cache, elem_dtype, head_dim, num_kv_heads, slots, pl.tr) &&
+          make_cache_map(&maps[1], v_cache, elem_dtype, head_dim, num_kv_heads, slots, pl.tr))
+        use_maps = maps;
+    }
     int e = -1000;
     switch (elem_dtype) {
-      case MVL_DTYPE_F32: e = mvl::launch_decode_split<float>(p, head_dim, pl.gt, grid, s); break;
-      case MVL_DTYPE_F16: e = mvl::launch_decode_split<__half>(p, head_dim, pl.gt, grid, s); break;
+      case MVL_DTYPE_F32: e = mvl::launch_decode_split<float>(p, use_maps, head_dim, pl.gt, grid, s); break;
+      case MVL_DTYPE_F16: e = mvl::launch_decode_split<__half>(p, use_maps, head_dim, pl.gt, grid, s); break;
       case MVL_DTYPE_BF16:
-        e = mvl::launch_decode_split<__nv_bfloat16>(p, head_dim, pl.gt, grid, s);
+        e = mvl::launch_decode_split<__nv_bfloat16>(p, use_maps, head_dim, pl.gt, grid, s);
         break;
     }
     if (e == -1000) return MVL_ERR_SHAPE;

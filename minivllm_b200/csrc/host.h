@@ -13,8 +13,10 @@ int launch_store_kvcache(const void* key, const void* value, void* k_cache, void
 
 // Launchers, one translation unit per element type (keeps nvcc parallel and fast).
 // Return cudaSuccess (0) or the cudaError_t of the failed call; -1000 if (D, GT) is not built.
+// maps: {K cache, V cache} tensor maps for the TMA load path, or nullptr for the cp.async path.
 template <typename T>
-int launch_decode_split(const DecodeParams& p, int head_dim, int gt, dim3 grid, cudaStream_t s);
+int launch_decode_split(const DecodeParams& p, const CUtensorMap* maps, int head_dim, int gt, dim3 grid,
+                        cudaStream_t s);
 template <typename T>
 int launch_decode_combine(const DecodeParams& p, int head_dim, long long rows, cudaStream_t s);
 // Rows of one warp tile for (T, head_dim, gt): the chunk must be a multiple of 4 warps x this.

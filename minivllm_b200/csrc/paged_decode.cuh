@@ -25,6 +25,8 @@
 //   At the end the NW warps' (m, l, o) states are merged through shared memory and the CTA writes
 //   either the final row (sequence fits one chunk) or an fp32 partial for the combine kernel.
 #pragma once
+#include <cuda.h>  // CUtensorMap (type only; the encoder is fetched from the driver at run time)
+
 #include "common.cuh"
 
 namespace mvl {
@@ -109,7 +111,8 @@ struct DecodeCfg {
   static constexpr int XB_BYTES = 32 * NV * 4;  // transpose buffer
   static constexpr int PB_BYTES = ((TR * GT * 8 + 255) / 256) * 256;  // (p,p) pairs, 256-B granular
   static constexpr int RING = 3;                // ring slots; RING-1 half tiles in flight
-  static constexpr int WARP_SMEM = RING * TILEB + XB_BYTES + PB_BYTES;
+  static constexpr int BAR_BYTES = 256;         // RING mbarriers (TMA variant), 256-B granular
+  static constexpr int WARP_SMEM = RING * TILEB + XB_BYTES + PB_BYTES + BAR_BYTES;
   static constexpr int QB_BYTES = (NSUB > 1) ? GT * D * 4 : 0;  // CTA-wide pre-scaled q (fp32)
   static constexpr int SMEM = NW * WARP_SMEM + QB_BYTES;
   static constexpr int MRG_BYTES = RPP * GT * D * 4 + GT * 8;  // merge area, aliases the ring
@@ -133,9 +136,14 @@ __device__ __forceinline__ int xb_key(int L) {
 
 // UNIFORM: every warp tile lies inside one page (block_size % TR == 0), so one block-table entry
 // addresses the whole tile; otherwise each row looks up its own page.
-template <typename T, int D, int GT, bool UNIFORM>
+// TMA: K/V tiles are fetched with ONE 3-D tiled TMA load per tile (cp.async.bulk.tensor over the
+// tensor map [num_slots][KVH][D], box [TR][1][D]) issued by lane 0 and completed on a per-slot
+// mbarrier, instead of 8 x 32 lane-wide cp.async (needs UNIFORM).  Same ring, same math.
+template <typename T, int D, int GT, bool UNIFORM, bool TMA>
 __global__ void __launch_bounds__(DecodeCfg<T, D, GT>::NW * 32, (DecodeCfg<T, D, GT>::GK >= 8 ? 2 : 3))
-paged_decode_split_kernel(const DecodeParams p) {
+paged_decode_split_kernel(const DecodeParams p, const __grid_constant__ CUtensorMap tm_k,
+                          const __grid_constant__ CUtensorMap tm_v) {
+  static_assert(!TMA || UNIFORM, "the TMA variant needs whole tiles inside one page");
   using C = DecodeCfg<T, D, GT>;
   constexpr int NP = C::NP, R = C::R, RPP = C::RPP, LPR = C::LPR, TR = C::TR, NV = C::NV,
                 NQ = C::NQ, VPL = C::VPL, NW = C::NW, ROWB = C::ROWB, TILEB = C::TILEB,
@@ -192,6 +200,15 @@ paged_decode_split_kernel(const DecodeParams p) {
   const uint32_t ring = wbase;
   const uint32_t xbuf = wbase + C::RING * TILEB;
   const uint32_t pbuf = xbuf + C::XB_BYTES;
+  const uint32_t bars = pbuf + C::PB_BYTES;  // RING mbarriers of this warp (TMA variant)
+  if (TMA) {
+    if (lane == 0) {
+#pragma unroll
+      for (int s = 0; s < RING; ++s) mbar_init(bars + s * 8, 1);
+      mbar_fence_init();
+    }
+    __syncwarp();
+  }
 
   // ---- q for the GT heads of this tile, as packed fp32 pairs scaled by scale*log2(e):
   // in registers when all heads are scored at once, else in shared memory (qbuf, [head][D] fp32)
@@ -271,7 +288,14 @@ paged_decode_split_kernel(const DecodeParams p) {
       const int tstart = start + (warp + (n >> 1) * NW) * TR;
       const char* base = (n & 1) ? vbase : kbase;
       const uint32_t dst = ring + slot * TILEB + lane_off;
-      if (UNIFORM) {
+      if (TMA) {
+        if (lane == 0) {
+          const uint32_t bar = bars + slot * 8;
+          mbar_expect_tx(bar, TILEB);
+          tma_load_3d(ring + slot * TILEB, (n & 1) ? &tm_v : &tm_k, 0, kvh,
+                      (int)((blk_a << p.bs_shift) + (tstart & bs_mask)), bar);
+        }
+      } else if (UNIFORM) {
         const uint32_t row0 = (blk_a << p.bs_shift) + (tstart & bs_mask) + h;
         if (tstart + TR <= end) {  // whole tile valid: no per-row predicate
 #pragma unroll
@@ -295,7 +319,7 @@ paged_decode_split_kernel(const DecodeParams p) {
         }
       }
     }
-    cp_async_commit();
+    if (!TMA) cp_async_commit();
     if (UNIFORM && (n & 1)) {  // both halves of tile n/2 issued: advance the table prefetch
       blk_a = blk_b;
       blk_b = table_entry((n >> 1) + 2);
@@ -329,13 +353,29 @@ paged_decode_split_kernel(const DecodeParams p) {
   const uint32_t pr = pbuf + h * R * GT * 8;                                // pairs of my row group
 
   int slot_c = 0;  // ring slot of the half tile being consumed
+  uint32_t phase = 0;  // mbarrier parity of that slot's current use (TMA variant)
 #pragma unroll 1
   for (int n = 0; n < 2 * my_nt; ++n) {
-    cp_async_wait<RING - 2>();
-    __syncwarp();
-    issue(n + RING - 1, slot_c == 0 ? RING - 1 : slot_c - 1);
+    if (TMA) {
+      __syncwarp();  // every lane is done with the slot about to be refilled
+      issue(n + RING - 1, slot_c == 0 ? RING - 1 : slot_c - 1);
+      mbar_wait(bars + slot_c * 8, phase);
+      const int ts = start + (warp + (n >> 1) * NW) * TR;
+      if (ts + TR > end) {  // partial last tile: rows past the end hold whatever the page holds
+#pragma unroll
+        for (int j = 0; j < R; ++j)
+          if (ts + j * RPP + h >= end)
+            sts128(ring + slot_c * TILEB + lane_off + j * RPP * ROWB, make_uint4(0, 0, 0, 0));
+        fence_proxy_async();  // before a later TMA load refills these bytes
+      }
+    } else {
+      cp_async_wait<RING - 2>();
+      __syncwarp();
+      issue(n + RING - 1, slot_c == 0 ? RING - 1 : slot_c - 1);
+    }
     const uint32_t tile = ring + slot_c * TILEB + lane_off;
     slot_c = (slot_c + 1 == RING) ? 0 : slot_c + 1;
+    if (TMA && slot_c == 0) phase ^= 1;
     if (!(n & 1)) {
       // ================================================================ K: scores
       const int tstart = start + (warp + (n >> 1) * NW) * TR;

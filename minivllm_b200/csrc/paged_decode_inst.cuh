@@ -5,10 +5,10 @@
 
 namespace mvl {
 
-template <typename T, int D, int GT, bool UNIFORM>
-static int launch_split_u(const DecodeParams& p, dim3 grid, cudaStream_t s) {
+template <typename T, int D, int GT, bool UNIFORM, bool TMA>
+static int launch_split_u(const DecodeParams& p, const CUtensorMap* maps, dim3 grid, cudaStream_t s) {
   using C = DecodeCfg<T, D, GT>;
-  auto kern = paged_decode_split_kernel<T, D, GT, UNIFORM>;
+  auto kern = paged_decode_split_kernel<T, D, GT, UNIFORM, TMA>;
   // Opt in to > 48 KB dynamic shared memory once per device.
   static bool configured[64] = {};
   int dev = 0;
@@ -22,34 +22,37 @@ static int launch_split_u(const DecodeParams& p, dim3 grid, cudaStream_t s) {
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
     if (e != cudaSuccess) return (int)e;
   }
-  kern<<<grid, C::NW * 32, C::SMEM, s>>>(p);
+  static const CUtensorMap kNoMap = {};
+  kern<<<grid, C::NW * 32, C::SMEM, s>>>(p, TMA ? maps[0] : kNoMap, TMA ? maps[1] : kNoMap);
   return (int)cudaGetLastError();
 }
 
 template <typename T, int D, int GT>
-static int launch_split_one(const DecodeParams& p, dim3 grid, cudaStream_t s) {
+static int launch_split_one(const DecodeParams& p, const CUtensorMap* maps, dim3 grid, cudaStream_t s) {
   const bool uniform = ((1 << p.bs_shift) % DecodeCfg<T, D, GT>::TR) == 0;
-  return uniform ? launch_split_u<T, D, GT, true>(p, grid, s)
-                 : launch_split_u<T, D, GT, false>(p, grid, s);
+  if (uniform && maps) return launch_split_u<T, D, GT, true, true>(p, maps, grid, s);
+  return uniform ? launch_split_u<T, D, GT, true, false>(p, nullptr, grid, s)
+                 : launch_split_u<T, D, GT, false, false>(p, nullptr, grid, s);
 }
 
 template <typename T, int D>
-static int launch_split_d(const DecodeParams& p, int gt, dim3 grid, cudaStream_t s) {
+static int launch_split_d(const DecodeParams& p, const CUtensorMap* maps, int gt, dim3 grid,
+                          cudaStream_t s) {
   switch (gt) {
-    case 1: return launch_split_one<T, D, 1>(p, grid, s);
-    case 2: return launch_split_one<T, D, 2>(p, grid, s);
-    case 4: return launch_split_one<T, D, 4>(p, grid, s);
-    case 8: return launch_split_one<T, D, 8>(p, grid, s);
+    case 1: return launch_split_one<T, D, 1>(p, maps, grid, s);
+    case 2: return launch_split_one<T, D, 2>(p, maps, grid, s);
+    case 4: return launch_split_one<T, D, 4>(p, maps, grid, s);
+    case 8: return launch_split_one<T, D, 8>(p, maps, grid, s);
   }
   return -1000;
 }
 
 template <>
-int launch_decode_split<MVL_T>(const DecodeParams& p, int head_dim, int gt, dim3 grid,
-                               cudaStream_t s) {
+int launch_decode_split<MVL_T>(const DecodeParams& p, const CUtensorMap* maps, int head_dim, int gt,
+                               dim3 grid, cudaStream_t s) {
   switch (head_dim) {
-    case 64: return launch_split_d<MVL_T, 64>(p, gt, grid, s);
-    case 128: return launch_split_d<MVL_T, 128>(p, gt, grid, s);
+    case 64: return launch_split_d<MVL_T, 64>(p, maps, gt, grid, s);
+    case 128: return launch_split_d<MVL_T, 128>(p, maps, gt, grid, s);
   }
   return -1000;
 }

@@ -109,7 +109,7 @@ class PeerGatheredDecode:
 
         sh = self.shard
         if flags is None:
-            flags = _ext.DECODE_FUSED_COMBINE
+            flags = att.DEFAULT_DECODE_FLAGS
         batch, max_blocks = query.shape[0], block_tables.shape[1]
         code = att._dtype_code(query)
         lib = _ext.lib()

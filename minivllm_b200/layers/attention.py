@@ -22,6 +22,9 @@ from ..utils.context import get_context
 
 _DTYPES = {torch.float32: _ext.F32, torch.float16: _ext.F16, torch.bfloat16: _ext.BF16}
 
+# ABI flags used when a caller does not pass any: chunk combine fused into the split kernel.
+DEFAULT_DECODE_FLAGS = _ext.DECODE_FUSED_COMBINE
+
 # One scratch tensor per (device, stream) for split-KV partials, grown on demand and reused, so
 # steady-state calls allocate nothing (a CUDA-graph capture sees a fixed pointer).
 _workspaces: dict = {}
@@ -154,7 +157,7 @@ def paged_attention_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: 
     and merge the chunks inside the split kernel (MVL_DECODE_FUSED_COMBINE).
     """
     if flags is None:
-        flags = _ext.DECODE_FUSED_COMBINE
+        flags = DEFAULT_DECODE_FLAGS
     dev = _need_cuda(query=query, k_cache=k_cache, v_cache=v_cache, block_tables=block_tables,
                      context_lens=context_lens)
     if query.dim() != 3 or query.shape[1] != num_heads or query.shape[2] != head_dim:
@@ -219,7 +222,7 @@ def decode_step(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, k_c
                 v_cache: torch.Tensor, slot_mapping: torch.Tensor, block_tables: torch.Tensor,
                 context_lens: torch.Tensor, scale: float, num_heads: int, num_kv_heads: int,
                 head_dim: int, block_size: int, *, out: Optional[torch.Tensor] = None,
-                chunk_tokens: int = 0) -> torch.Tensor:
+                chunk_tokens: int = 0, flags: Optional[int] = None) -> torch.Tensor:
     """``store_kvcache`` then ``paged_attention_decode`` of one decode step in ONE kernel launch
     (``mvl_decode_step``).  ``key``/``value`` are the step's new rows (batch, num_kv_heads,
     head_dim); ``slot_mapping[b]`` is the slot of token ``context_lens[b] - 1`` (or -1), as the
@@ -242,7 +245,7 @@ def decode_step(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, k_c
 
     return paged_attention_decode(query, k_cache, v_cache, block_tables, context_lens, scale, num_heads,
                                   num_kv_heads, head_dim, block_size, out=out,
-                                  chunk_tokens=chunk_tokens,
+                                  chunk_tokens=chunk_tokens, flags=flags,
                                   _store=(rows(key), rows(value), slot_mapping.contiguous()))
 
 

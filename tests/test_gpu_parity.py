@@ -342,3 +342,35 @@ def test_fused_step_skips_rows_without_a_slot(cuda_device):
                       inp["scale"], inp["H"], KVH, D, BS)
     assert torch.equal(kc, inp["k_cache"]) and torch.equal(vc, inp["v_cache"])
     assert torch.equal(out, _run(inp))
+
+
+# ------------------------------------------------------------------ TMA load path
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_tma_load_path_matches_cp_async_bitwise(cuda_device, name):
+    """MVL_DECODE_LOAD_TMA only changes how tiles reach shared memory: results must be identical
+    bit for bit to the cp.async path (and so inherit its parity with the reference)."""
+    from minivllm_b200 import _ext
+    inp = _dev(make_inputs(name), cuda_device)
+    base = _run(inp, flags=_ext.DECODE_FUSED_COMBINE)
+    tma = _run(inp, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_LOAD_TMA)
+    assert torch.equal(base, tma)
+    tma2 = _run(inp, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_LOAD_TMA, chunk_tokens=64)
+    _assert_close(tma2.float().cpu().numpy(), _oracle(make_inputs(name)).numpy(), inp["q"].dtype)
+
+
+def test_tma_load_path_ignores_garbage_past_the_end(cuda_device):
+    """Rows of the last page beyond context_len may hold NaN bit patterns (uninitialised cache
+    memory); the TMA path loads them with the tile and must blank them."""
+    from minivllm_b200 import _ext
+    inp = make_inputs("ragged_bf16")
+    BS = inp["BS"]
+    kc, vc = inp["k_cache"].clone(), inp["v_cache"].clone()
+    for b, n in enumerate(inp["context_lens"].tolist()):
+        if n % BS:
+            blk = int(inp["block_tables"][b, (n - 1) // BS])
+            kc[blk, n % BS:] = float("nan")
+            vc[blk, n % BS:] = float("nan")
+    poisoned = _dev(dict(inp, k_cache=kc, v_cache=vc), cuda_device)
+    clean = _dev(inp, cuda_device)
+    for flags in (_ext.DECODE_FUSED_COMBINE, _ext.DECODE_FUSED_COMBINE | _ext.DECODE_LOAD_TMA):
+        assert torch.equal(_run(poisoned, flags=flags), _run(clean, flags=flags))
