@@ -152,6 +152,29 @@ int mvl_paged_decode_peers(void* const* out_peers, int num_peers, int total_head
                            size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream);
 
 /*
+ * mvl_qk_norm_rope_store — q/k RMSNorm + rotary embedding + KV-cache write in one pass over the
+ * projections' output.  Replaces, per layer, reference models/qwen3.py:104-108 (rms_norm on q and k,
+ * layers/layernorm.py:13-15: x / sqrt(mean(x^2) + eps) * gamma; rotary_emb, layers/
+ * rotary_embedding.py:74-83 with the half-split rotation of :4-23) followed by the store of
+ * layers/attention.py:498-510.
+ *   q (N, H, D), k and v (N, KVH, D): head dims dense, token strides in elements (views of the fused
+ *   QKV output are fine).  q_out (N, H, D) contiguous receives the normalised, rotated q (may be q
+ *   itself when q is contiguous).  k (normalised, rotated) and v (as is) go to
+ *   cache.view(-1, KVH, D)[slot_mapping[t]]; slot -1 skips the token; slot_mapping NULL = no cache
+ *   write.  gamma (D) fp32 or NULL (no RMSNorm: the reference skips it for qkv_bias models,
+ *   qwen3.py:104).  cos_sin_cache (max_position, D) fp32 laid out [cos(D/2) | sin(D/2)] per
+ *   position (rotary_embedding.py:62-68) or NULL (no rotation); positions (N,) int32/int64.
+ * Arithmetic in fp32, one rounding to elem_dtype on store.
+ */
+int mvl_qk_norm_rope_store(void* q_out, const void* q, const void* k, const void* v,
+                           int64_t q_token_stride, int64_t k_token_stride, int64_t v_token_stride,
+                           const float* gamma, float eps, const float* cos_sin_cache,
+                           int64_t max_position, const void* positions, int pos_is_i64,
+                           void* k_cache, void* v_cache, const void* slot_mapping, int slot_is_i64,
+                           int64_t num_slots, int64_t num_tokens, int num_heads, int num_kv_heads,
+                           int head_dim, int elem_dtype, void* stream);
+
+/*
  * mvl_decode_step — store + decode of one decode step in ONE kernel launch (plus the combine unless
  * MVL_DECODE_FUSED_COMBINE): what reference Attention.forward does with two Triton launches
  * (attention.py:498-510 store_kvcache, then :544-555 paged_attention_decode).  key/value are the

@@ -104,3 +104,28 @@ def test_store_oracles_follow_kernel_index_math(dtype):
     c_oracle.store_kvcache(key, val, k2, v2, slots)
     assert torch.equal(k2.view(torch.uint8), want_k.view(torch.uint8))
     assert torch.equal(v2.view(torch.uint8), want_v.view(torch.uint8))
+
+
+# ------------------------------------------------------------------ pre-attention pass (N4)
+import hashlib  # noqa: E402
+
+from cases_pre import PRE_CASES, make_pre_inputs, pre_digest  # noqa: E402
+from oracle import pre_attention_oracle as pre  # noqa: E402
+
+
+@pytest.mark.parametrize("name", sorted(PRE_CASES))
+def test_pre_attention_oracle_matches_reference_modules(name):
+    """oracle/pre_attention_oracle.py against LayerNorm.rms_forward + RotaryEmbedding.forward of the
+    reference (goldens written by tests/golden/make_golden_pre.py).  fp32 cases: 1e-5; the bf16
+    case: the reference rounds after every op, the oracle computes exactly -> 2e-2."""
+    c = PRE_CASES[name]
+    z = np.load(os.path.join(GOLD, f"pre_{name}.npz"))
+    inp = make_pre_inputs(name)
+    assert pre_digest(inp) == str(z["digest"])
+    table = pre.rope_table(c["base"], c["D"], c["max_position"])
+    assert hashlib.sha256(table.numpy().tobytes()).hexdigest() == str(z["table_digest"])
+    qn, kn = pre.pre_attention(inp["q"], inp["k"], inp["v"], inp["positions"],
+                               inp["gamma"] if c["norm"] else None, c["eps"], table, None, None, None)
+    tol = 1e-5 if c["dtype"] == "f32" else 2e-2
+    assert np.abs(qn.numpy() - z["q_ref"]).max() <= tol * max(1.0, np.abs(z["q_ref"]).max())
+    assert np.abs(kn.numpy() - z["k_ref"]).max() <= tol * max(1.0, np.abs(z["k_ref"]).max())
