@@ -8,7 +8,7 @@
 //   store_kvcache(k, v, ...)                  layers/attention.py:498-510
 // i.e. two torch.compile'd norm kernels, a gather + rotate, two contiguous() copies and the Triton
 // store.  Here one kernel reads each q/k/v row once and writes q (normalised, rotated) and the
-// cache rows.  HBM-bound byte work: one warp per (token, head) row, coalesced 4- or 8-byte lanes,
+// cache rows.  HBM-bound byte work: 128-bit coalesced lanes, several (token, head) rows per warp,
 // fp32 arithmetic, one rounding on store.
 #include "common.cuh"
 #include "host.h"
@@ -35,103 +35,111 @@ struct PreAttnParams {
   int H, KVH;
 };
 
-template <typename T> struct Pair;  // two adjacent elements <-> float2
-template <> struct Pair<float> {
-  static __device__ __forceinline__ float2 ld(const float* p) { return *reinterpret_cast<const float2*>(p); }
-  static __device__ __forceinline__ void st(float* p, float2 v) { *reinterpret_cast<float2*>(p) = v; }
-};
-template <> struct Pair<__nv_bfloat16> {
-  static __device__ __forceinline__ float2 ld(const __nv_bfloat16* p) {
-    return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
-  }
-  static __device__ __forceinline__ void st(__nv_bfloat16* p, float2 v) {
-    *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(v.x, v.y);
-  }
-};
-template <> struct Pair<__half> {
-  static __device__ __forceinline__ float2 ld(const __half* p) {
-    return __half22float2(*reinterpret_cast<const __half2*>(p));
-  }
-  static __device__ __forceinline__ void st(__half* p, float2 v) {
-    *reinterpret_cast<__half2*>(p) = __floats2half2_rn(v.x, v.y);
-  }
-};
-
-// One warp per row.  Lane l (< D/4) owns elements {2l, 2l+1} of the first half and the same two of
-// the second half — exactly the pairs the rotation mixes, so RoPE needs no cross-lane traffic.
+// 16-byte lanes.  A row of one head is CH = D*es/16 chunks; lane l of a row's LR = CH/2 lanes owns
+// chunk l of the first half and chunk l of the second half — exactly the element pairs the
+// rotation mixes, so RoPE needs no cross-lane traffic and the RMS sum is a shuffle over LR lanes.
+// A warp covers 32/LR rows at once (4 rows of 256 B for bf16, D = 128) with two 128-bit loads per
+// lane in flight.
 template <typename T, int D>
 __global__ void __launch_bounds__(256) qk_norm_rope_store_kernel(const PreAttnParams p) {
-  constexpr int HALF = D / 2;
-  const int lane = threadIdx.x & 31;
+  constexpr int VEC = Chunk<T>::VEC, NP = Chunk<T>::NP;
+  constexpr int HALF = D / 2, LR = HALF / VEC, RW = 32 / LR;
+  const int lane = threadIdx.x & 31, sub = lane / LR, l = lane % LR;
   const int rows_per_token = p.H + 2 * p.KVH;
-  const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (row >= p.num_tokens * rows_per_token) return;
-  const long long t = row / rows_per_token;
-  const int r = (int)(row - t * rows_per_token);
-  const bool active = lane < HALF / 2;
-  const int i0 = 2 * lane;  // index inside a half
-
+  const long long total = p.num_tokens * rows_per_token;
+  const long long row = ((long long)blockIdx.x * 8 + (threadIdx.x >> 5)) * RW + sub;
+  const bool in_range = row < total;
+  const long long rr = in_range ? row : total - 1;
+  const long long t = rr / rows_per_token;
+  const int r = (int)(rr - t * rows_per_token);
   const bool is_q = r < p.H, is_k = !is_q && r < p.H + p.KVH;
   const int head = is_q ? r : (is_k ? r - p.H : r - p.H - p.KVH);
-  const T* src = is_q ? reinterpret_cast<const T*>(p.q) + t * p.q_stride
-                      : (is_k ? reinterpret_cast<const T*>(p.k) + t * p.k_stride
-                              : reinterpret_cast<const T*>(p.v) + t * p.v_stride);
-  src += (long long)head * D;
-
+  const T* src = (is_q ? reinterpret_cast<const T*>(p.q) + t * p.q_stride
+                       : (is_k ? reinterpret_cast<const T*>(p.k) + t * p.k_stride
+                               : reinterpret_cast<const T*>(p.v) + t * p.v_stride)) +
+                 (long long)head * D + l * VEC;
   T* dst = nullptr;
-  if (is_q) {
-    dst = reinterpret_cast<T*>(p.q_out) + (t * p.H + head) * D;
-  } else if (p.slots != nullptr) {
-    const long long s = p.slot_is_i64 ? reinterpret_cast<const long long*>(p.slots)[t]
-                                      : (long long)reinterpret_cast<const int*>(p.slots)[t];
-    if (s >= 0 && s < p.num_slots)  // -1: token has no slot (attention.py:29-30)
-      dst = reinterpret_cast<T*>(is_k ? p.k_cache : p.v_cache) + (s * p.KVH + head) * D;
+  if (in_range) {
+    if (is_q) {
+      dst = reinterpret_cast<T*>(p.q_out) + (t * p.H + head) * D + l * VEC;
+    } else if (p.slots != nullptr) {
+      const long long s = p.slot_is_i64 ? reinterpret_cast<const long long*>(p.slots)[t]
+                                        : (long long)reinterpret_cast<const int*>(p.slots)[t];
+      if (s >= 0 && s < p.num_slots)  // -1: token has no slot (attention.py:29-30)
+        dst = reinterpret_cast<T*>(is_k ? p.k_cache : p.v_cache) + (s * p.KVH + head) * D + l * VEC;
+    }
   }
-  if (dst == nullptr) return;  // warp-uniform
-
-  float2 a = make_float2(0.f, 0.f), b = make_float2(0.f, 0.f);  // first-half pair, second-half pair
-  if (active) {
-    a = Pair<T>::ld(src + i0);
-    b = Pair<T>::ld(src + HALF + i0);
+  const bool live = dst != nullptr;
+  uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
+  if (live) {
+    ra = __ldg(reinterpret_cast<const uint4*>(src));
+    rb = __ldg(reinterpret_cast<const uint4*>(src + HALF));
   }
-  if (is_q || is_k) {
-    if (p.gamma != nullptr) {
-      float ss = a.x * a.x + a.y * a.y + b.x * b.x + b.y * b.y;
+  if (!is_q && !is_k) {  // v row: byte copy
+    if (live) {
+      *reinterpret_cast<uint4*>(dst) = ra;
+      *reinterpret_cast<uint4*>(dst + HALF) = rb;
+    }
+    return;
+  }
+  float a[VEC], b[VEC];
+  {
+    u64 pa[NP], pb[NP];
+    Chunk<T>::widen(ra, pa);
+    Chunk<T>::widen(rb, pb);
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-      const float rms = sqrtf(ss / (float)D + p.eps);
-      if (active) {
-        const float2 g1 = *reinterpret_cast<const float2*>(p.gamma + i0);
-        const float2 g2 = *reinterpret_cast<const float2*>(p.gamma + HALF + i0);
-        a.x = a.x / rms * g1.x;
-        a.y = a.y / rms * g1.y;
-        b.x = b.x / rms * g2.x;
-        b.y = b.y / rms * g2.y;
+    for (int e = 0; e < NP; ++e) {
+      unpack2(pa[e], a[2 * e], a[2 * e + 1]);
+      unpack2(pb[e], b[2 * e], b[2 * e + 1]);
+    }
+  }
+  if (p.gamma != nullptr) {
+    float ss = 0.f;
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) ss += a[e] * a[e] + b[e] * b[e];
+#pragma unroll
+    for (int o = LR / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    const float inv = 1.0f / sqrtf(ss / (float)D + p.eps);
+#pragma unroll
+    for (int e = 0; e < VEC; e += 4) {
+      const float4 g1 = __ldg(reinterpret_cast<const float4*>(p.gamma + l * VEC + e));
+      const float4 g2 = __ldg(reinterpret_cast<const float4*>(p.gamma + HALF + l * VEC + e));
+      a[e] *= inv * g1.x; a[e + 1] *= inv * g1.y; a[e + 2] *= inv * g1.z; a[e + 3] *= inv * g1.w;
+      b[e] *= inv * g2.x; b[e + 1] *= inv * g2.y; b[e + 2] *= inv * g2.z; b[e + 3] *= inv * g2.w;
+    }
+  }
+  if (p.cos_sin != nullptr) {
+    long long pos = p.pos_is_i64 ? reinterpret_cast<const long long*>(p.positions)[t]
+                                 : (long long)reinterpret_cast<const int*>(p.positions)[t];
+    pos = pos < 0 ? 0 : (pos >= p.max_position ? p.max_position - 1 : pos);
+    const float* cs = p.cos_sin + pos * D + l * VEC;
+#pragma unroll
+    for (int e = 0; e < VEC; e += 4) {
+      const float4 c = __ldg(reinterpret_cast<const float4*>(cs + e));
+      const float4 s = __ldg(reinterpret_cast<const float4*>(cs + HALF + e));
+      const float cc[4] = {c.x, c.y, c.z, c.w}, sn[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float x1 = a[e + u], x2 = b[e + u];
+        a[e + u] = x1 * cc[u] - x2 * sn[u];
+        b[e + u] = x1 * sn[u] + x2 * cc[u];
       }
     }
-    if (p.cos_sin != nullptr && active) {
-      long long pos = p.pos_is_i64 ? reinterpret_cast<const long long*>(p.positions)[t]
-                                   : (long long)reinterpret_cast<const int*>(p.positions)[t];
-      pos = pos < 0 ? 0 : (pos >= p.max_position ? p.max_position - 1 : pos);
-      const float2 c = *reinterpret_cast<const float2*>(p.cos_sin + pos * D + i0);
-      const float2 s = *reinterpret_cast<const float2*>(p.cos_sin + pos * D + HALF + i0);
-      const float2 x1 = a, x2 = b;
-      a.x = x1.x * c.x - x2.x * s.x;
-      a.y = x1.y * c.y - x2.y * s.y;
-      b.x = x1.x * s.x + x2.x * c.x;
-      b.y = x1.y * s.y + x2.y * c.y;
-    }
   }
-  if (active) {
-    Pair<T>::st(dst + i0, a);
-    Pair<T>::st(dst + HALF + i0, b);
+  if (live) {
+#pragma unroll
+    for (int e = 0; e < VEC; e += 4) {
+      store4<T>(dst + e, a[e], a[e + 1], a[e + 2], a[e + 3]);
+      store4<T>(dst + HALF + e, b[e], b[e + 1], b[e + 2], b[e + 3]);
+    }
   }
 }
 
 template <typename T>
 static int launch_pre_t(const PreAttnParams& p, int head_dim, cudaStream_t s) {
   const long long rows = p.num_tokens * (p.H + 2 * p.KVH);
-  const unsigned blocks = (unsigned)((rows + 7) / 8);
+  const int rw = 32 / ((head_dim / 2) / Chunk<T>::VEC);  // rows per warp
+  const unsigned blocks = (unsigned)((rows + 8 * rw - 1) / (8 * rw));
   switch (head_dim) {
     case 64: qk_norm_rope_store_kernel<T, 64><<<blocks, 256, 0, s>>>(p); break;
     case 128: qk_norm_rope_store_kernel<T, 128><<<blocks, 256, 0, s>>>(p); break;
@@ -174,7 +182,7 @@ extern "C" int mvl_qk_norm_rope_store(void* q_out, const void* q, const void* k,
                          (uintptr_t)v_cache | (uintptr_t)gamma | (uintptr_t)cos_sin_cache |
                          (uintptr_t)(q_token_stride * es) | (uintptr_t)(k_token_stride * es) |
                          (uintptr_t)(v_token_stride * es);
-  if (bits & 7u) return -4;                                             // MVL_ERR_ALIGNMENT (8-byte lanes)
+  if (bits & 15u) return -4;                                            // MVL_ERR_ALIGNMENT (16-byte lanes)
   mvl::PreAttnParams p;
   p.q_out = q_out; p.q = q; p.k = k; p.v = v;
   p.q_stride = q_token_stride; p.k_stride = k_token_stride; p.v_stride = v_token_stride;
