@@ -47,6 +47,9 @@ def parse_args():
                     help="c1..c5: one attention call per step; c2e: 28-layer engine-shaped decode "
                          "loop of config 2 under CUDA-graph replay")
     ap.add_argument("--eager", action="store_true", help="c2e: no CUDA graphs")
+    ap.add_argument("--cuda-cores", action="store_true",
+                    help="16-bit caches: packed-fp32 FFMA2 kernel instead of the tensor-core one "
+                         "(MVL_DECODE_CUDA_CORES)")
     ap.add_argument("--tma", action="store_true",
                     help="fetch K/V tiles with tensor-map TMA instead of cp.async (MVL_DECODE_LOAD_TMA)")
     ap.add_argument("--unfused", action="store_true",
@@ -232,10 +235,10 @@ def run_ours(args, rank, world, local_rank):
     dec_args = (w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"], w["H"],
                 w["KVH"], w["D"], w["BS"])
     lib = _ext.lib()
-    tma = _ext.DECODE_LOAD_TMA if args.tma else 0
+    tma = (_ext.DECODE_LOAD_TMA if args.tma else 0) | (_ext.DECODE_CUDA_CORES if args.cuda_cores else 0)
     if tma:
         from minivllm_b200.layers import attention as att_mod
-        att_mod.DEFAULT_DECODE_FLAGS |= _ext.DECODE_LOAD_TMA
+        att_mod.DEFAULT_DECODE_FLAGS |= tma
     code = {"f32": 0, "f16": 1, "bf16": 2}[sp.dtype]
     chunk = args.chunk or lib.mvl_paged_decode_default_chunk(B, w["H"], w["KVH"], w["D"],
                                                              t.tables.shape[1], w["BS"], code)
@@ -381,6 +384,8 @@ def run_ours(args, rank, world, local_rank):
                    "parallelism": f"kv-head-shard x{world}" if args.shard_of == 1 else
                    f"rank 0's shard of a {args.shard_of}-way head split, alone on one GPU",
                    "gather": gather_kind, "kv_load": "tensor-map TMA" if args.tma else "cp.async",
+                   "math": "FFMA2 (CUDA cores)" if (args.cuda_cores or args.tma or sp.dtype == "f32")
+                   else "mma.sync m16n8k16 (tensor cores)",
                    "l2": "inputs larger than L2 (KV bytes per step >> 126 MB); no flush needed"
                          if alg_unique > 4 * 126e6 else "KV fits in L2: number is L2-assisted"},
         "hbm_gbs_step": alg_unique / (ms_step * 1e-3) / 1e9,

@@ -62,6 +62,13 @@ typedef enum mvl_dtype {
                                   Used when block_size is a multiple of the 16-row (bf16/fp16,
                                   head_dim 128) warp tile; otherwise the cp.async path runs. */
 
+#define MVL_DECODE_CUDA_CORES 16u /* 16-bit caches run their score and P.V products on the tensor
+                                     cores by default (mma.sync m16n8k16, fp32 accumulate, p carried
+                                     as a 16-bit value plus a 16-bit correction; see DESIGN.md for why
+                                     this departs from "no tensor cores").  This flag selects the
+                                     packed-fp32 (FFMA2) CUDA-core kernel instead; fp32 caches always
+                                     use it. */
+
 /* Library / ABI identification.  No reference counterpart (the reference has no native layer). */
 int mvl_abi_version(void);
 

@@ -80,7 +80,7 @@ constexpr int kMaxChunk = 4096;
 
 // Shape checks shared by the planning entry points and mvl_paged_decode.
 int make_plan(long long batch, int H, int KVH, int D, long long max_num_blocks, int block_size,
-              int dtype, int chunk_req, int num_sms, Plan* pl) {
+              int dtype, int chunk_req, int num_sms, Plan* pl, bool mma = false) {
   if (elem_size(dtype) == 0) return MVL_ERR_DTYPE;
   if (batch < 0 || H <= 0 || KVH <= 0 || H % KVH != 0 || max_num_blocks <= 0) return MVL_ERR_SHAPE;
   if (D != 64 && D != 128) return MVL_ERR_SHAPE;
@@ -89,9 +89,9 @@ int make_plan(long long batch, int H, int KVH, int D, long long max_num_blocks, 
   const long long max_ctx = max_num_blocks * (long long)block_size;
   if (max_ctx >= (1ll << 31) || batch > 65535) return MVL_ERR_LIMIT;
   const int G = H / KVH;
-  pl->gt = pick_gt(G);
+  pl->gt = mma ? 8 : pick_gt(G);  // the tensor-core kernel always carries 8 heads (N of the MMA)
   pl->n_gt = (G + pl->gt - 1) / pl->gt;
-  pl->tr = tile_rows(dtype, D, pl->gt);
+  pl->tr = mma ? 16 : tile_rows(dtype, D, pl->gt);
   if (pl->tr <= 0) return MVL_ERR_SHAPE;
   pl->bs_shift = bs_shift;
   pl->max_ctx = max_ctx;
@@ -257,7 +257,14 @@ size_t mvl_paged_decode_workspace_bytes(int64_t batch, int num_heads, int num_kv
   if (make_plan(batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, elem_dtype,
                 chunk_tokens, sms, &pl) != MVL_OK)
     return 0;
-  return plan_workspace(pl, batch, num_heads, head_dim);
+  size_t need = plan_workspace(pl, batch, num_heads, head_dim);
+  if (elem_size(elem_dtype) == 2 &&  // the tensor-core path may split differently: cover both
+      make_plan(batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, elem_dtype,
+                chunk_tokens, sms, &pl, true) == MVL_OK) {
+    const size_t alt = plan_workspace(pl, batch, num_heads, head_dim);
+    if (alt > need) need = alt;
+  }
+  return need;
 }
 
 static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, int h_out, int head_off,
@@ -271,9 +278,11 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
   int sms = 0;
   int st = current_sm_count(&sms);
   if (st != MVL_OK) return st;
+  const bool mma = !(flags & MVL_DECODE_CUDA_CORES) && !(flags & MVL_DECODE_LOAD_TMA) &&
+                   elem_size(elem_dtype) == 2;
   Plan pl;
   st = make_plan(batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, elem_dtype,
-                 chunk_tokens, sms, &pl);
+                 chunk_tokens, sms, &pl, mma);
   if (st != MVL_OK) return st;
   if (batch == 0) return MVL_OK;
   if (num_blocks <= 0 || block_table_stride < max_num_blocks) return MVL_ERR_SHAPE;
@@ -354,6 +363,10 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
         use_maps = maps;
     }
     int e = -1000;
+    if (mma) {
+      e = elem_dtype == MVL_DTYPE_F16 ? mvl::launch_decode_split_mma<__half>(p, head_dim, grid, s)
+                                      : mvl::launch_decode_split_mma<__nv_bfloat16>(p, head_dim, grid, s);
+    } else
     switch (elem_dtype) {
       case MVL_DTYPE_F32: e = mvl::launch_decode_split<float>(p, use_maps, head_dim, pl.gt, grid, s); break;
       case MVL_DTYPE_F16: e = mvl::launch_decode_split<__half>(p, use_maps, head_dim, pl.gt, grid, s); break;

@@ -17,6 +17,9 @@ int launch_store_kvcache(const void* key, const void* value, void* k_cache, void
 template <typename T>
 int launch_decode_split(const DecodeParams& p, const CUtensorMap* maps, int head_dim, int gt, dim3 grid,
                         cudaStream_t s);
+// Tensor-core variant (16-bit element types only): 8 heads per CTA, 16-token warp tiles.
+template <typename T>
+int launch_decode_split_mma(const DecodeParams& p, int head_dim, dim3 grid, cudaStream_t s);
 template <typename T>
 int launch_decode_combine(const DecodeParams& p, int head_dim, long long rows, cudaStream_t s);
 // Rows of one warp tile for (T, head_dim, gt): the chunk must be a multiple of 4 warps x this.

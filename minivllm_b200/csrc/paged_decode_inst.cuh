@@ -2,6 +2,7 @@
 #include <mutex>
 
 #include "host.h"
+#include "paged_decode_mma.cuh"
 
 namespace mvl {
 
@@ -56,6 +57,37 @@ int launch_decode_split<MVL_T>(const DecodeParams& p, const CUtensorMap* maps, i
   }
   return -1000;
 }
+
+#ifdef MVL_T_IS_16BIT
+template <typename T, int D, bool UNIFORM>
+static int launch_mma_u(const DecodeParams& p, dim3 grid, cudaStream_t s) {
+  using C = MmaCfg<T, D>;
+  auto kern = paged_decode_split_mma_kernel<T, D, UNIFORM>;
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev >= 64 || !configured[dev]) {
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 64) configured[dev] = true;
+  }
+  kern<<<grid, C::NW * 32, C::SMEM, s>>>(p);
+  return (int)cudaGetLastError();
+}
+
+template <>
+int launch_decode_split_mma<MVL_T>(const DecodeParams& p, int head_dim, dim3 grid, cudaStream_t s) {
+  const bool uniform = ((1 << p.bs_shift) % 16) == 0;
+  switch (head_dim) {
+    case 64:
+      return uniform ? launch_mma_u<MVL_T, 64, true>(p, grid, s) : launch_mma_u<MVL_T, 64, false>(p, grid, s);
+    case 128:
+      return uniform ? launch_mma_u<MVL_T, 128, true>(p, grid, s) : launch_mma_u<MVL_T, 128, false>(p, grid, s);
+  }
+  return -1000;
+}
+#endif
 
 template <>
 int launch_decode_combine<MVL_T>(const DecodeParams& p, int head_dim, long long rows,

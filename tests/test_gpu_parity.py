@@ -351,7 +351,7 @@ def test_tma_load_path_matches_cp_async_bitwise(cuda_device, name):
     bit for bit to the cp.async path (and so inherit its parity with the reference)."""
     from minivllm_b200 import _ext
     inp = _dev(make_inputs(name), cuda_device)
-    base = _run(inp, flags=_ext.DECODE_FUSED_COMBINE)
+    base = _run(inp, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_CUDA_CORES)
     tma = _run(inp, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_LOAD_TMA)
     assert torch.equal(base, tma)
     tma2 = _run(inp, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_LOAD_TMA, chunk_tokens=64)
@@ -374,3 +374,71 @@ def test_tma_load_path_ignores_garbage_past_the_end(cuda_device):
     clean = _dev(inp, cuda_device)
     for flags in (_ext.DECODE_FUSED_COMBINE, _ext.DECODE_FUSED_COMBINE | _ext.DECODE_LOAD_TMA):
         assert torch.equal(_run(poisoned, flags=flags), _run(clean, flags=flags))
+
+
+# ------------------------------------------------------------------ tensor-core kernel (default for 16-bit caches)
+def _mma_flags():
+    from minivllm_b200 import _ext
+    return _ext.DECODE_FUSED_COMBINE  # tensor cores are the default for 16-bit caches
+
+
+def _ffma_flags():
+    from minivllm_b200 import _ext
+    return _ext.DECODE_FUSED_COMBINE | _ext.DECODE_CUDA_CORES
+
+
+@pytest.mark.parametrize("name", sorted(n for n in CASES if CASES[n]["dtype"] != "f32"))
+@pytest.mark.parametrize("chunk", [0, 64, 100000])
+def test_mma_variant_matches_reference_and_oracle(cuda_device, name, chunk):
+    inp = make_inputs(name)
+    z = np.load(os.path.join(GOLD, name + ".npz"))
+    out = _run(_dev(inp, cuda_device), flags=_mma_flags(), chunk_tokens=chunk)
+    got = out.float().cpu().numpy()
+    assert np.abs(got - z["ref_out"]).max() <= 2e-2          # reference run in bf16/fp16
+    _assert_close(got, z["ref_out_f32"], inp["q"].dtype)     # same bound as the FFMA2 kernel
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("H,KVH", [(4, 4), (8, 4), (32, 8), (16, 2), (10, 2), (32, 2), (6, 2)])
+@pytest.mark.parametrize("D,BS", [(128, 16), (64, 16), (128, 256), (64, 8), (128, 4)])
+def test_mma_variant_random_ragged(cuda_device, dtype, H, KVH, D, BS):
+    inp = _random_case(2000 + H * 7 + KVH + D + BS, dtype, H, KVH, D, BS, B=5, max_ctx=600)
+    want = _oracle(inp).numpy()
+    got = _run(_dev(inp, cuda_device), flags=_mma_flags()).float().cpu().numpy()
+    assert np.isfinite(got).all()
+    _assert_close(got, want, dtype)
+
+
+def test_mma_variant_fused_step_and_fp32_fallback(cuda_device):
+    from minivllm_b200.layers.attention import decode_step
+    inp = make_inputs("ragged_bf16")
+    B, KVH, D, BS = inp["q"].shape[0], inp["KVH"], inp["D"], inp["BS"]
+    g = torch.Generator().manual_seed(5)
+    k = torch.randn(B, KVH, D, generator=g).to(torch.bfloat16)
+    v = torch.randn(B, KVH, D, generator=g).to(torch.bfloat16)
+    last = inp["context_lens"].long() - 1
+    slots = inp["block_tables"][torch.arange(B), last // BS].long() * BS + last % BS
+    dev = _dev(inp, cuda_device)
+    kc, vc = dev["k_cache"].clone(), dev["v_cache"].clone()
+    out = decode_step(dev["q"], k.to(cuda_device), v.to(cuda_device), kc, vc, slots.to(cuda_device),
+                      dev["block_tables"], dev["context_lens"], inp["scale"], inp["H"], KVH, D, BS,
+                      flags=_mma_flags())
+    okc, ovc = inp["k_cache"].clone(), inp["v_cache"].clone()
+    po.store_kvcache_oracle(k, v, okc, ovc, slots)
+    assert torch.equal(kc.cpu().view(torch.uint8), okc.view(torch.uint8))
+    want = c_oracle.paged_decode(inp["q"], okc, ovc, inp["block_tables"], inp["context_lens"],
+                                 inp["scale"], inp["H"], KVH, D, BS)
+    _assert_close(out.float().cpu().numpy(), want.numpy(), torch.bfloat16)
+    # fp32 caches have no 16-bit MMA: they always run the FFMA2 kernel, flag or not
+    f32 = _dev(make_inputs("ragged_g4"), cuda_device)
+    assert torch.equal(_run(f32, flags=_ffma_flags()), _run(f32))
+
+
+@pytest.mark.parametrize("name", sorted(n for n in CASES if CASES[n]["dtype"] != "f32"))
+def test_cuda_core_kernel_still_selectable_for_16bit(cuda_device, name):
+    """MVL_DECODE_CUDA_CORES: the FFMA2 kernel on 16-bit caches, same bound."""
+    inp = make_inputs(name)
+    z = np.load(os.path.join(GOLD, name + ".npz"))
+    got = _run(_dev(inp, cuda_device), flags=_ffma_flags()).float().cpu().numpy()
+    assert np.abs(got - z["ref_out"]).max() <= 2e-2
+    _assert_close(got, z["ref_out_f32"], inp["q"].dtype)
