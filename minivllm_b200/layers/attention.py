@@ -339,17 +339,31 @@ class HostDecodeStep:
         dt = k_cache.dtype
         self.code = _DTYPES[dt]
 
-        def pair(shape, dtype):
-            return (torch.empty(shape, dtype=dtype, pin_memory=True),
-                    torch.empty(shape, dtype=dtype, device=dev))
+        # The six input arrays live back to back in ONE pinned arena and ONE device arena, so the
+        # library moves a step's inputs with a single host-to-device copy.
+        es = k_cache.element_size()
+        isz = 8 if index_dtype == torch.int64 else 4
+        sizes = [batch * num_heads * self.head_dim * es, batch * self.num_kv_heads * self.head_dim * es,
+                 batch * self.num_kv_heads * self.head_dim * es, batch * isz, batch * isz,
+                 batch * max_num_blocks * 4]
+        total = sum(sizes)
+        self._h_arena = torch.empty(total, dtype=torch.uint8, pin_memory=True)
+        self._d_arena = torch.empty(total, dtype=torch.uint8, device=dev)
 
-        self.q_h, self.q_d = pair((batch, num_heads, self.head_dim), dt)
-        self.k_h, self.k_d = pair((batch, self.num_kv_heads, self.head_dim), dt)
-        self.v_h, self.v_d = pair((batch, self.num_kv_heads, self.head_dim), dt)
-        self.slot_h, self.slot_d = pair((batch,), index_dtype)
-        self.ctx_h, self.ctx_d = pair((batch,), index_dtype)
-        self.bt_h, self.bt_d = pair((batch, max_num_blocks), torch.int32)
-        self.out_h, self.out_d = pair((batch, num_heads, self.head_dim), dt)
+        def views(arena):
+            out, at = [], 0
+            shapes = [((batch, num_heads, self.head_dim), dt), ((batch, self.num_kv_heads, self.head_dim), dt),
+                      ((batch, self.num_kv_heads, self.head_dim), dt), ((batch,), index_dtype),
+                      ((batch,), index_dtype), ((batch, max_num_blocks), torch.int32)]
+            for n, (shape, dtype) in zip(sizes, shapes):
+                out.append(arena[at:at + n].view(dtype).view(shape))
+                at += n
+            return out
+
+        self.q_h, self.k_h, self.v_h, self.slot_h, self.ctx_h, self.bt_h = views(self._h_arena)
+        self.q_d, self.k_d, self.v_d, self.slot_d, self.ctx_d, self.bt_d = views(self._d_arena)
+        self.out_h = torch.empty((batch, num_heads, self.head_dim), dtype=dt, pin_memory=True)
+        self.out_d = torch.empty((batch, num_heads, self.head_dim), dtype=dt, device=dev)
         with torch.cuda.device(dev):
             nbytes = _ext.lib().mvl_paged_decode_workspace_bytes(
                 batch, num_heads, self.num_kv_heads, self.head_dim, max_num_blocks, self.block_size,

@@ -442,3 +442,34 @@ def test_cuda_core_kernel_still_selectable_for_16bit(cuda_device, name):
     got = _run(_dev(inp, cuda_device), flags=_ffma_flags()).float().cpu().numpy()
     assert np.abs(got - z["ref_out"]).max() <= 2e-2
     _assert_close(got, z["ref_out_f32"], inp["q"].dtype)
+
+
+# ------------------------------------------------------------------ host-buffer step (e2e path)
+@pytest.mark.parametrize("idx", [torch.int64, torch.int32])
+def test_host_decode_step_matches_device_path(cuda_device, idx):
+    """mvl_decode_step_host (pinned H2D of the step's inputs, fused store + decode, D2H) against the
+    device-resident fused step on the same inputs; two steps in a row reuse every buffer."""
+    from minivllm_b200.layers.attention import HostDecodeStep, decode_step
+    inp = make_inputs("ragged_bf16")
+    B, H, KVH, D, BS = inp["q"].shape[0], inp["H"], inp["KVH"], inp["D"], inp["BS"]
+    kc = inp["k_cache"].to(cuda_device)
+    vc = inp["v_cache"].to(cuda_device)
+    kc2, vc2 = kc.clone(), vc.clone()
+    hs = HostDecodeStep(kc, vc, B, inp["block_tables"].shape[1], H, inp["scale"], index_dtype=idx)
+    g = torch.Generator().manual_seed(8)
+    last = inp["context_lens"].long() - 1
+    slots = inp["block_tables"][torch.arange(B), last // BS].long() * BS + last % BS
+    for step in range(2):
+        q = torch.randn(B, H, D, generator=g).to(torch.bfloat16)
+        k = torch.randn(B, KVH, D, generator=g).to(torch.bfloat16)
+        v = torch.randn(B, KVH, D, generator=g).to(torch.bfloat16)
+        hs.q_h.copy_(q), hs.k_h.copy_(k), hs.v_h.copy_(v)
+        hs.slot_h.copy_(slots.to(idx)), hs.ctx_h.copy_(inp["context_lens"].to(idx))
+        hs.bt_h.copy_(inp["block_tables"])
+        got = hs().clone()
+        want = decode_step(q.to(cuda_device), k.to(cuda_device), v.to(cuda_device), kc2, vc2,
+                           slots.to(cuda_device, idx), inp["block_tables"].to(cuda_device),
+                           inp["context_lens"].to(cuda_device, idx), inp["scale"], H, KVH, D, BS)
+        assert torch.equal(got, want.cpu())
+        assert torch.equal(kc, kc2) and torch.equal(vc, vc2)
+    assert hs.h2d_bytes == hs._h_arena.numel()
