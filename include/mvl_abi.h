@@ -159,6 +159,23 @@ int mvl_paged_decode_peers(void* const* out_peers, int num_peers, int total_head
                            size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream);
 
 /*
+ * mvl_flash_prefill — varlen causal GQA flash attention over the NEW tokens of each sequence.
+ * Replaces: flash_attention_prefill() + flash_attention_varlen_kernel, reference
+ * attention.py:212-280 and :111-209.
+ *   out[i, h, :] = softmax_{j <= i, j in i's sequence}( scale * <q[i,h,:], k[j,h/G,:]> ) @ v[j,h/G,:]
+ * q (T, H, D), k and v (T, KVH, D): head dims dense, token strides in elements; out (T, H, D)
+ * contiguous.  cu_seqlens (num_seqs + 1) int32 on the device delimits the packed sequences
+ * (attention.py:136-138); max_seqlen >= the longest one sizes the grid (the reference reads it
+ * back from the device each call, :263-264; the engine already has it, model_runner.py:219).
+ * 16-bit element types only (tensor-core path); MVL_ERR_DTYPE for fp32.  Like the reference it
+ * attends over the new tokens only, not over cached-prefix pages.
+ */
+int mvl_flash_prefill(void* out, const void* q, const void* k, const void* v, int64_t q_token_stride,
+                      int64_t k_token_stride, int64_t v_token_stride, const int32_t* cu_seqlens,
+                      int num_seqs, int max_seqlen, int num_heads, int num_kv_heads, int head_dim,
+                      float scale, int elem_dtype, void* stream);
+
+/*
  * mvl_qk_norm_rope_store — q/k RMSNorm + rotary embedding + KV-cache write in one pass over the
  * projections' output.  Replaces, per layer, reference models/qwen3.py:104-108 (rms_norm on q and k,
  * layers/layernorm.py:13-15: x / sqrt(mean(x^2) + eps) * gamma; rotary_emb, layers/

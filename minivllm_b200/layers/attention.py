@@ -7,8 +7,8 @@ programs, these functions pass raw device pointers to the C ABI (include/mvl_abi
 current stream.  Nothing here computes on the CPU and nothing falls back: non-CUDA tensors and a
 missing library are errors.
 
-Prefill (reference ``flash_attention_prefill``, :212-280) is outside this path (SURVEY.md §8(f)
-row N3); ``Attention.forward`` raises NotImplementedError for ``context.is_prefill``.
+``flash_attention_prefill`` (:212-280) is here too for 16-bit inputs, so
+``Attention.forward`` covers both branches of the reference.
 """
 from __future__ import annotations
 
@@ -218,6 +218,44 @@ def paged_attention_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: 
     return out
 
 
+def flash_attention_prefill(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens: torch.Tensor,
+                            scale: float, num_heads: int, num_kv_heads: int, head_dim: int,
+                            *, max_seqlen: Optional[int] = None) -> torch.Tensor:
+    """Causal attention over packed variable-length sequences (prefill), reference signature
+    (attention.py:212-221).  q (total_tokens, num_heads, head_dim); k, v (total_tokens,
+    num_kv_heads, head_dim); cu_seqlens (num_seqs + 1) cumulative lengths.  Returns a new
+    (total_tokens, num_heads, head_dim) tensor.  ``max_seqlen`` (keyword-only) sizes the grid
+    without reading ``cu_seqlens`` back; when omitted it is read from the device, as the
+    reference does (attention.py:263-264).  bf16 / fp16 only."""
+    dev = _need_cuda(q=q, k=k, v=v, cu_seqlens=cu_seqlens)
+    if q.dim() != 3 or k.dim() != 3 or v.shape != k.shape or q.shape[0] != k.shape[0]:
+        raise ValueError("q must be (T, H, D) and k, v (T, KVH, D)")
+    total, H, D = q.shape
+    if (H, D) != (num_heads, head_dim) or k.shape[1:] != (num_kv_heads, head_dim):
+        raise ValueError("tensor shapes do not match num_heads / num_kv_heads / head_dim")
+    if q.dtype not in (torch.bfloat16, torch.float16) or k.dtype != q.dtype or v.dtype != q.dtype:
+        raise NotImplementedError("prefill attention runs on the tensor cores: bf16 or fp16 inputs only")
+
+    def rows(x, heads):
+        dense = x.stride(2) == 1 and x.stride(1) == D and (total <= 1 or x.stride(0) >= heads * D)
+        x = x if dense else x.contiguous()
+        return x, (x.stride(0) if total > 1 else heads * D)
+
+    (q, qs), (k, ks), (v, vs) = rows(q, H), rows(k, num_kv_heads), rows(v, num_kv_heads)
+    cu = cu_seqlens.to(torch.int32).contiguous()
+    num_seqs = cu.numel() - 1
+    out = torch.empty((total, H, D), dtype=q.dtype, device=dev)
+    if total == 0 or num_seqs <= 0:
+        return out
+    if max_seqlen is None:
+        max_seqlen = int((cu[1:] - cu[:-1]).max())
+    with _on_device(dev):
+        _ext.check(_ext.lib().mvl_flash_prefill(
+            out.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(), qs, ks, vs, cu.data_ptr(), num_seqs,
+            int(max_seqlen), H, num_kv_heads, D, float(scale), _dtype_code(q), _stream_ptr(dev)))
+    return out
+
+
 def decode_step(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor,
                 v_cache: torch.Tensor, slot_mapping: torch.Tensor, block_tables: torch.Tensor,
                 context_lens: torch.Tensor, scale: float, num_heads: int, num_kv_heads: int,
@@ -290,10 +328,18 @@ class Attention(nn.Module):
         scale = self.scale / (self.head_dim ** 0.5)
 
         if context.is_prefill:
+            # reference attention.py:514-531: store, then causal attention over the new tokens
             if has_cache:
                 store_kvcache(k, v, k_cache, v_cache, context.slot_mapping, block_size)
-            raise NotImplementedError(
-                "prefill attention is outside the B200 decode path (SURVEY.md §8(f) N3)")
+            if q.dim() != 3:
+                raise NotImplementedError("batched (4-D) prefill: the reference calls an undefined "
+                                          "flash_attention_batched here (attention.py:528)")
+            if context.cu_seqlens_q is None:
+                raise ValueError("cu_seqlens_q must be provided for varlen attention")
+            o = flash_attention_prefill(q, k, v, context.cu_seqlens_q, scale, self.num_heads,
+                                        self.num_kv_heads, self.head_dim,
+                                        max_seqlen=context.max_seqlen_q or None)
+            return o.reshape(o.shape[0], self.num_heads * self.head_dim)
         if q.dim() == 4:  # (B, 1, H, D) -> (B, H, D)
             q = q.squeeze(1)
         one_token_each = (has_cache and k.shape[0] == q.shape[0]

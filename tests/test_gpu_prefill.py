@@ -1,0 +1,117 @@
+"""GPU (-m gpu): prefill attention (varlen causal GQA flash attention) against
+the reference's own PyTorch implementation (goldens) and the float64 oracle, and the prefill
+branch of Attention.forward (store, then attend; reference attention.py:498-525).
+
+Tolerances: 2e-2 abs against the reference run in the 16-bit dtype (north star); against the
+exact oracle |err| <= A + R |want| with (A, R) = (4e-3, 2^-7) for bf16 and (1e-3, 2^-10) for fp16:
+probabilities are rounded to the 16-bit type once before the P.V product (unit roundoff 2^-8 /
+2^-11 times the p-weighted mean of |v|, as in FlashAttention) plus the output rounding."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from cases_prefill import PREFILL_CASES, make_prefill_inputs
+from minivllm_b200 import reset_context, set_context
+from minivllm_b200.layers.attention import Attention, flash_attention_prefill
+from oracle import prefill_oracle
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _check(got, want):
+    a, r = (4e-3, 2.0 ** -7) if got.dtype == torch.bfloat16 else (1e-3, 2.0 ** -10)
+    got, want = got.double().cpu().numpy(), want.double().cpu().numpy()
+    excess = np.abs(got - want) - (a + r * np.abs(want))
+    assert np.isfinite(got).all() and excess.max() <= 0, f"max excess {excess.max():.3e}"
+
+
+@pytest.mark.parametrize("name", sorted(PREFILL_CASES))
+@pytest.mark.parametrize("pass_max", [True, False])
+def test_prefill_matches_reference_and_oracle(cuda_device, name, pass_max):
+    inp = make_prefill_inputs(name)
+    z = np.load(os.path.join(GOLD, f"prefill_{name}.npz"))
+    out = flash_attention_prefill(inp["q"].to(cuda_device), inp["k"].to(cuda_device), inp["v"].to(cuda_device),
+                                  inp["cu_seqlens"].to(cuda_device), inp["scale"], inp["H"], inp["KVH"], inp["D"],
+                                  max_seqlen=inp["max_seqlen"] if pass_max else None)
+    assert out.shape == inp["q"].shape and out.dtype == inp["q"].dtype
+    native = torch.from_numpy(z["ref_out_bits"]).view(inp["q"].dtype).float()
+    assert (out.float().cpu() - native).abs().max() <= 2e-2
+    want = prefill_oracle.causal_varlen_attention(inp["q"], inp["k"], inp["v"], inp["cu_seqlens"], inp["scale"],
+                                                  inp["H"], inp["KVH"], inp["D"])
+    _check(out, want)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("H,KVH,D", [(8, 8, 64), (8, 2, 128), (6, 2, 128), (16, 1, 64)])
+def test_prefill_random_ragged_and_strided(cuda_device, dtype, H, KVH, D):
+    g = torch.Generator().manual_seed(H * 100 + KVH * 10 + D)
+    lens = [int(x) for x in torch.randint(1, 300, (5,), generator=g)] + [64, 128, 1]
+    total = sum(lens)
+    qkv = torch.randn(total, (H + 2 * KVH) * D, generator=g).to(dtype)
+    q, k, v = qkv.split([H * D, KVH * D, KVH * D], dim=-1)       # strided views of a fused projection
+    q, k, v = q.view(total, H, D), k.view(total, KVH, D), v.view(total, KVH, D)
+    cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32)
+    dq = qkv.to(cuda_device)
+    a, b, c = dq.split([H * D, KVH * D, KVH * D], dim=-1)
+    out = flash_attention_prefill(a.view(total, H, D), b.view(total, KVH, D), c.view(total, KVH, D),
+                                  cu.to(cuda_device), 1.0 / D ** 0.5, H, KVH, D)
+    want = prefill_oracle.causal_varlen_attention(q, k, v, cu, 1.0 / D ** 0.5, H, KVH, D)
+    _check(out, want)
+    # the first token of every sequence attends to itself only: output == its v row
+    for s in cu[:-1].tolist():
+        assert torch.equal(out[s].cpu(), v[s].repeat_interleave(H // KVH, dim=0))
+
+
+def test_attention_forward_prefill_then_decode(cuda_device):
+    """Prefill two prompts through Attention.forward (store + causal attention), then one decode step
+    over the cache the prefill wrote: the engine's real sequence of calls."""
+    from oracle import c_oracle
+    H, KVH, D, BS = 8, 2, 128, 16
+    g = torch.Generator().manual_seed(9)
+    lens = [37, 64]
+    total = sum(lens)
+    q = torch.randn(total, H, D, generator=g).to(torch.bfloat16)
+    k = torch.randn(total, KVH, D, generator=g).to(torch.bfloat16)
+    v = torch.randn(total, KVH, D, generator=g).to(torch.bfloat16)
+    cu = torch.tensor([0, 37, 101], dtype=torch.int32)
+    tables = torch.tensor([[5, 2, 7, -1, -1], [0, 9, 3, 1, 8]], dtype=torch.int32)  # room for the decode token
+    slots = torch.cat([tables[b, torch.arange(n) // BS].long() * BS + torch.arange(n) % BS
+                       for b, n in enumerate(lens)])
+    layer = Attention(H, D, scale=1.0, num_kv_heads=KVH, block_size=BS)
+    layer.k_cache = torch.zeros(10, BS, KVH, D, dtype=torch.bfloat16, device=cuda_device)
+    layer.v_cache = torch.zeros_like(layer.k_cache)
+    set_context(True, cu_seqlens_q=cu.to(cuda_device), cu_seqlens_k=cu.to(cuda_device), max_seqlen_q=64,
+                max_seqlen_k=64, slot_mapping=slots.to(cuda_device))
+    try:
+        out = layer(q.to(cuda_device), k.to(cuda_device), v.to(cuda_device))
+    finally:
+        reset_context()
+    assert out.shape == (total, H * D)
+    want = prefill_oracle.causal_varlen_attention(q, k, v, cu, 1.0 / D ** 0.5, H, KVH, D)
+    _check(out.view(total, H, D), want)
+    flat_k = layer.k_cache.cpu().view(-1, KVH, D)
+    assert torch.equal(flat_k[slots], k)
+    # decode step on top of the prefilled cache
+    qd = torch.randn(2, H, D, generator=g).to(torch.bfloat16)
+    kd = torch.randn(2, KVH, D, generator=g).to(torch.bfloat16)
+    vd = torch.randn(2, KVH, D, generator=g).to(torch.bfloat16)
+    ctx = torch.tensor([38, 65])
+    dslots = tables[torch.arange(2), (ctx - 1) // BS].long() * BS + (ctx - 1) % BS
+    set_context(False, slot_mapping=dslots.to(cuda_device), context_lens=ctx.to(cuda_device),
+                block_tables=tables.to(cuda_device))
+    try:
+        od = layer(qd.to(cuda_device), kd.to(cuda_device), vd.to(cuda_device))
+    finally:
+        reset_context()
+    wd = c_oracle.paged_decode(qd, layer.k_cache.cpu(), layer.v_cache.cpu(), tables, ctx, 1.0 / D ** 0.5, H, KVH, D, BS)
+    err = (od.float().cpu().view(2, H, D) - wd).abs() - (1e-3 + 2.0 ** -8 * wd.abs())
+    assert err.max() <= 0
+
+
+def test_prefill_rejects_fp32(cuda_device):
+    q = torch.zeros(4, 2, 64, device=cuda_device)
+    with pytest.raises(NotImplementedError):
+        flash_attention_prefill(q, q, q, torch.tensor([0, 4], device=cuda_device), 1.0, 2, 2, 64)

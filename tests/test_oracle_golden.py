@@ -129,3 +129,22 @@ def test_pre_attention_oracle_matches_reference_modules(name):
     tol = 1e-5 if c["dtype"] == "f32" else 2e-2
     assert np.abs(qn.numpy() - z["q_ref"]).max() <= tol * max(1.0, np.abs(z["q_ref"]).max())
     assert np.abs(kn.numpy() - z["k_ref"]).max() <= tol * max(1.0, np.abs(z["k_ref"]).max())
+
+
+# ------------------------------------------------------------------ prefill attention (N3)
+from cases_prefill import PREFILL_CASES, make_prefill_inputs, prefill_digest  # noqa: E402
+from oracle import prefill_oracle  # noqa: E402
+
+
+@pytest.mark.parametrize("name", sorted(PREFILL_CASES))
+def test_prefill_oracle_matches_reference(name):
+    """oracle/prefill_oracle.py against the reference's pytorch_standard_attention
+    (benchmark_prefilling.py:9-52): 1e-5 vs its fp32 run, 2e-2 vs its run in the 16-bit dtype."""
+    z = np.load(os.path.join(GOLD, f"prefill_{name}.npz"))
+    inp = make_prefill_inputs(name)
+    assert prefill_digest(inp) == str(z["digest"])
+    got = prefill_oracle.causal_varlen_attention(inp["q"], inp["k"], inp["v"], inp["cu_seqlens"], inp["scale"],
+                                                 inp["H"], inp["KVH"], inp["D"]).numpy()
+    assert np.abs(got[::3] - z["ref_out_f32"]).max() <= 1e-5
+    native = torch.from_numpy(z["ref_out_bits"]).view(inp["q"].dtype).float().numpy()
+    assert np.abs(got - native).max() <= 2e-2
