@@ -111,13 +111,15 @@ int make_plan(long long batch, int H, int KVH, int D, long long max_num_blocks, 
     const double rate_sm = 44000.0;  // bytes per microsecond per SM
     const double t_est_us = units * (double)max_ctx * tok_bytes / (rate_sm * num_sms);
     const double life_us = sqrt(4.0 * t_est_us);
-    const double want = life_us * rate_sm / (3.0 * tok_bytes);
+    // The tensor-core kernel streams a chunk in less time, so its fixed costs weigh more: its
+    // measured optima (scripts/sweep_small.py, scripts/sweep_mma.sh) sit one step higher.
+    const double want = life_us * rate_sm / (3.0 * tok_bytes) * (mma ? 2.0 : 1.0);
     chunk = cta_rows;
     while (chunk * 2 <= kMaxChunk && (double)chunk * 1.41421356 < want) chunk *= 2;
     // Wave quantisation (scripts/sweep_small.py): a grid of one to two waves of resident CTAs runs
     // a nearly empty second wave; if half as many, twice as long CTAs still cover half a wave, take
     // those (B=1, ctx 16k: 25.9 -> 21.2 us; B=4, ctx 4k: 21.6 -> 19.0 us).
-    const double slots = 3.0 * num_sms;
+    const double slots = (mma ? 4.0 : 3.0) * num_sms;  // resident CTAs
     auto ctas = [&](long long c) { return units * (double)((max_ctx + c - 1) / c); };
     if (chunk * 2 <= kMaxChunk && ctas(chunk) <= 2.0 * slots && ctas(chunk * 2) >= 0.5 * slots) chunk *= 2;
   }
@@ -242,9 +244,9 @@ int mvl_paged_decode_default_chunk(int64_t batch, int num_heads, int num_kv_head
   int sms = 0;
   int st = current_sm_count(&sms);
   if (st != MVL_OK) return st;
-  Plan pl;
+  Plan pl;  // the plan of the default kernel: tensor cores for 16-bit caches
   st = make_plan(batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, elem_dtype, 0,
-                 sms, &pl);
+                 sms, &pl, elem_size(elem_dtype) == 2);
   return st != MVL_OK ? st : pl.chunk;
 }
 
