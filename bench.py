@@ -47,6 +47,9 @@ def parse_args():
                     help="c1..c5: one attention call per step; c2e: 28-layer engine-shaped decode "
                          "loop of config 2 under CUDA-graph replay")
     ap.add_argument("--eager", action="store_true", help="c2e: no CUDA graphs")
+    ap.add_argument("--share-prefix", choices=["auto", "on", "off"], default="auto",
+                    help="score sequences with aliased block-table prefixes together "
+                         "(MVL_DECODE_SHARE_PREFIX); auto = on for the shared-prefix workload c5")
     ap.add_argument("--cuda-cores", action="store_true",
                     help="16-bit caches: packed-fp32 FFMA2 kernel instead of the tensor-core one "
                          "(MVL_DECODE_CUDA_CORES)")
@@ -235,7 +238,9 @@ def run_ours(args, rank, world, local_rank):
     dec_args = (w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"], w["H"],
                 w["KVH"], w["D"], w["BS"])
     lib = _ext.lib()
-    tma = (_ext.DECODE_LOAD_TMA if args.tma else 0) | (_ext.DECODE_CUDA_CORES if args.cuda_cores else 0)
+    share = args.share_prefix == "on" or (args.share_prefix == "auto" and args.workload == "c5")
+    tma = ((_ext.DECODE_LOAD_TMA if args.tma else 0) | (_ext.DECODE_CUDA_CORES if args.cuda_cores else 0) |
+           (_ext.DECODE_SHARE_PREFIX if share else 0))
     if tma:
         from minivllm_b200.layers import attention as att_mod
         att_mod.DEFAULT_DECODE_FLAGS |= tma
@@ -383,7 +388,7 @@ def run_ours(args, rank, world, local_rank):
                    "context_range": [int(t.ctx.min()), int(t.ctx.max())], "chunk_tokens": int(chunk),
                    "parallelism": f"kv-head-shard x{world}" if args.shard_of == 1 else
                    f"rank 0's shard of a {args.shard_of}-way head split, alone on one GPU",
-                   "gather": gather_kind, "kv_load": "tensor-map TMA" if args.tma else "cp.async",
+                   "gather": gather_kind, "prefix_sharing": bool(share), "kv_load": "tensor-map TMA" if args.tma else "cp.async",
                    "math": "FFMA2 (CUDA cores)" if (args.cuda_cores or args.tma or sp.dtype == "f32")
                    else "mma.sync m16n8k16 (tensor cores)",
                    "l2": "inputs larger than L2 (KV bytes per step >> 126 MB); no flush needed"

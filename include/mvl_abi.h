@@ -69,6 +69,14 @@ typedef enum mvl_dtype {
                                      packed-fp32 (FFMA2) CUDA-core kernel instead; fp32 caches always
                                      use it. */
 
+#define MVL_DECODE_SHARE_PREFIX 32u /* sequences whose block tables start with the same entries
+                                       (prefix caching, reference block_manager.py:67-97) are found
+                                       by a device pre-pass (two small launches) and scored together
+                                       against ONE copy of the shared K/V pages: with G <= 4 query
+                                       heads per KV head the tensor-core tile's 8 columns hold 8/G
+                                       sequences.  Same results bit for bit.  Needs the tensor-core
+                                       kernel, G <= 4 and a workspace; ignored otherwise. */
+
 /* Library / ABI identification.  No reference counterpart (the reference has no native layer). */
 int mvl_abi_version(void);
 

@@ -132,15 +132,18 @@ int make_plan(long long batch, int H, int KVH, int D, long long max_num_blocks, 
   return MVL_OK;
 }
 
-// Workspace layout: [arrival counters, fixed kCounterBytes][part_o fp32][part_ml float2].
+// Workspace layout: [arrival counters, fixed kCounterBytes][share meta, 16 B x batch rounded to
+// 256][part_o fp32][part_ml float2].
 // The counter region has a fixed size and position so that it never overlaps another call's
 // partials, whatever the shapes: it only ever holds counters, which every call leaves at zero.
 constexpr size_t kCounterBytes = 256u << 10;  // 65536 counters
 
+size_t share_meta_bytes(long long batch) { return (((size_t)batch * 16 + 255) / 256) * 256; }
+
 size_t plan_workspace(const Plan& pl, long long batch, int H, int D) {
   if (pl.max_splits <= 1) return 0;
   const size_t rows = (size_t)batch * H * pl.max_splits;
-  return kCounterBytes + rows * D * sizeof(float) + rows * sizeof(float2);
+  return kCounterBytes + share_meta_bytes(batch) + rows * D * sizeof(float) + rows * sizeof(float2);
 }
 
 // ---- tensor maps for the TMA load path: [num_slots][KVH][D] with a [tile_rows][1][D] box
@@ -318,8 +321,9 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
   const size_t rows = (size_t)batch * num_heads * pl.max_splits;
   if (need) {
     char* base = reinterpret_cast<char*>(workspace);
-    p.part_o = reinterpret_cast<float*>(base + kCounterBytes);
-    p.part_ml = reinterpret_cast<float2*>(base + kCounterBytes + rows * head_dim * sizeof(float));
+    const size_t head_bytes = kCounterBytes + share_meta_bytes(batch);
+    p.part_o = reinterpret_cast<float*>(base + head_bytes);
+    p.part_ml = reinterpret_cast<float2*>(base + head_bytes + rows * head_dim * sizeof(float));
     const size_t n_counters = (size_t)batch * num_kv_heads * pl.n_gt;
     if ((flags & MVL_DECODE_FUSED_COMBINE) && n_counters * sizeof(int) <= kCounterBytes &&
         !(flags & (MVL_DECODE_SKIP_COMBINE | MVL_DECODE_ONLY_COMBINE)))
@@ -352,8 +356,23 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
   p.chunk = pl.chunk;
   p.max_splits = pl.max_splits;
   p.qscale = scale * 1.4426950408889634f;
+  p.gp_shift = 3;  // 8 columns = 8 heads of one sequence unless prefix sharing packs several
 
   cudaStream_t s = (cudaStream_t)stream;
+  // Prefix sharing: tensor-core kernel, fewer than 8 heads per KV head (spare columns), more than
+  // one sequence, and a workspace to hold the grouping.  Two tiny launches find the groups.
+  if ((flags & MVL_DECODE_SHARE_PREFIX) && mma && need && batch > 1 && p.G <= 4 &&
+      !(flags & MVL_DECODE_ONLY_COMBINE)) {
+    int gp = 1;
+    while (gp < p.G) gp <<= 1;
+    p.gp_shift = gp == 1 ? 0 : (gp == 2 ? 1 : 2);
+    int* meta = reinterpret_cast<int*>(reinterpret_cast<char*>(workspace) + kCounterBytes);
+    const int e = mvl::launch_prefix_share(block_tables, block_table_stride, context_lens, p.ctx_is_i64,
+                                           batch, pl.max_ctx, pl.bs_shift, pl.chunk, 8 / gp, meta, s);
+    if (e != 0) return cuda_fail((cudaError_t)e, "prefix_share launch");
+    p.share_meta = meta;
+  }
+
   if (!(flags & MVL_DECODE_ONLY_COMBINE)) {
     dim3 grid((unsigned)(num_kv_heads * pl.n_gt), (unsigned)batch, (unsigned)pl.max_splits);
     CUtensorMap maps[2];

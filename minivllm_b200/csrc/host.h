@@ -11,6 +11,11 @@ int launch_store_kvcache(const void* key, const void* value, void* k_cache, void
                          int chunks_per_row, long long key_stride16, long long value_stride16,
                          long long num_slots, int num_sms, cudaStream_t stream);
 
+// Prefix-sharing pre-pass (prefix_share.cu): fills meta[4*batch] = leader | gsize | gshare | lcpt.
+int launch_prefix_share(const int32_t* bt, long long bt_stride, const void* ctx, int ctx_is_i64,
+                        long long batch, long long max_ctx, int bs_shift, int chunk, int mm, int* meta,
+                        cudaStream_t s);
+
 // Launchers, one translation unit per element type (keeps nvcc parallel and fast).
 // Return cudaSuccess (0) or the cudaError_t of the failed call; -1000 if (D, GT) is not built.
 // maps: {K cache, V cache} tensor maps for the TMA load path, or nullptr for the cp.async path.

@@ -48,6 +48,12 @@ struct DecodeParams {
   // Optional fusion of the combine: per (sequence, head tile) arrival counters (zero before the
   // call, left zero after it); the last chunk's CTA to arrive merges the partials itself.
   int* counters;            // nullptr = separate combine kernel
+  // Optional prefix sharing (tensor-core kernel, G < 8): sequences whose block tables alias are
+  // grouped by a device pre-pass (prefix_share.cu); for chunks every member of a sub-group shares,
+  // the leader's CTA scores all members against ONE copy of the K/V tiles (the instruction's 8
+  // columns hold 8/Gp sequences x Gp heads).  meta = leader[B], gsize[B], gshare[B], lcpt[B].
+  const int* share_meta;    // nullptr = every sequence on its own
+  int gp_shift;             // log2(Gp), Gp = heads per sequence in the 8 columns (8 when not sharing)
   const void* q;
   const void* kc;
   const void* vc;

@@ -152,17 +152,36 @@ __global__ void __launch_bounds__(128, 4) paged_decode_split_mma_kernel(const De
     __syncthreads();
   }
 
+  // ---- prefix sharing: if every member of b's sub-group shares this whole chunk, the leader's
+  // CTA scores all of them (columns = member x head) and the other members' CTAs have nothing to do
+  int nmem = 1;
+  if (p.share_meta != nullptr) {
+    const int nb = gridDim.y;
+    const int lead = p.share_meta[b];
+    const int sz = p.share_meta[nb + lead];
+    if (sz > 1 && start + p.chunk <= p.share_meta[2 * nb + lead]) {
+      if (b != lead) return;
+      nmem = sz;
+    }
+  }
+  const int gp_mask = (1 << p.gp_shift) - 1;
+
   const uint32_t ring = smem_u32(smem) + warp * C::WARP_SMEM;
 
-  // ---- q as B fragments of the score product: n = head g, k = d.  Two registers per k-step.
+  // ---- q as B fragments of the score product: n = column g = (member, head), k = d.
   uint32_t qb[KS][2];
+  {
+    const int cm = g >> p.gp_shift, chd = g & gp_mask;  // this column's member and head
+    const bool col_ok = cm < nmem && chd < g_valid;
 #pragma unroll
-  for (int ks = 0; ks < KS; ++ks) {
-    qb[ks][0] = qb[ks][1] = 0u;
-    if (g < g_valid) {
-      const T* qrow = reinterpret_cast<const T*>(p.q) + ((long long)b * p.H + head0 + g) * D + ks * 16 + 2 * t;
-      qb[ks][0] = *reinterpret_cast<const uint32_t*>(qrow);
-      qb[ks][1] = *reinterpret_cast<const uint32_t*>(qrow + 8);
+    for (int ks = 0; ks < KS; ++ks) {
+      qb[ks][0] = qb[ks][1] = 0u;
+      if (col_ok) {
+        const T* qrow = reinterpret_cast<const T*>(p.q) + ((long long)(b + cm) * p.H + head0 + chd) * D +
+                        ks * 16 + 2 * t;
+        qb[ks][0] = *reinterpret_cast<const uint32_t*>(qrow);
+        qb[ks][1] = *reinterpret_cast<const uint32_t*>(qrow + 8);
+      }
     }
   }
 
@@ -325,60 +344,77 @@ __global__ void __launch_bounds__(128, 4) paged_decode_split_mma_kernel(const De
   }
   __syncthreads();
 
-  // ---- merge the warps; write the row (one chunk) or a partial; optionally combine (as FFMA2 kernel)
+  // ---- merge the warps; per column (member, head): write the row (one chunk) or a partial
   const uint32_t sbase = smem_u32(smem);
+  auto member_chunks = [&](int cm) -> int {  // number of chunks sequence b+cm really has
+    if (cm == 0) return n_act;
+    long long c = p.ctx_is_i64 ? reinterpret_cast<const long long*>(p.ctx)[b + cm]
+                               : (long long)reinterpret_cast<const int*>(p.ctx)[b + cm];
+    if (c > p.max_ctx) c = p.max_ctx;
+    return (int)((c + p.chunk - 1) / p.chunk);
+  };
   for (int item = threadIdx.x; item < GT * (D / 4); item += NW * 32) {
-    const int hd = item / (D / 4), dq = item % (D / 4);
-    if (hd >= g_valid) continue;
+    const int col = item / (D / 4), dq = item % (D / 4);
+    const int cm = col >> p.gp_shift, hd = col & gp_mask;
+    if (cm >= nmem || hd >= g_valid) continue;
     float Mx = -INFINITY;
 #pragma unroll
     for (int w = 0; w < NW; ++w)
-      Mx = fmaxf(Mx, __uint_as_float(lds32(sbase + w * C::WARP_SMEM + GT * D * 4 + hd * 8)));
+      Mx = fmaxf(Mx, __uint_as_float(lds32(sbase + w * C::WARP_SMEM + GT * D * 4 + col * 8)));
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, Lsum = 0.f;
 #pragma unroll
     for (int w = 0; w < NW; ++w) {
       const uint32_t wb = sbase + w * C::WARP_SMEM;
-      const uint2 ml = lds64(wb + GT * D * 4 + hd * 8);
+      const uint2 ml = lds64(wb + GT * D * 4 + col * 8);
       const float sw = fast_exp2(__uint_as_float(ml.x) - Mx);
       Lsum += sw * __uint_as_float(ml.y);
-      const uint4 v = lds128(wb + (hd * D + dq * 4) * 4);
+      const uint4 v = lds128(wb + (col * D + dq * 4) * 4);
       a0 += sw * __uint_as_float(v.x);
       a1 += sw * __uint_as_float(v.y);
       a2 += sw * __uint_as_float(v.z);
       a3 += sw * __uint_as_float(v.w);
     }
-    if (n_act == 1) {
+    if (member_chunks(cm) == 1) {
       const float inv = 1.f / Lsum;
-      store_out4<T, D>(p, b, head0 + hd, dq * 4, a0 * inv, a1 * inv, a2 * inv, a3 * inv);
+      store_out4<T, D>(p, b + cm, head0 + hd, dq * 4, a0 * inv, a1 * inv, a2 * inv, a3 * inv);
     } else {
-      const long long pi = ((long long)b * p.H + head0 + hd) * p.max_splits + split;
+      const long long pi = ((long long)(b + cm) * p.H + head0 + hd) * p.max_splits + split;
       *reinterpret_cast<float4*>(p.part_o + pi * D + dq * 4) = make_float4(a0, a1, a2, a3);
       if (dq == 0) p.part_ml[pi] = make_float2(Mx, Lsum);
     }
   }
-  if (n_act == 1 || p.counters == nullptr) return;
+  if (p.counters == nullptr) return;
+  if (nmem == 1 && n_act == 1) return;
 
+  // ---- fused combine, per member: the last of a sequence's chunk CTAs to arrive merges its partials
   const uint32_t flag = sbase + C::WARP_SMEM - 16;  // last bytes of warp 0's region (unused by the merge)
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
-    int* cnt = p.counters + (long long)b * gridDim.x + blockIdx.x;
-    const int prev = atomicAdd(cnt, 1);
-    const int last = (prev == n_act - 1);
-    if (last) {
-      *cnt = 0;
-      __threadfence();
+    uint32_t last_mask = 0;
+    for (int cm = 0; cm < nmem; ++cm) {
+      const int na = member_chunks(cm);
+      if (na == 1) continue;
+      int* cnt = p.counters + (long long)(b + cm) * gridDim.x + blockIdx.x;
+      if (atomicAdd(cnt, 1) == na - 1) {
+        *cnt = 0;
+        last_mask |= 1u << cm;
+      }
     }
-    sts32(flag, (uint32_t)last);
+    if (last_mask) __threadfence();
+    sts32(flag, last_mask);
   }
   __syncthreads();
-  if (lds32(flag) == 0) return;
+  const uint32_t last_mask = lds32(flag);
+  if (last_mask == 0) return;
   for (int item = threadIdx.x; item < GT * (D / 4); item += NW * 32) {
-    const int hd = item / (D / 4), dq = item % (D / 4);
-    if (hd >= g_valid) continue;
-    const long long pi0 = ((long long)b * p.H + head0 + hd) * p.max_splits;
+    const int col = item / (D / 4), dq = item % (D / 4);
+    const int cm = col >> p.gp_shift, hd = col & gp_mask;
+    if (cm >= nmem || hd >= g_valid || !((last_mask >> cm) & 1u)) continue;
+    const int na = member_chunks(cm);
+    const long long pi0 = ((long long)(b + cm) * p.H + head0 + hd) * p.max_splits;
     float Mx = -INFINITY, Lsum = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-    for (int sidx = 0; sidx < n_act; ++sidx) {
+    for (int sidx = 0; sidx < na; ++sidx) {
       const float2 ml = __ldcg(p.part_ml + pi0 + sidx);
       const float4 v = __ldcg(reinterpret_cast<const float4*>(p.part_o + (pi0 + sidx) * D + dq * 4));
       const float Mn = fmaxf(Mx, ml.x);
@@ -391,7 +427,7 @@ __global__ void __launch_bounds__(128, 4) paged_decode_split_mma_kernel(const De
       Mx = Mn;
     }
     const float inv = 1.f / Lsum;
-    store_out4<T, D>(p, b, head0 + hd, dq * 4, a0 * inv, a1 * inv, a2 * inv, a3 * inv);
+    store_out4<T, D>(p, b + cm, head0 + hd, dq * 4, a0 * inv, a1 * inv, a2 * inv, a3 * inv);
   }
 }
 

@@ -473,3 +473,81 @@ def test_host_decode_step_matches_device_path(cuda_device, idx):
         assert torch.equal(got, want.cpu())
         assert torch.equal(kc, kc2) and torch.equal(vc, vc2)
     assert hs.h2d_bytes == hs._h_arena.numel()
+
+
+# ------------------------------------------------------------------ prefix sharing (MVL_DECODE_SHARE_PREFIX)
+def _aliased_case(seed, dtype, H, KVH, D, BS, groups):
+    """groups: list of (shared_tokens, [context lengths]); members of a group alias the blocks of the
+    shared prefix (block aligned), each has private blocks after it."""
+    g = torch.Generator().manual_seed(seed)
+    rng = np.random.RandomState(seed)
+    ctx = [n for _, lens in groups for n in lens]
+    B = len(ctx)
+    nblk = [(n + BS - 1) // BS for n in ctx]
+    total = sum(nblk) + 4
+    perm = list(rng.permutation(total))
+    tables = np.full((B, max(nblk) + 1), -1, dtype=np.int32)
+    b = 0
+    for shared, lens in groups:
+        sb = shared // BS
+        shared_ids = [perm.pop() for _ in range(sb)]
+        for n in lens:
+            need = (n + BS - 1) // BS
+            assert need >= sb
+            tables[b, :sb] = shared_ids
+            tables[b, sb:need] = [perm.pop() for _ in range(need - sb)]
+            b += 1
+    return dict(q=torch.randn(B, H, D, generator=g).to(dtype),
+                k_cache=torch.randn(total, BS, KVH, D, generator=g).to(dtype),
+                v_cache=torch.randn(total, BS, KVH, D, generator=g).to(dtype),
+                block_tables=torch.from_numpy(tables), context_lens=torch.tensor(ctx, dtype=torch.int64),
+                scale=1.0 / D ** 0.5, H=H, KVH=KVH, D=D, BS=BS)
+
+
+@pytest.mark.parametrize("H,KVH,D", [(8, 2, 128), (4, 2, 128), (2, 2, 64), (6, 2, 128), (16, 2, 128)])
+@pytest.mark.parametrize("chunk", [64, 128, 0])
+def test_prefix_sharing_is_bit_identical(cuda_device, H, KVH, D, chunk):
+    """Sequences aliasing a prefix scored together (one copy of the K/V tiles) must give exactly the
+    bits of scoring each alone; groups of 1..5, shared lengths off the chunk grid, a member whose
+    whole context is the shared part plus one token, identical twins, and G = 8 (flag ignored)."""
+    from minivllm_b200 import _ext
+    groups = [(256, [300, 257, 700, 290, 512]), (0, [130]), (128, [129, 129]), (384, [385, 1000, 400]),
+              (64, [200]), (512, [600, 520])]
+    inp = _aliased_case(900 + H + D, torch.bfloat16, H, KVH, D, 16, groups)
+    dev = _dev(inp, cuda_device)
+    base = _run(dev, chunk_tokens=chunk, flags=_ext.DECODE_FUSED_COMBINE)
+    for flags in (_ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX, _ext.DECODE_SHARE_PREFIX):
+        for _ in range(2):  # twice: the arrival counters must come back to zero
+            got = _run(dev, chunk_tokens=chunk, flags=flags)
+            if flags & _ext.DECODE_FUSED_COMBINE:
+                assert torch.equal(got, base)
+            else:  # separate combine kernel merges in another order
+                assert (got.float() - base.float()).abs().max() <= 2e-2
+    _assert_close(base.float().cpu().numpy(), _oracle(inp).numpy(), torch.bfloat16)
+
+
+def test_prefix_sharing_golden_and_fused_step(cuda_device):
+    from minivllm_b200 import _ext
+    from minivllm_b200.layers.attention import decode_step
+    inp = make_inputs("aliased_bf16")   # 4 sequences sharing a 384-token prefix, G = 4
+    z = np.load(os.path.join(GOLD, "aliased_bf16.npz"))
+    flags = _ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX
+    for chunk in (64, 128, 0):
+        got = _run(_dev(inp, cuda_device), flags=flags, chunk_tokens=chunk).float().cpu().numpy()
+        assert np.abs(got - z["ref_out"]).max() <= 2e-2
+        _assert_close(got, z["ref_out_f32"], torch.bfloat16)
+    # fused store + sharing: the new token's page is private, its chunk is never scored jointly
+    B, KVH, D, BS = 4, inp["KVH"], inp["D"], inp["BS"]
+    g = torch.Generator().manual_seed(4)
+    k = torch.randn(B, KVH, D, generator=g).to(torch.bfloat16)
+    v = torch.randn(B, KVH, D, generator=g).to(torch.bfloat16)
+    last = inp["context_lens"].long() - 1
+    slots = inp["block_tables"][torch.arange(B), last // BS].long() * BS + last % BS
+    dev = _dev(inp, cuda_device)
+    outs = []
+    for fl in (_ext.DECODE_FUSED_COMBINE, flags):
+        kc, vc = dev["k_cache"].clone(), dev["v_cache"].clone()
+        outs.append(decode_step(dev["q"], k.to(cuda_device), v.to(cuda_device), kc, vc, slots.to(cuda_device),
+                                dev["block_tables"], dev["context_lens"], inp["scale"], inp["H"], KVH, D, BS,
+                                chunk_tokens=64, flags=fl))
+    assert torch.equal(outs[0], outs[1])
