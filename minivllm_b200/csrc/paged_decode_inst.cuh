@@ -59,10 +59,10 @@ int launch_decode_split<MVL_T>(const DecodeParams& p, const CUtensorMap* maps, i
 }
 
 #ifdef MVL_T_IS_16BIT
-template <typename T, int D, bool UNIFORM>
-static int launch_mma_u(const DecodeParams& p, dim3 grid, cudaStream_t s) {
-  using C = MmaCfg<T, D>;
-  auto kern = paged_decode_split_mma_kernel<T, D, UNIFORM>;
+template <typename T, int D, bool UNIFORM, int NT>
+static int launch_mma_nt(const DecodeParams& p, dim3 grid, cudaStream_t s) {
+  using C = MmaCfg<T, D, NT>;
+  auto kern = paged_decode_split_mma_kernel<T, D, UNIFORM, NT>;
   static bool configured[64] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -74,6 +74,14 @@ static int launch_mma_u(const DecodeParams& p, dim3 grid, cudaStream_t s) {
   }
   kern<<<grid, C::NW * 32, C::SMEM, s>>>(p);
   return (int)cudaGetLastError();
+}
+
+// One column tile (8 columns).  The kernel is written for NT column tiles; NT = 2 (16 columns, up
+// to 16/Gp sequences per CTA under prefix sharing) was measured on C5 and lost to NT = 1: 205
+// registers halve the occupancy (0.442 ms vs 0.420 ms), and batches without sharing pay 8 %.
+template <typename T, int D, bool UNIFORM>
+static int launch_mma_u(const DecodeParams& p, dim3 grid, cudaStream_t s) {
+  return launch_mma_nt<T, D, UNIFORM, 1>(p, grid, s);
 }
 
 template <>

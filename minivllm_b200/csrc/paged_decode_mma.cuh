@@ -85,8 +85,12 @@ __device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
   return d;
 }
 
-template <typename T, int D_>
+// NT = column tiles per CTA: 1 (8 columns) normally, 2 (16 columns) when prefix sharing packs up
+// to 16/Gp sequences into one CTA.
+template <typename T, int D_, int NT_ = 1>
 struct MmaCfg {
+  static constexpr int NT = NT_;
+  static constexpr int NC = 8 * NT_;           // columns = (sequence, head) pairs
   static constexpr int D = D_;
   static constexpr int GT = 8;                 // heads per CTA = N of the instruction
   static constexpr int NW = 4;
@@ -98,16 +102,17 @@ struct MmaCfg {
   static constexpr int TILEB = TR * ROWB;
   static constexpr int KS = D / 16;            // k-steps of the score product = m-tiles of P.V
   static constexpr int RING = 3;
-  static constexpr int MRG_BYTES = GT * D * 4 + GT * 8;  // merged [head][D] fp32 + (m,l)[head]
+  static constexpr int MRG_BYTES = NC * D * 4 + NC * 8;  // merged [column][D] fp32 + (m,l)[column]
   static constexpr int WARP_SMEM = (RING * TILEB > MRG_BYTES ? RING * TILEB : ((MRG_BYTES + 255) / 256) * 256);
   static constexpr int SMEM = NW * WARP_SMEM;
   static_assert(sizeof(T) == 2, "tensor-core path is for 16-bit caches");
   static_assert(CPRW >= 8 && CPRW <= 16, "head_dim 64 or 128");
 };
 
-template <typename T, int D, bool UNIFORM>
-__global__ void __launch_bounds__(128, 4) paged_decode_split_mma_kernel(const DecodeParams p) {
-  using C = MmaCfg<T, D>;
+template <typename T, int D, bool UNIFORM, int NT>
+__global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_kernel(const DecodeParams p) {
+  using C = MmaCfg<T, D, NT>;
+  constexpr int NC = C::NC;
   using M = MmaType<T>;
   constexpr int GT = C::GT, NW = C::NW, TR = C::TR, ROWB = C::ROWB, CPRW = C::CPRW, RPP = C::RPP,
                 R = C::R, TILEB = C::TILEB, KS = C::KS, RING = C::RING;
@@ -168,19 +173,20 @@ __global__ void __launch_bounds__(128, 4) paged_decode_split_mma_kernel(const De
 
   const uint32_t ring = smem_u32(smem) + warp * C::WARP_SMEM;
 
-  // ---- q as B fragments of the score product: n = column g = (member, head), k = d.
-  uint32_t qb[KS][2];
-  {
-    const int cm = g >> p.gp_shift, chd = g & gp_mask;  // this column's member and head
+  // ---- q as B fragments of the score product: n = column nt*8+g = (member, head), k = d.
+  uint32_t qb[NT][KS][2];
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt) {
+    const int col = nt * 8 + g, cm = col >> p.gp_shift, chd = col & gp_mask;  // member and head
     const bool col_ok = cm < nmem && chd < g_valid;
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks) {
-      qb[ks][0] = qb[ks][1] = 0u;
+      qb[nt][ks][0] = qb[nt][ks][1] = 0u;
       if (col_ok) {
         const T* qrow = reinterpret_cast<const T*>(p.q) + ((long long)(b + cm) * p.H + head0 + chd) * D +
                         ks * 16 + 2 * t;
-        qb[ks][0] = *reinterpret_cast<const uint32_t*>(qrow);
-        qb[ks][1] = *reinterpret_cast<const uint32_t*>(qrow + 8);
+        qb[nt][ks][0] = *reinterpret_cast<const uint32_t*>(qrow);
+        qb[nt][ks][1] = *reinterpret_cast<const uint32_t*>(qrow + 8);
       }
     }
   }
@@ -232,12 +238,19 @@ __global__ void __launch_bounds__(128, 4) paged_decode_split_mma_kernel(const De
 #pragma unroll 1
   for (int n = 0; n < RING - 1; ++n) issue(n, n);
 
-  // ---- state: O^T accumulators (d x heads), running max / sum of this thread's two heads
-  float o[KS][4];
+  // ---- state per column tile: O^T accumulators (d x 8 columns), running max / sum of this thread's
+  // two columns (2t, 2t+1), P^T B fragments
+  float o[NT][KS][4];
+  float m_a[NT], m_b[NT], l_a[NT], l_b[NT];
+  uint32_t pb_hi[NT][2], pb_lo[NT][2];
 #pragma unroll
-  for (int mt = 0; mt < KS; ++mt) o[mt][0] = o[mt][1] = o[mt][2] = o[mt][3] = 0.f;
-  float m_a = -INFINITY, m_b = -INFINITY, l_a = 0.f, l_b = 0.f;  // heads 2t and 2t+1
-  uint32_t pb_hi[2] = {0u, 0u}, pb_lo[2] = {0u, 0u};               // P^T B fragments (k = tokens)
+  for (int nt = 0; nt < NT; ++nt) {
+#pragma unroll
+    for (int mt = 0; mt < KS; ++mt) o[nt][mt][0] = o[nt][mt][1] = o[nt][mt][2] = o[nt][mt][3] = 0.f;
+    m_a[nt] = m_b[nt] = -INFINITY;
+    l_a[nt] = l_b[nt] = 0.f;
+    pb_hi[nt][0] = pb_hi[nt][1] = pb_lo[nt][0] = pb_lo[nt][1] = 0u;
+  }
 
   // ldmatrix lane addressing: matrix mi = lane/8, row lane%8
   const int mi = lane >> 3, mr = lane & 7;
@@ -256,91 +269,112 @@ __global__ void __launch_bounds__(128, 4) paged_decode_split_mma_kernel(const De
     if (!(n & 1)) {
       // ================================================================ scores S^T = K . Q^T
       const int tstart = start + (warp + (n >> 1) * NW) * TR;
-      float s[4] = {0.f, 0.f, 0.f, 0.f};
+      float s[NT][4];
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
 #pragma unroll
       for (int ks = 0; ks < KS; ++ks) {
         uint32_t a[4];
         ldmatrix_x4(a, tile + k_off + (((2 * ks + k_chk) ^ (k_tok & 7)) << 4));
-        M::mma(s, a, qb[ks][0], qb[ks][1]);
-      }
-      // s[0]: (token g, head 2t)  s[1]: (token g, head 2t+1)  s[2], s[3]: token g+8
 #pragma unroll
-      for (int i = 0; i < 4; ++i) s[i] *= p.qscale;
-      if (tstart + TR > end) {
-        if (tstart + g >= end) s[0] = s[1] = -INFINITY;
-        if (tstart + g + 8 >= end) s[2] = s[3] = -INFINITY;
+        for (int nt = 0; nt < NT; ++nt) M::mma(s[nt], a, qb[nt][ks][0], qb[nt][ks][1]);
       }
-      const bool need = fmaxf(s[0], s[2]) > m_a + 8.f || fmaxf(s[1], s[3]) > m_b + 8.f;
+      // s[.][0]: (token g, column 2t)  [1]: (token g, column 2t+1)  [2], [3]: token g+8
+      const bool cut = tstart + TR > end;
+      bool need = false;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) s[nt][i] *= p.qscale;
+        if (cut) {
+          if (tstart + g >= end) s[nt][0] = s[nt][1] = -INFINITY;
+          if (tstart + g + 8 >= end) s[nt][2] = s[nt][3] = -INFINITY;
+        }
+        need |= fmaxf(s[nt][0], s[nt][2]) > m_a[nt] + 8.f || fmaxf(s[nt][1], s[nt][3]) > m_b[nt] + 8.f;
+      }
       if (__any_sync(0xffffffffu, need)) {  // rare: refresh the running maxima, rescale the state
-        float xa = fmaxf(s[0], s[2]), xb = fmaxf(s[1], s[3]);
 #pragma unroll
-        for (int off = 4; off < 32; off <<= 1) {
-          xa = fmaxf(xa, __shfl_xor_sync(0xffffffffu, xa, off));
-          xb = fmaxf(xb, __shfl_xor_sync(0xffffffffu, xb, off));
-        }
-        const float na = fmaxf(m_a, xa), nb = fmaxf(m_b, xb);
-        const float fa = fast_exp2(m_a - na), fb = fast_exp2(m_b - nb);  // -inf -> 0
-        l_a *= fa;
-        l_b *= fb;
+        for (int nt = 0; nt < NT; ++nt) {
+          float xa = fmaxf(s[nt][0], s[nt][2]), xb = fmaxf(s[nt][1], s[nt][3]);
 #pragma unroll
-        for (int mt = 0; mt < KS; ++mt) {
-          o[mt][0] *= fa;
-          o[mt][2] *= fa;
-          o[mt][1] *= fb;
-          o[mt][3] *= fb;
+          for (int off = 4; off < 32; off <<= 1) {
+            xa = fmaxf(xa, __shfl_xor_sync(0xffffffffu, xa, off));
+            xb = fmaxf(xb, __shfl_xor_sync(0xffffffffu, xb, off));
+          }
+          const float na = fmaxf(m_a[nt], xa), nb = fmaxf(m_b[nt], xb);
+          const float fa = fast_exp2(m_a[nt] - na), fb = fast_exp2(m_b[nt] - nb);  // -inf -> 0
+          l_a[nt] *= fa;
+          l_b[nt] *= fb;
+#pragma unroll
+          for (int mt = 0; mt < KS; ++mt) {
+            o[nt][mt][0] *= fa;
+            o[nt][mt][2] *= fa;
+            o[nt][mt][1] *= fb;
+            o[nt][mt][3] *= fb;
+          }
+          m_a[nt] = na;
+          m_b[nt] = nb;
         }
-        m_a = na;
-        m_b = nb;
       }
-      float pr[4];
-      pr[0] = fast_exp2(s[0] - m_a);
-      pr[1] = fast_exp2(s[1] - m_b);
-      pr[2] = fast_exp2(s[2] - m_a);
-      pr[3] = fast_exp2(s[3] - m_b);
-      // split p into a 16-bit value and a 16-bit correction; sums use what the products will use
-      const uint32_t h0 = M::pack(pr[0], pr[1]), h1 = M::pack(pr[2], pr[3]);
-      const float r0 = pr[0] - M::lo_f(h0), r1 = pr[1] - M::hi_f(h0);
-      const float r2 = pr[2] - M::lo_f(h1), r3 = pr[3] - M::hi_f(h1);
-      const uint32_t c0 = M::pack(r0, r1), c1 = M::pack(r2, r3);
-      l_a += (M::lo_f(h0) + M::lo_f(c0)) + (M::lo_f(h1) + M::lo_f(c1));
-      l_b += (M::hi_f(h0) + M::hi_f(c0)) + (M::hi_f(h1) + M::hi_f(c1));
-      // (token, heads) 8x8 blocks -> (head, tokens): the B fragments of the P.V product
-      pb_hi[0] = movmatrix_trans(h0);
-      pb_hi[1] = movmatrix_trans(h1);
-      pb_lo[0] = movmatrix_trans(c0);
-      pb_lo[1] = movmatrix_trans(c1);
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        float pr[4];
+        pr[0] = fast_exp2(s[nt][0] - m_a[nt]);
+        pr[1] = fast_exp2(s[nt][1] - m_b[nt]);
+        pr[2] = fast_exp2(s[nt][2] - m_a[nt]);
+        pr[3] = fast_exp2(s[nt][3] - m_b[nt]);
+        // split p into a 16-bit value and a 16-bit correction; sums use what the products will use
+        const uint32_t h0 = M::pack(pr[0], pr[1]), h1 = M::pack(pr[2], pr[3]);
+        const float r0 = pr[0] - M::lo_f(h0), r1 = pr[1] - M::hi_f(h0);
+        const float r2 = pr[2] - M::lo_f(h1), r3 = pr[3] - M::hi_f(h1);
+        const uint32_t c0 = M::pack(r0, r1), c1 = M::pack(r2, r3);
+        l_a[nt] += (M::lo_f(h0) + M::lo_f(c0)) + (M::lo_f(h1) + M::lo_f(c1));
+        l_b[nt] += (M::hi_f(h0) + M::hi_f(c0)) + (M::hi_f(h1) + M::hi_f(c1));
+        // (token, columns) 8x8 blocks -> (column, tokens): the B fragments of the P.V product
+        pb_hi[nt][0] = movmatrix_trans(h0);
+        pb_hi[nt][1] = movmatrix_trans(h1);
+        pb_lo[nt][0] = movmatrix_trans(c0);
+        pb_lo[nt][1] = movmatrix_trans(c1);
+      }
     } else {
       // ================================================================ O^T += V^T . P^T
 #pragma unroll
       for (int mt = 0; mt < KS; ++mt) {
         uint32_t a[4];
         ldmatrix_x4_trans(a, tile + v_off + (((2 * mt + v_chk) ^ (v_tok & 7)) << 4));
-        M::mma(o[mt], a, pb_hi[0], pb_hi[1]);
-        M::mma(o[mt], a, pb_lo[0], pb_lo[1]);
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+          M::mma(o[nt][mt], a, pb_hi[nt][0], pb_hi[nt][1]);
+          M::mma(o[nt][mt], a, pb_lo[nt][0], pb_lo[nt][1]);
+        }
       }
     }
   }
   cp_async_wait<0>();
   __syncwarp();
 
-  // ---- warp state -> merge area (aliases the ring): o[head][D] fp32, then (m, l)[head]
+  // ---- warp state -> merge area (aliases the ring): o[column][D] fp32, then (m, l)[column]
+  const uint32_t mo = ring, mml = ring + NC * D * 4;
 #pragma unroll
-  for (int off = 4; off < 32; off <<= 1) {
-    l_a += __shfl_xor_sync(0xffffffffu, l_a, off);
-    l_b += __shfl_xor_sync(0xffffffffu, l_b, off);
-  }
-  const uint32_t mo = ring, mml = ring + GT * D * 4;
+  for (int nt = 0; nt < NT; ++nt) {
 #pragma unroll
-  for (int mt = 0; mt < KS; ++mt) {
-    // o[mt][0]: (d = 16mt+g, head 2t)  [1]: head 2t+1  [2],[3]: d + 8
-    sts32(mo + ((2 * t) * D + 16 * mt + g) * 4, __float_as_uint(o[mt][0]));
-    sts32(mo + ((2 * t + 1) * D + 16 * mt + g) * 4, __float_as_uint(o[mt][1]));
-    sts32(mo + ((2 * t) * D + 16 * mt + g + 8) * 4, __float_as_uint(o[mt][2]));
-    sts32(mo + ((2 * t + 1) * D + 16 * mt + g + 8) * 4, __float_as_uint(o[mt][3]));
-  }
-  if (g == 0) {
-    sts64(mml + (2 * t) * 8, make_uint2(__float_as_uint(m_a), __float_as_uint(l_a)));
-    sts64(mml + (2 * t + 1) * 8, make_uint2(__float_as_uint(m_b), __float_as_uint(l_b)));
+    for (int off = 4; off < 32; off <<= 1) {
+      l_a[nt] += __shfl_xor_sync(0xffffffffu, l_a[nt], off);
+      l_b[nt] += __shfl_xor_sync(0xffffffffu, l_b[nt], off);
+    }
+    const int ca = nt * 8 + 2 * t, cb = ca + 1;
+#pragma unroll
+    for (int mt = 0; mt < KS; ++mt) {
+      // o[nt][mt][0]: (d = 16mt+g, column 2t)  [1]: column 2t+1  [2],[3]: d + 8
+      sts32(mo + (ca * D + 16 * mt + g) * 4, __float_as_uint(o[nt][mt][0]));
+      sts32(mo + (cb * D + 16 * mt + g) * 4, __float_as_uint(o[nt][mt][1]));
+      sts32(mo + (ca * D + 16 * mt + g + 8) * 4, __float_as_uint(o[nt][mt][2]));
+      sts32(mo + (cb * D + 16 * mt + g + 8) * 4, __float_as_uint(o[nt][mt][3]));
+    }
+    if (g == 0) {
+      sts64(mml + ca * 8, make_uint2(__float_as_uint(m_a[nt]), __float_as_uint(l_a[nt])));
+      sts64(mml + cb * 8, make_uint2(__float_as_uint(m_b[nt]), __float_as_uint(l_b[nt])));
+    }
   }
   __syncthreads();
 
@@ -353,19 +387,19 @@ __global__ void __launch_bounds__(128, 4) paged_decode_split_mma_kernel(const De
     if (c > p.max_ctx) c = p.max_ctx;
     return (int)((c + p.chunk - 1) / p.chunk);
   };
-  for (int item = threadIdx.x; item < GT * (D / 4); item += NW * 32) {
+  for (int item = threadIdx.x; item < NC * (D / 4); item += NW * 32) {
     const int col = item / (D / 4), dq = item % (D / 4);
     const int cm = col >> p.gp_shift, hd = col & gp_mask;
     if (cm >= nmem || hd >= g_valid) continue;
     float Mx = -INFINITY;
 #pragma unroll
     for (int w = 0; w < NW; ++w)
-      Mx = fmaxf(Mx, __uint_as_float(lds32(sbase + w * C::WARP_SMEM + GT * D * 4 + col * 8)));
+      Mx = fmaxf(Mx, __uint_as_float(lds32(sbase + w * C::WARP_SMEM + NC * D * 4 + col * 8)));
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, Lsum = 0.f;
 #pragma unroll
     for (int w = 0; w < NW; ++w) {
       const uint32_t wb = sbase + w * C::WARP_SMEM;
-      const uint2 ml = lds64(wb + GT * D * 4 + col * 8);
+      const uint2 ml = lds64(wb + NC * D * 4 + col * 8);
       const float sw = fast_exp2(__uint_as_float(ml.x) - Mx);
       Lsum += sw * __uint_as_float(ml.y);
       const uint4 v = lds128(wb + (col * D + dq * 4) * 4);
@@ -407,7 +441,7 @@ __global__ void __launch_bounds__(128, 4) paged_decode_split_mma_kernel(const De
   __syncthreads();
   const uint32_t last_mask = lds32(flag);
   if (last_mask == 0) return;
-  for (int item = threadIdx.x; item < GT * (D / 4); item += NW * 32) {
+  for (int item = threadIdx.x; item < NC * (D / 4); item += NW * 32) {
     const int col = item / (D / 4), dq = item % (D / 4);
     const int cm = col >> p.gp_shift, hd = col & gp_mask;
     if (cm >= nmem || hd >= g_valid || !((last_mask >> cm) & 1u)) continue;
