@@ -322,7 +322,7 @@ def run_ours(args, rank, world, local_rank):
     e2e = None
     if not args.no_e2e:
         hs = HostDecodeStep(w["k_cache"], w["v_cache"], B, t.tables.shape[1], w["H"], w["scale"],
-                            index_dtype=torch.int64, chunk_tokens=args.chunk)
+                            index_dtype=torch.int64, chunk_tokens=args.chunk, flags=tma)
         hs.q_h.copy_(w["q"].cpu()), hs.k_h.copy_(w["k"].cpu()), hs.v_h.copy_(w["v"].cpu())
         hs.slot_h.copy_(w["slot_mapping"].cpu()), hs.ctx_h.copy_(w["context_lens"].cpu())
         hs.bt_h.copy_(w["block_tables"].cpu())

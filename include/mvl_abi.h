@@ -245,8 +245,8 @@ int mvl_decode_step_peers(void* const* out_peers, int num_peers, int total_heads
  * model_runner.py:231-256 (prepare_decode's H2D copies) + attention.py:493-557
  * (Attention.forward decode branch) do per layer.  slot_mapping/context_lens are int64 when
  * idx_is_i64 != 0 else int32.  Staging buffers must hold at least the host arrays' bytes.
- * Runs mvl_decode_step with MVL_DECODE_FUSED_COMBINE: the first 256 KiB of the workspace must be
- * zero before the first call.
+ * Runs mvl_decode_step with MVL_DECODE_FUSED_COMBINE | flags: the first 256 KiB of the workspace
+ * must be zero before the first call.
  */
 int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_host,
                          const void* slot_mapping_host, const void* context_lens_host,
@@ -256,7 +256,7 @@ int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_h
                          int idx_is_i64, int64_t batch, int64_t max_num_blocks, int num_heads,
                          int num_kv_heads, int head_dim, int block_size, int64_t num_blocks,
                          float scale, int elem_dtype, void* workspace, size_t workspace_bytes,
-                         int chunk_tokens, void* stream);
+                         int chunk_tokens, unsigned flags, void* stream);
 
 /*
  * mvl_paged_decode_static — mvl_paged_decode for callers that cannot allocate device memory.

@@ -42,7 +42,7 @@ PROTOTYPES = {
     "mvl_decode_step_peers": (_i, [_vp, _i, _i, _i] + [_vp] * 8 + [_i, _i64, _i64, _i64, _i64, _i64, _i,
                                    _i, _i, _i, _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
     "mvl_decode_step_host": (_i, [_vp] * 16 + [_i, _i64, _i64, _i, _i, _i, _i, _i64, _f, _i, _vp,
-                                               _sz, _i, _vp]),
+                                               _sz, _i, _u, _vp]),
     "mvl_paged_decode_static": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i64, _i64, _i64, _i, _i, _i,
                                      _i, _i64, _f, _i, _i, _vp]),
     "mvl_static_scratch_bytes": (_sz, []),

@@ -477,7 +477,7 @@ int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_h
                          int idx_is_i64, int64_t batch, int64_t max_num_blocks, int num_heads,
                          int num_kv_heads, int head_dim, int block_size, int64_t num_blocks,
                          float scale, int elem_dtype, void* workspace, size_t workspace_bytes,
-                         int chunk_tokens, void* stream) {
+                         int chunk_tokens, unsigned flags, void* stream) {
   const int es = elem_size(elem_dtype);
   if (es == 0) return MVL_ERR_DTYPE;
   if (batch < 0 || num_heads <= 0 || num_kv_heads <= 0 || head_dim <= 0 || max_num_blocks <= 0)
@@ -520,7 +520,7 @@ int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_h
                                  max_num_blocks, (int64_t)num_kv_heads * head_dim,
                                  (int64_t)num_kv_heads * head_dim, num_heads, num_kv_heads, head_dim,
                                  block_size, num_blocks, scale, elem_dtype, workspace, workspace_bytes,
-                                 chunk_tokens, MVL_DECODE_FUSED_COMBINE, stream);
+                                 chunk_tokens, MVL_DECODE_FUSED_COMBINE | flags, stream);
   if (st != MVL_OK) return st;
   e = cudaMemcpyAsync(out_host, out_dev, qb, cudaMemcpyDeviceToHost, s);
   if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync D2H out");

@@ -372,7 +372,7 @@ class HostDecodeStep:
 
     def __init__(self, k_cache: torch.Tensor, v_cache: torch.Tensor, batch: int, max_num_blocks: int,
                  num_heads: int, scale: float, index_dtype: torch.dtype = torch.int64,
-                 chunk_tokens: int = 0):
+                 chunk_tokens: int = 0, flags: int = 0):
         dev = _need_cuda(k_cache=k_cache, v_cache=v_cache)
         if k_cache.dim() != 4 or k_cache.shape != v_cache.shape or not (
                 k_cache.is_contiguous() and v_cache.is_contiguous()):
@@ -380,7 +380,7 @@ class HostDecodeStep:
         self.dev, self.k_cache, self.v_cache = dev, k_cache, v_cache
         self.num_blocks, self.block_size, self.num_kv_heads, self.head_dim = k_cache.shape
         self.batch, self.max_num_blocks, self.num_heads = batch, max_num_blocks, num_heads
-        self.scale, self.chunk_tokens = float(scale), chunk_tokens
+        self.scale, self.chunk_tokens, self.flags = float(scale), chunk_tokens, flags
         self.idx_flag = 1 if index_dtype == torch.int64 else 0
         dt = k_cache.dtype
         self.code = _DTYPES[dt]
@@ -433,7 +433,7 @@ class HostDecodeStep:
                 self.k_cache.data_ptr(), self.v_cache.data_ptr(), self.idx_flag, self.batch,
                 self.max_num_blocks, self.num_heads, self.num_kv_heads, self.head_dim,
                 self.block_size, self.num_blocks, self.scale, self.code, self.ws.data_ptr(),
-                self.ws_bytes, self.chunk_tokens, stream))
+                self.ws_bytes, self.chunk_tokens, self.flags, stream))
             if synchronize:
                 torch.cuda.current_stream(self.dev).synchronize()
         return self.out_h
