@@ -1,1 +1,1 @@
-from .decode_runner import BlockPool, DecodeRunner, SeqState  # noqa: F401
+from .decode_runner import BlockPool, DecodeRunner, SeqState, prefill_metadata  # noqa: F401

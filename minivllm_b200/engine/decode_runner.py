@@ -74,6 +74,31 @@ class BlockPool:
         seq.num_tokens = 0
 
 
+def prefill_metadata(seqs: Sequence["SeqState"], block_size: int):
+    """(cu_seqlens int32 (n+1), slot_mapping int64 (T), longest prompt) of a prefill batch —
+    what reference model_runner.py:186-213 builds with per-sequence, per-block Python loops, here a
+    repeat + arange: token ``j`` of a prompt lands in ``table[j // BS] * BS + j % BS``."""
+    if not seqs:
+        raise ValueError("empty prefill batch")
+    BS = block_size
+    n = np.fromiter((s.num_tokens for s in seqs), dtype=np.int64, count=len(seqs))
+    if (n <= 0).any():
+        raise ValueError("prefill of an empty sequence")
+    n_pages = (n + BS - 1) // BS
+    for s, need in zip(seqs, n_pages):
+        if len(s.block_table) < need:
+            raise ValueError("a sequence's block table is shorter than its prompt")
+    cu = np.zeros(len(seqs) + 1, dtype=np.int32)
+    np.cumsum(n, out=cu[1:])
+    pos = np.arange(int(cu[-1]), dtype=np.int64) - np.repeat(cu[:-1].astype(np.int64), n)
+    pages = np.concatenate([np.asarray(s.block_table[:need], dtype=np.int64)
+                            for s, need in zip(seqs, n_pages)])
+    first_page = np.zeros(len(seqs), dtype=np.int64)
+    np.cumsum(n_pages[:-1], out=first_page[1:])
+    slots = pages[np.repeat(first_page, n) + pos // BS] * BS + pos % BS
+    return cu, slots, int(n.max())
+
+
 class DecodeRunner:
     def __init__(self, num_layers: int, num_heads: int, num_kv_heads: int, head_dim: int,
                  block_size: int, num_blocks: int, max_num_seqs: int, max_model_length: int,
@@ -153,6 +178,35 @@ class DecodeRunner:
         set_context(False, slot_mapping=self.d_slot[:bucket], context_lens=self.d_ctx[:bucket],
                     block_tables=self.d_tab[:bucket, :width])
         return bucket
+
+    def prepare_prefill(self, seqs: Sequence[SeqState]) -> int:
+        """Metadata of a prefill step over whole prompts (reference model_runner.py:180-227):
+        ``cu_seqlens_q == cu_seqlens_k`` (exclusive prefix sums of ``len(seq)``), the longest
+        prompt, and ONE slot per prompt token, ``table[j // BS] * BS + j % BS`` — built with numpy
+        (a repeat + arange, no per-token Python loop) and sent with one H2D copy per array.
+        Prompts with an already-cached prefix (``num_cached_tokens > 0``, row N2) are not part of
+        this path: the reference's prefill kernel attends over the new tokens only and ignores the
+        block tables it is handed, so there is no behaviour to match.  Returns the token count."""
+        cu, slots, longest = prefill_metadata(seqs, self.block_size)
+        total = int(cu[-1])
+        h_cu = torch.from_numpy(cu).pin_memory()
+        h_slot = torch.from_numpy(slots).pin_memory()
+        d_cu = h_cu.to(self.device, non_blocking=True)
+        d_slot = h_slot.to(self.device, non_blocking=True)
+        self._prefill_keep = (h_cu, h_slot)   # pinned sources stay alive until the copies ran
+        set_context(True, cu_seqlens_q=d_cu, cu_seqlens_k=d_cu, max_seqlen_q=longest,
+                    max_seqlen_k=longest, slot_mapping=d_slot)
+        return total
+
+    @torch.inference_mode()
+    def run_prefill(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
+        """Every layer's prefill attention for the step prepared by ``prepare_prefill``:
+        ``q`` (L, T, H, D), ``k``/``v`` (L, T, KVH, D) as the projections would have produced them.
+        Stores K/V into the pages and returns (L, T, H*D).  Eager, as in the reference (graphs are
+        for decode only, model_runner.py:292-300)."""
+        outs = [layer(q[i], k[i], v[i]) for i, layer in enumerate(self.layers)]
+        reset_context()
+        return torch.stack(outs)
 
     # ------------------------------------------------------------------ the layer loop
     def _forward_layers(self, bucket: int) -> None:

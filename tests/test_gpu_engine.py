@@ -64,3 +64,57 @@ def test_decode_steps_eager_graph_oracle(cuda_device, block_size):
             assert err.max() <= 0
     for name, r in runners.items():   # caches ended bit-identical to the CPU mirror
         assert torch.equal(r.kv_cache.cpu().view(torch.uint8), cpu_cache.view(torch.uint8))
+
+
+@pytest.mark.parametrize("block_size", [16, 256])
+def test_prefill_then_decode(cuda_device, block_size):
+    """Whole-prompt prefill through the runner (store + causal attention, reference
+    attention.py:514-531), then decode steps that read what the prefill stored."""
+    from oracle import prefill_oracle as pf
+    g = torch.Generator().manual_seed(77)
+    nb = 24 if block_size == 256 else NB
+    lens = [block_size + 5, 3, 2 * block_size, 40]
+    maxlen = 3 * block_size + 8
+    r = DecodeRunner(L, H, KVH, D, block_size, nb, MAXBS, maxlen, torch.bfloat16, cuda_device, enforce_eager=True)
+    pool = BlockPool(nb, block_size, seed=9)
+    seqs = [SeqState() for _ in lens]
+    for s, n in zip(seqs, lens):
+        pool.allocate(s, n)
+    T = sum(lens)
+    q = torch.randn(L, T, H, D, generator=g).to(torch.bfloat16)
+    k = torch.randn(L, T, KVH, D, generator=g).to(torch.bfloat16)
+    v = torch.randn(L, T, KVH, D, generator=g).to(torch.bfloat16)
+    assert r.prepare_prefill(seqs) == T
+    got = r.run_prefill(q.to(cuda_device), k.to(cuda_device), v.to(cuda_device)).float().cpu()
+    cu = torch.tensor(np.concatenate([[0], np.cumsum(lens)]), dtype=torch.int32)
+    cpu_cache = torch.zeros(2, L, nb, block_size, KVH, D, dtype=torch.bfloat16)
+    slots = torch.tensor([s.block_table[j // block_size] * block_size + j % block_size
+                          for s in seqs for j in range(len(s))])
+    for layer in range(L):
+        want = pf.causal_varlen_attention(q[layer], k[layer], v[layer], cu, 1.0 / D ** 0.5, H, KVH, D)
+        want = torch.as_tensor(want, dtype=torch.float32).reshape(T, H * D)
+        err = (got[layer] - want).abs() - (4e-3 + 2.0 ** -7 * want.abs())
+        assert err.max() <= 0
+        po.store_kvcache_oracle(k[layer], v[layer], cpu_cache[0, layer], cpu_cache[1, layer], slots)
+    assert torch.equal(r.kv_cache.cpu().view(torch.uint8), cpu_cache.view(torch.uint8))
+    for step in range(2):
+        qd = torch.randn(L, len(lens), H, D, generator=g).to(torch.bfloat16)
+        kd = torch.randn(L, len(lens), KVH, D, generator=g).to(torch.bfloat16)
+        vd = torch.randn(L, len(lens), KVH, D, generator=g).to(torch.bfloat16)
+        for s in seqs:
+            pool.append_token(s)
+        bucket = r.prepare_decode(seqs)
+        r.q[:, :bucket].copy_(qd), r.k[:, :bucket].copy_(kd), r.v[:, :bucket].copy_(vd)
+        out = r.run().float().cpu()
+        n = torch.tensor([s.num_tokens for s in seqs])
+        width = max(len(s.block_table) for s in seqs)
+        tab = torch.full((len(seqs), width), -1, dtype=torch.int32)
+        for i, s in enumerate(seqs):
+            tab[i, :len(s.block_table)] = torch.tensor(s.block_table, dtype=torch.int32)
+        dslots = torch.tensor([s.block_table[-1] * block_size + (s.num_tokens - 1) % block_size for s in seqs])
+        for layer in range(L):
+            po.store_kvcache_oracle(kd[layer], vd[layer], cpu_cache[0, layer], cpu_cache[1, layer], dslots)
+            want = c_oracle.paged_decode(qd[layer], cpu_cache[0, layer], cpu_cache[1, layer], tab, n,
+                                         1.0 / D ** 0.5, H, KVH, D, block_size)
+            err = (out[layer].view(len(seqs), H, D) - want).abs() - (1e-3 + 2.0 ** -8 * want.abs())
+            assert err.max() <= 0

@@ -8,6 +8,7 @@ import inspect
 import os
 import re
 
+import numpy as np
 import pytest
 import torch
 
@@ -129,3 +130,24 @@ def test_block_pool_bookkeeping():
     assert len(pool.free) == 8 and len(s) == 0
     with pytest.raises(MemoryError):
         pool.allocate(s, 16 * 9)
+
+
+def test_prefill_metadata_matches_per_token_loop():
+    """Slot of prompt token j is table[j // BS] * BS + j % BS (reference model_runner.py:201-213,
+    written there as per-block ranges); ragged prompts incl. exact page multiples and one token."""
+    from minivllm_b200.engine import BlockPool, SeqState, prefill_metadata
+    BS = 16
+    pool = BlockPool(64, BS, seed=3)
+    lens = [1, 15, 16, 17, 48, 5]
+    seqs = [SeqState() for _ in lens]
+    for s, n in zip(seqs, lens):
+        pool.allocate(s, n)
+    cu, slots, longest = prefill_metadata(seqs, BS)
+    assert cu.tolist() == np.concatenate([[0], np.cumsum(lens)]).tolist() and longest == 48
+    want = [s.block_table[j // BS] * BS + j % BS for s in seqs for j in range(len(s))]
+    assert slots.tolist() == want and len(set(want)) == len(want)
+    with pytest.raises(ValueError):
+        prefill_metadata([], BS)
+    seqs[0].block_table = []
+    with pytest.raises(ValueError):
+        prefill_metadata(seqs, BS)
