@@ -175,13 +175,19 @@ int mvl_paged_decode_peers(void* const* out_peers, int num_peers, int total_head
  * contiguous.  cu_seqlens (num_seqs + 1) int32 on the device delimits the packed sequences
  * (attention.py:136-138); max_seqlen >= the longest one sizes the grid (the reference reads it
  * back from the device each call, :263-264; the engine already has it, model_runner.py:219).
- * 16-bit element types only (tensor-core path); MVL_ERR_DTYPE for fp32.  Like the reference it
- * attends over the new tokens only, not over cached-prefix pages.
+ * total_tokens = T, the packed tensors' first dimension (bounds the TMA loads: rows past it read
+ * as zero).  16-bit element types only (tensor-core path); MVL_ERR_DTYPE for fp32.  Like the
+ * reference it attends over the new tokens only, not over cached-prefix pages.
+ * Two kernels: tcgen05 (TMA tiles, both products on the 5th-generation tensor cores, accumulators in
+ * tensor memory), taken when scale > 0 and max_seqlen > 64; and an mma.sync kernel for short
+ * batches, non-positive scales, or when flags has MVL_PREFILL_MMA_SYNC.
  */
+#define MVL_PREFILL_MMA_SYNC 1u
 int mvl_flash_prefill(void* out, const void* q, const void* k, const void* v, int64_t q_token_stride,
-                      int64_t k_token_stride, int64_t v_token_stride, const int32_t* cu_seqlens,
-                      int num_seqs, int max_seqlen, int num_heads, int num_kv_heads, int head_dim,
-                      float scale, int elem_dtype, void* stream);
+                      int64_t k_token_stride, int64_t v_token_stride, int64_t total_tokens,
+                      const int32_t* cu_seqlens, int num_seqs, int max_seqlen, int num_heads,
+                      int num_kv_heads, int head_dim, float scale, int elem_dtype, unsigned flags,
+                      void* stream);
 
 /*
  * mvl_qk_norm_rope_store — q/k RMSNorm + rotary embedding + KV-cache write in one pass over the

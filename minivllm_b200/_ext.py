@@ -19,6 +19,8 @@ F32, F16, BF16 = 0, 1, 2
 # flags of mvl_paged_decode
 DECODE_SKIP_COMBINE, DECODE_ONLY_COMBINE, DECODE_FUSED_COMBINE, DECODE_LOAD_TMA, DECODE_CUDA_CORES = 1, 2, 4, 8, 16
 DECODE_SHARE_PREFIX = 32
+# flags of mvl_flash_prefill
+PREFILL_MMA_SYNC = 1
 
 _vp, _i, _i64, _sz, _f, _u = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float, C.c_uint
 
@@ -34,7 +36,8 @@ PROTOTYPES = {
                               _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
     "mvl_paged_decode_peers": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _i64, _i64, _i64, _i,
                                     _i, _i, _i, _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
-    "mvl_flash_prefill": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _i, _i, _i, _i, _i, _f, _i, _vp]),
+    "mvl_flash_prefill": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp, _i, _i, _i, _i, _i, _f, _i, _u,
+                               _vp]),
     "mvl_qk_norm_rope_store": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _f, _vp, _i64, _vp, _i,
                                     _vp, _vp, _vp, _i, _i64, _i64, _i, _i, _i, _i, _vp]),
     "mvl_decode_step": (_i, [_vp] * 9 + [_i, _i64, _i64, _i64, _i64, _i64, _i, _i, _i, _i, _i64, _f, _i,

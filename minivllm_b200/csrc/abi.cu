@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include "host.h"
+#include "prefill.h"
 #include "mvl_abi.h"
 
 namespace {
@@ -190,6 +191,29 @@ struct StoreArgs {  // the step's new K/V rows for the fused store (mvl_decode_s
 };
 
 }  // namespace
+
+namespace mvl {
+// Tensor map over a packed (tokens, heads, D) 16-bit tensor (prefill.h).
+int make_packed_map(CUtensorMap* map, const void* base, int dtype, int D, int heads, long long tokens,
+                    long long token_stride, int box_rows) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc) return -1;
+  const CUtensorMapDataType dt =
+      dtype == MVL_DTYPE_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  const cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)heads, (cuuint64_t)tokens};
+  const cuuint64_t strides[2] = {(cuuint64_t)D * 2, (cuuint64_t)token_stride * 2};  // bytes, dims 1..2
+  const cuuint32_t box[3] = {64u, 1u, (cuuint32_t)box_rows};
+  const cuuint32_t estr[3] = {1u, 1u, 1u};
+  return (int)enc(map, dt, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+}
+int fail_text(const char* where, int code) {
+  snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: code %d", where, code);
+  return MVL_ERR_CUDA;
+}
+int fail_cuda(int cuda_error, const char* where) { return cuda_fail((cudaError_t)cuda_error, where); }
+}  // namespace mvl
 
 extern "C" {
 

@@ -18,19 +18,9 @@
 #include "common.cuh"
 #include "host.h"
 #include "paged_decode_mma.cuh"
+#include "prefill.h"
 
 namespace mvl {
-
-struct PrefillParams {
-  void* out;          // (T, H, D) contiguous
-  const void* q;      // (T, H, D), token stride q_stride (elements)
-  const void* k;      // (T, KVH, D), token stride k_stride
-  const void* v;
-  const int* cu_seqlens;  // (S + 1)
-  long long q_stride, k_stride, v_stride;
-  int H, KVH;
-  float qscale;       // scale * log2(e)
-};
 
 template <typename T, int D>
 __global__ void __launch_bounds__(128, 2) flash_prefill_kernel(const PrefillParams p) {
@@ -236,14 +226,14 @@ static int launch_prefill_td(const PrefillParams& p, int num_seqs, int max_seqle
 
 extern "C" int mvl_flash_prefill(void* out, const void* q, const void* k, const void* v,
                                  int64_t q_token_stride, int64_t k_token_stride, int64_t v_token_stride,
-                                 const int32_t* cu_seqlens, int num_seqs, int max_seqlen, int num_heads,
-                                 int num_kv_heads, int head_dim, float scale, int elem_dtype,
-                                 void* stream) {
+                                 int64_t total_tokens, const int32_t* cu_seqlens, int num_seqs,
+                                 int max_seqlen, int num_heads, int num_kv_heads, int head_dim, float scale,
+                                 int elem_dtype, unsigned flags, void* stream) {
   if (elem_dtype != 1 && elem_dtype != 2) return -2;  // MVL_ERR_DTYPE: 16-bit types only
-  if (num_seqs < 0 || max_seqlen < 0 || num_heads <= 0 || num_kv_heads <= 0 || num_heads % num_kv_heads)
+  if (total_tokens < 0 || num_seqs < 0 || max_seqlen < 0 || num_heads <= 0 || num_kv_heads <= 0 || num_heads % num_kv_heads)
     return -3;
   if (head_dim != 64 && head_dim != 128) return -3;
-  if (num_seqs == 0 || max_seqlen == 0) return 0;
+  if (num_seqs == 0 || max_seqlen == 0 || total_tokens == 0) return 0;
   if (num_seqs > 65535 || num_heads > 65535) return -7;
   if (!out || !q || !k || !v || !cu_seqlens) return -1;
   if (q_token_stride < (int64_t)num_heads * head_dim || k_token_stride < (int64_t)num_kv_heads * head_dim ||
@@ -256,9 +246,14 @@ extern "C" int mvl_flash_prefill(void* out, const void* q, const void* k, const 
   mvl::PrefillParams p;
   p.out = out; p.q = q; p.k = k; p.v = v; p.cu_seqlens = cu_seqlens;
   p.q_stride = q_token_stride; p.k_stride = k_token_stride; p.v_stride = v_token_stride;
+  p.total_tokens = total_tokens;
   p.H = num_heads; p.KVH = num_kv_heads;
   p.qscale = scale * 1.4426950408889634f;
   cudaStream_t s = (cudaStream_t)stream;
+  // tcgen05 kernel: 128-query tiles, maximum taken on raw scores (needs scale > 0); short batches
+  // and the explicit flag keep the mma.sync kernel.
+  if (!(flags & 1u) && scale > 0.f && max_seqlen > 64 && total_tokens < (1ll << 31))
+    return mvl::launch_prefill_tcgen05(p, elem_dtype, head_dim, num_seqs, max_seqlen, s);
   int e = -1000;
   if (elem_dtype == 2)
     e = head_dim == 64 ? mvl::launch_prefill_td<__nv_bfloat16, 64>(p, num_seqs, max_seqlen, s)
@@ -266,5 +261,5 @@ extern "C" int mvl_flash_prefill(void* out, const void* q, const void* k, const 
   else
     e = head_dim == 64 ? mvl::launch_prefill_td<__half, 64>(p, num_seqs, max_seqlen, s)
                        : mvl::launch_prefill_td<__half, 128>(p, num_seqs, max_seqlen, s);
-  return e == 0 ? 0 : -6;
+  return e == 0 ? 0 : mvl::fail_cuda(e, "flash_prefill launch");
 }

@@ -1,0 +1,34 @@
+// prefill.h — parameters shared by the two prefill kernels (prefill.cu: mma.sync; prefill_tcgen05.cu).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+namespace mvl {
+
+struct PrefillParams {
+  void* out;          // (T, H, D) contiguous
+  const void* q;      // (T, H, D), token stride q_stride (elements)
+  const void* k;      // (T, KVH, D), token stride k_stride
+  const void* v;
+  const int* cu_seqlens;  // (S + 1)
+  long long q_stride, k_stride, v_stride;
+  long long total_tokens;
+  int H, KVH;
+  float qscale;       // scale * log2(e)
+};
+
+// Tensor map over a packed (tokens, heads, D) 16-bit tensor with a token stride: box = 64 elements
+// (128 bytes, the swizzle span) x 1 head x box_rows tokens, 128-byte swizzle, rows past the end
+// zero-filled.  Returns 0, the CUresult of a failed encode, or -1 without the driver entry point.
+int make_packed_map(CUtensorMap* map, const void* base, int dtype, int D, int heads, long long tokens,
+                     long long token_stride, int box_rows);
+
+// Record a failure for mvl_last_cuda_error() and return MVL_ERR_CUDA (abi.cu).
+int fail_text(const char* where, int code);
+int fail_cuda(int cuda_error, const char* where);
+
+// tcgen05 kernel (bf16 / fp16, D in {64, 128}); returns MVL_OK or MVL_ERR_CUDA (text recorded).
+int launch_prefill_tcgen05(const PrefillParams& p, int dtype, int head_dim, int num_seqs, int max_seqlen,
+                           cudaStream_t s);
+
+}  // namespace mvl

@@ -220,13 +220,14 @@ def paged_attention_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: 
 
 def flash_attention_prefill(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens: torch.Tensor,
                             scale: float, num_heads: int, num_kv_heads: int, head_dim: int,
-                            *, max_seqlen: Optional[int] = None) -> torch.Tensor:
+                            *, max_seqlen: Optional[int] = None, flags: int = 0) -> torch.Tensor:
     """Causal attention over packed variable-length sequences (prefill), reference signature
     (attention.py:212-221).  q (total_tokens, num_heads, head_dim); k, v (total_tokens,
     num_kv_heads, head_dim); cu_seqlens (num_seqs + 1) cumulative lengths.  Returns a new
     (total_tokens, num_heads, head_dim) tensor.  ``max_seqlen`` (keyword-only) sizes the grid
     without reading ``cu_seqlens`` back; when omitted it is read from the device, as the
-    reference does (attention.py:263-264).  bf16 / fp16 only."""
+    reference does (attention.py:263-264).  ``flags``: ``_ext.PREFILL_MMA_SYNC`` forces the mma.sync
+    kernel (the default is the tcgen05 kernel whenever max_seqlen > 64).  bf16 / fp16 only."""
     dev = _need_cuda(q=q, k=k, v=v, cu_seqlens=cu_seqlens)
     if q.dim() != 3 or k.dim() != 3 or v.shape != k.shape or q.shape[0] != k.shape[0]:
         raise ValueError("q must be (T, H, D) and k, v (T, KVH, D)")
@@ -251,8 +252,9 @@ def flash_attention_prefill(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, c
         max_seqlen = int((cu[1:] - cu[:-1]).max())
     with _on_device(dev):
         _ext.check(_ext.lib().mvl_flash_prefill(
-            out.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(), qs, ks, vs, cu.data_ptr(), num_seqs,
-            int(max_seqlen), H, num_kv_heads, D, float(scale), _dtype_code(q), _stream_ptr(dev)))
+            out.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(), qs, ks, vs, total, cu.data_ptr(),
+            num_seqs, int(max_seqlen), H, num_kv_heads, D, float(scale), _dtype_code(q), int(flags),
+            _stream_ptr(dev)))
     return out
 
 
