@@ -178,11 +178,15 @@ int mvl_paged_decode_peers(void* const* out_peers, int num_peers, int total_head
  * total_tokens = T, the packed tensors' first dimension (bounds the TMA loads: rows past it read
  * as zero).  16-bit element types only (tensor-core path); MVL_ERR_DTYPE for fp32.  Like the
  * reference it attends over the new tokens only, not over cached-prefix pages.
- * Two kernels: tcgen05 (TMA tiles, both products on the 5th-generation tensor cores, accumulators in
- * tensor memory), taken when scale > 0 and max_seqlen > 64; and an mma.sync kernel for short
- * batches, non-positive scales, or when flags has MVL_PREFILL_MMA_SYNC.
+ * Kernels: two on tcgen05 (TMA tiles, both products on the 5th-generation tensor cores, accumulators
+ * and probabilities in tensor memory) — a pair kernel (256 queries per CTA, two tiles in ping-pong,
+ * taken from max_seqlen >= 2048) and a one-tile kernel (64 < max_seqlen < 2048) — and an mma.sync
+ * kernel for batches of short sequences and non-positive scales.  flags force one of them (the
+ * tcgen05 ones still need scale > 0): measurement and test switches, results agree to rounding.
  */
 #define MVL_PREFILL_MMA_SYNC 1u
+#define MVL_PREFILL_ONE_TILE 2u
+#define MVL_PREFILL_PAIR 4u
 int mvl_flash_prefill(void* out, const void* q, const void* k, const void* v, int64_t q_token_stride,
                       int64_t k_token_stride, int64_t v_token_stride, int64_t total_tokens,
                       const int32_t* cu_seqlens, int num_seqs, int max_seqlen, int num_heads,

@@ -20,7 +20,7 @@ F32, F16, BF16 = 0, 1, 2
 DECODE_SKIP_COMBINE, DECODE_ONLY_COMBINE, DECODE_FUSED_COMBINE, DECODE_LOAD_TMA, DECODE_CUDA_CORES = 1, 2, 4, 8, 16
 DECODE_SHARE_PREFIX = 32
 # flags of mvl_flash_prefill
-PREFILL_MMA_SYNC = 1
+PREFILL_MMA_SYNC, PREFILL_ONE_TILE, PREFILL_PAIR = 1, 2, 4
 
 _vp, _i, _i64, _sz, _f, _u = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float, C.c_uint
 

@@ -250,10 +250,14 @@ extern "C" int mvl_flash_prefill(void* out, const void* q, const void* k, const 
   p.H = num_heads; p.KVH = num_kv_heads;
   p.qscale = scale * 1.4426950408889634f;
   cudaStream_t s = (cudaStream_t)stream;
-  // tcgen05 kernel: 128-query tiles, maximum taken on raw scores (needs scale > 0); short batches
-  // and the explicit flag keep the mma.sync kernel.
-  if (!(flags & 1u) && scale > 0.f && max_seqlen > 64 && total_tokens < (1ll << 31))
-    return mvl::launch_prefill_tcgen05(p, elem_dtype, head_dim, num_seqs, max_seqlen, s);
+  // tcgen05 kernels: 128-query tiles, maximum taken on raw scores (needs scale > 0).  The pair kernel
+  // (256 queries per CTA, ping-pong) wins from ~2k tokens per sequence, the one-tile kernel below
+  // (1024: 582 vs 549 TFLOP/s; 4096: 904 vs 976); batches of short sequences keep mma.sync.
+  const bool tc5_ok = scale > 0.f && total_tokens < (1ll << 31);
+  if (!(flags & 1u) && tc5_ok && ((flags & 6u) || max_seqlen > 64)) {
+    const bool single = (flags & 2u) || (!(flags & 4u) && max_seqlen < 2048);
+    return mvl::launch_prefill_tcgen05(p, elem_dtype, head_dim, num_seqs, max_seqlen, single, s);
+  }
   int e = -1000;
   if (elem_dtype == 2)
     e = head_dim == 64 ? mvl::launch_prefill_td<__nv_bfloat16, 64>(p, num_seqs, max_seqlen, s)

@@ -29,6 +29,6 @@ int fail_cuda(int cuda_error, const char* where);
 
 // tcgen05 kernel (bf16 / fp16, D in {64, 128}); returns MVL_OK or MVL_ERR_CUDA (text recorded).
 int launch_prefill_tcgen05(const PrefillParams& p, int dtype, int head_dim, int num_seqs, int max_seqlen,
-                           cudaStream_t s);
+                           bool single_tile, cudaStream_t s);
 
 }  // namespace mvl

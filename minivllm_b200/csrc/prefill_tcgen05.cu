@@ -22,6 +22,7 @@
 namespace mvl {
 namespace {
 
+
 template <int D>
 struct Tc5Cfg {
   static constexpr int BM = 128, BN = 128;
@@ -40,12 +41,104 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
   return v;
 }
 
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+
+// One softmax step of one query row (thread = row = TMEM lane): S row -> registers, causal mask on the
+// diagonal tile (key c visible iff c <= t), lazy maximum (O rescaled in TMEM only when the row maximum
+// grew by more than 2^8), P = exp2((S - m_ref) * qs) packed to 16 bits over the first 64 S columns.
+// Ends with tcgen05.wait::st: the caller fences and signals.
+template <typename T, int D>
+__device__ __forceinline__ void softmax_step(uint32_t s_addr, uint32_t o_addr, bool first, bool diag, int t,
+                                             float qs, float& m_ref, float& l) {
+  using M = MmaType<T>;
+  uint32_t su[128];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) tc5::tmem_ld32(s_addr + c * 32, su + c * 32);
+  tc5::tmem_wait_ld();
+  if (diag) {
+#pragma unroll
+    for (int c = 0; c < 128; ++c)
+      if (c > t) su[c] = 0xff800000u;
+  }
+  float mxa[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four chains: the row maximum is latency-bound
+#pragma unroll
+  for (int c = 0; c < 128; c += 8)
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      mxa[k] = fmax3(mxa[k], __uint_as_float(su[c + 2 * k]), __uint_as_float(su[c + 2 * k + 1]));
+  const float mx = fmaxf(fmaxf(mxa[0], mxa[1]), fmaxf(mxa[2], mxa[3]));
+  bool grow = false;
+  if (first) m_ref = mx;
+  else grow = (mx - m_ref) * qs > 8.f;
+  if (__any_sync(0xffffffffu, grow)) {  // warp-uniform: the TMEM moves are warp-collective
+    float alpha = 1.f;
+    if (grow) {
+      alpha = fast_exp2((m_ref - mx) * qs);
+      m_ref = mx;
+      l *= alpha;
+    }
+#pragma unroll
+    for (int c = 0; c < D / 32; ++c) {
+      uint32_t o[32];
+      tc5::tmem_ld32(o_addr + c * 32, o);
+      tc5::tmem_wait_ld();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+      tc5::tmem_st32(o_addr + c * 32, o);
+    }
+  }
+  const float neg = -m_ref * qs;
+  const u64 qs2 = pack2(qs, qs), neg2 = pack2(neg, neg);
+  u64 acc[4] = {0ull, 0ull, 0ull, 0ull};
+  uint32_t pk[64];
+#pragma unroll
+  for (int c = 0; c < 64; ++c) {
+    float x0, x1;
+    unpack2(ffma2(pack2(__uint_as_float(su[2 * c]), __uint_as_float(su[2 * c + 1])), qs2, neg2), x0, x1);
+    // MUFU.EX2 for every element: a polynomial 2^x on the FMA pipe for 1, 2 or 3 of every 4 column
+    // pairs was measured slower (1175 / 1104 / 1023 vs 1202 TFLOP/s at 2 x 16k tokens)
+    const float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
+    acc[c & 3] = fadd2(acc[c & 3], pack2(p0, p1));
+    pk[c] = M::pack(p0, p1);
+  }
+  l += hsum2(fadd2(fadd2(acc[0], acc[1]), fadd2(acc[2], acc[3])));
+  tc5::tmem_st32(s_addr, pk);
+  tc5::tmem_st32(s_addr + 32, pk + 32);
+  tc5::tmem_wait_st();
+}
+
+// O row (fp32, TMEM) * inv -> 16-bit row in global memory.
+template <typename T, int D>
+__device__ __forceinline__ void store_row(uint32_t o_addr, T* out, float inv, bool valid) {
+  using M = MmaType<T>;
+#pragma unroll
+  for (int c = 0; c < D / 32; ++c) {
+    uint32_t o[32];
+    tc5::tmem_ld32(o_addr + c * 32, o);
+    tc5::tmem_wait_ld();
+    if (valid) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint4 w;
+        w.x = M::pack(__uint_as_float(o[8 * i + 0]) * inv, __uint_as_float(o[8 * i + 1]) * inv);
+        w.y = M::pack(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv);
+        w.z = M::pack(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv);
+        w.w = M::pack(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv);
+        *reinterpret_cast<uint4*>(out + c * 32 + i * 8) = w;
+      }
+    }
+  }
+}
+
 template <typename T, int D>
 __global__ void __launch_bounds__(128, 2)
 flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
                              const __grid_constant__ CUtensorMap mv, const PrefillParams p) {
   using C = Tc5Cfg<D>;
-  using M = MmaType<T>;
   constexpr int FMT = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
   constexpr uint32_t IDESC_QK = tc5::instr_desc_f16(FMT, 0, 128, 128);
   constexpr uint32_t IDESC_PV = tc5::instr_desc_f16(FMT, 1, 128, D);
@@ -84,20 +177,22 @@ flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __gri
 #pragma unroll
     for (int pn = 0; pn < C::PANELS; ++pn) tma_load_3d(dst + pn * C::PANEL_BYTES, map, pn * 64, head, token, bar);
   };
+  constexpr uint32_t HI = tc5::smem_desc_hi_sw128(1024);
+  const uint32_t q_lo = tc5::smem_desc_lo(sQ, 16), k_lo = tc5::smem_desc_lo(sK, 16),
+                 v_lo = tc5::smem_desc_lo(sV, C::PANEL_BYTES);
   auto issue_qk = [&]() {  // S = Q . K^T: D/16 steps of K = 16 (32 bytes along the swizzled row)
 #pragma unroll
     for (int ks = 0; ks < D / 16; ++ks) {
-      const uint32_t off = (ks >> 2) * C::PANEL_BYTES + (ks & 3) * 32;
-      tc5::mma_ss(tmem, tc5::smem_desc_sw128(sQ + off, 16, 1024), tc5::smem_desc_sw128(sK + off, 16, 1024),
-                  IDESC_QK, ks > 0);
+      const uint32_t off = ((ks >> 2) * C::PANEL_BYTES + (ks & 3) * 32) >> 4;
+      tc5::mma_ss(tmem, tc5::desc64(q_lo + off, HI), tc5::desc64(k_lo + off, HI), IDESC_QK, ks > 0);
     }
     tc5::commit(bar_s);
   };
   auto issue_pv = [&](int j) {  // O += P . V: 8 steps of 16 keys (8 TMEM columns of P, 16 rows of V)
 #pragma unroll
     for (int kk = 0; kk < C::BN / 16; ++kk)
-      tc5::mma_ts(tmem + C::O_COL, tmem + kk * 8, tc5::smem_desc_sw128(sV + kk * 2048, C::PANEL_BYTES, 1024),
-                  IDESC_PV, (j > 0 || kk > 0) ? 1u : 0u);
+      tc5::mma_ts(tmem + C::O_COL, tmem + kk * 8, tc5::desc64(v_lo + kk * (2048 >> 4), HI), IDESC_PV,
+                  (j > 0 || kk > 0) ? 1u : 0u);
     tc5::commit(bar_o);
   };
 
@@ -120,55 +215,7 @@ flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __gri
       if (j > 0) load_tile(&mv, sV, kvh, seq_start + j * C::BN, bar_v);               // product j-1 has retired
       if (j + 1 < ntiles) load_tile(&mk, sK, kvh, seq_start + (j + 1) * C::BN, bar_k);  // S_j no longer reads K_j
     }
-    uint32_t su[128];
-#pragma unroll
-    for (int c = 0; c < 4; ++c) tc5::tmem_ld32(lane_base + c * 32, su + c * 32);
-    tc5::tmem_wait_ld();
-    float mx = -INFINITY;
-    if (j == ntiles - 1) {  // diagonal tile: key (kv0 + c) is visible to query (m0 + tid) iff c <= tid
-#pragma unroll
-      for (int c = 0; c < 128; ++c) {
-        if (c > tid) su[c] = 0xff800000u;
-        mx = fmaxf(mx, __uint_as_float(su[c]));
-      }
-    } else {
-#pragma unroll
-      for (int c = 0; c < 128; ++c) mx = fmaxf(mx, __uint_as_float(su[c]));
-    }
-    bool grow = false;
-    if (j == 0) m_ref = mx;
-    else grow = (mx - m_ref) * qs > 8.f;
-    if (__any_sync(0xffffffffu, grow)) {  // warp-uniform: the TMEM moves are warp-collective
-      float alpha = 1.f;
-      if (grow) {
-        alpha = fast_exp2((m_ref - mx) * qs);
-        m_ref = mx;
-        l *= alpha;
-      }
-#pragma unroll
-      for (int c = 0; c < D / 32; ++c) {
-        uint32_t o[32];
-        tc5::tmem_ld32(lane_base + C::O_COL + c * 32, o);
-        tc5::tmem_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-        tc5::tmem_st32(lane_base + C::O_COL + c * 32, o);
-      }
-    }
-    const float neg = -m_ref * qs;
-    float sum = 0.f;
-    uint32_t pk[64];
-#pragma unroll
-    for (int c = 0; c < 64; ++c) {
-      const float p0 = fast_exp2(fmaf(__uint_as_float(su[2 * c]), qs, neg));
-      const float p1 = fast_exp2(fmaf(__uint_as_float(su[2 * c + 1]), qs, neg));
-      sum += p0 + p1;
-      pk[c] = M::pack(p0, p1);
-    }
-    l += sum;
-    tc5::tmem_st32(lane_base, pk);
-    tc5::tmem_st32(lane_base + 32, pk + 32);
-    tc5::tmem_wait_st();
+    softmax_step<T, D>(lane_base, lane_base + C::O_COL, j == 0, j == ntiles - 1, tid, qs, m_ref, l);
     tc5::fence_before_sync();
     __syncthreads();  // every row of P_j (and any rescaled O) is in TMEM
     if (tid == 0) {
@@ -187,28 +234,210 @@ flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __gri
 
   // ---- O / l -> out: thread t writes row m0 + t
   const int row = m0 + tid;
-  const float inv = 1.f / l;
-  T* out = reinterpret_cast<T*>(p.out) + ((long long)(seq_start + row) * p.H + h) * D;
+  store_row<T, D>(lane_base + C::O_COL, reinterpret_cast<T*>(p.out) + ((long long)(seq_start + row) * p.H + h) * D,
+                  1.f / l, row < seq_len);
+  tc5::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc5::tmem_dealloc(tmem, C::TMEM_COLS);
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Pair kernel: one CTA = 256 consecutive queries (two 128-row tiles) of one sequence for one head,
+// one CTA per SM.  Warps 0-3 run the softmax of tile 0, warps 4-7 of tile 1; lane 0 of warp 8 issues
+// every MMA.  Each tile has its own S (and aliased P) and O in tensor memory, so
+// the issue order   P0V(j), QK0(j+1), P1V(j), QK1(j+1), ...   keeps the tensor pipe busy with one
+// tile's products while the other tile's softmax runs.  K and V are double-buffered and shared by
+// the two tiles; lane 0 of warp 9 issues the TMA loads, waiting on "empty" barriers that the MMA
+// thread arms with tcgen05.commit after the last product reading a buffer.
+template <int D>
+struct PairCfg {
+  static constexpr int PANELS = D / 64, PANEL_BYTES = 128 * 128, TILE_BYTES = PANELS * PANEL_BYTES;
+  static constexpr int OFF_K = 2 * TILE_BYTES, OFF_V = 4 * TILE_BYTES, OFF_BAR = 6 * TILE_BYTES;
+  static constexpr int NEED = OFF_BAR + 128 + 1024;
+  // one CTA per SM (it allocates all 512 TMEM columns): ask for more than half the SM's shared memory
+  static constexpr int SMEM = NEED > 120 * 1024 ? NEED : 120 * 1024;
+  static constexpr int TMEM_COLS = 512;  // S0 [0,128) S1 [128,256) O0 [256,256+D) O1 [256+D, 256+2D)
+};
+
+template <typename T, int D>
+__global__ void __launch_bounds__(384, 1)
+flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
+                                  const __grid_constant__ CUtensorMap mv, const PrefillParams p) {
+  using C = PairCfg<D>;
+  constexpr int FMT = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+  constexpr uint32_t IDESC_QK = tc5::instr_desc_f16(FMT, 0, 128, 128);
+  constexpr uint32_t IDESC_PV = tc5::instr_desc_f16(FMT, 1, 128, D);
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sQ = base, sK = base + C::OFF_K, sV = base + C::OFF_V, bars = base + C::OFF_BAR;
+  const uint32_t q_full = bars, k_full = bars + 8, v_full = bars + 24, s_full = bars + 40, p_ready = bars + 56,
+                 o_done = bars + 72, k_empty = bars + 88, v_empty = bars + 104,
+                 tmem_slot = bars + 120;  // pairs of barriers: [i] at + 8 * i
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int mb2 = gridDim.x - 1 - blockIdx.x;  // heaviest (latest) query tiles first
+  const int h = blockIdx.y, seq = blockIdx.z;
+  const int kvh = h / (p.H / p.KVH);
+  const int seq_start = p.cu_seqlens[seq];
+  const int seq_len = p.cu_seqlens[seq + 1] - seq_start;
+  const int m0 = mb2 * 256;
+  if (m0 >= seq_len) return;
+  const int n0 = 2 * mb2 + 1;                           // key tiles of query tile 0 (last = its diagonal)
+  const int n1 = m0 + 128 < seq_len ? n0 + 1 : 0;       // query tile 1, if the sequence reaches it
+  const int n = n1 ? n1 : n0;
+
+  if (warp == 8) {
+    tc5::tmem_alloc(tmem_slot, C::TMEM_COLS);
+    tc5::tmem_relinquish();
+  }
+  if (tid == 0) {
+    mbar_init(q_full, 1);
 #pragma unroll
-  for (int c = 0; c < D / 32; ++c) {
-    uint32_t o[32];
-    tc5::tmem_ld32(lane_base + C::O_COL + c * 32, o);
-    tc5::tmem_wait_ld();
-    if (row < seq_len) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(k_full + 8 * i, 1), mbar_init(v_full + 8 * i, 1), mbar_init(s_full + 8 * i, 1);
+      mbar_init(p_ready + 8 * i, 128), mbar_init(o_done + 8 * i, 1);
+      mbar_init(k_empty + 8 * i, 1), mbar_init(v_empty + 8 * i, 1);
+    }
+    mbar_fence_init();
+  }
+  tc5::fence_before_sync();
+  __syncthreads();
+  tc5::fence_after_sync();
+  const uint32_t tmem = lds_u32(tmem_slot);
+
+  if (warp >= 8) {
+    // issue warpgroup: hands most of its registers to the two softmax warpgroups
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
+    if (tid == 288) {
+      // ---- TMA thread: Q once, then K_j / V_j into stage j & 1 as soon as the products that read
+      // the previous occupant (tile j - 2) have retired (k_empty / v_empty, signalled by tcgen05.commit)
+      auto load_tile = [&](const CUtensorMap* map, uint32_t dst, int head, int token, uint32_t bar) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        uint4 w;
-        w.x = M::pack(__uint_as_float(o[8 * i + 0]) * inv, __uint_as_float(o[8 * i + 1]) * inv);
-        w.y = M::pack(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv);
-        w.z = M::pack(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv);
-        w.w = M::pack(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv);
-        *reinterpret_cast<uint4*>(out + c * 32 + i * 8) = w;
+        for (int pn = 0; pn < C::PANELS; ++pn)
+          tma_load_3d(dst + pn * C::PANEL_BYTES, map, pn * 64, head, token, bar);
+      };
+      mbar_expect_tx(q_full, (n1 ? 2 : 1) * C::TILE_BYTES);
+      load_tile(&mq, sQ, h, seq_start + m0, q_full);
+      if (n1) load_tile(&mq, sQ + C::TILE_BYTES, h, seq_start + m0 + 128, q_full);
+      for (int j = 0; j < n; ++j) {
+        const int st = j & 1;
+        if (j >= 2) tc5::mbar_wait_bounded(k_empty + 8 * st, ((j >> 1) - 1) & 1);
+        mbar_expect_tx(k_full + 8 * st, C::TILE_BYTES);
+        load_tile(&mk, sK + st * C::TILE_BYTES, kvh, seq_start + j * 128, k_full + 8 * st);
+        if (j >= 2) tc5::mbar_wait_bounded(v_empty + 8 * st, ((j >> 1) - 1) & 1);
+        mbar_expect_tx(v_full + 8 * st, C::TILE_BYTES);
+        load_tile(&mv, sV + st * C::TILE_BYTES, kvh, seq_start + j * 128, v_full + 8 * st);
       }
+    } else if (tid == 256) {
+      // ---- MMA thread
+      constexpr uint32_t HI = tc5::smem_desc_hi_sw128(1024);
+      constexpr uint32_t STAGE = C::TILE_BYTES >> 4;
+      const uint32_t q_lo = tc5::smem_desc_lo(sQ, 16), k_lo = tc5::smem_desc_lo(sK, 16),
+                     v_lo = tc5::smem_desc_lo(sV, C::PANEL_BYTES);
+      auto issue_qk = [&](int w, int j) {  // S_w = Q_w . K_j^T
+        const uint32_t q = q_lo + w * STAGE, k = k_lo + (j & 1) * STAGE;
+#pragma unroll
+        for (int ks = 0; ks < D / 16; ++ks) {
+          const uint32_t off = ((ks >> 2) * C::PANEL_BYTES + (ks & 3) * 32) >> 4;
+          tc5::mma_ss(tmem + w * 128, tc5::desc64(q + off, HI), tc5::desc64(k + off, HI), IDESC_QK, ks > 0);
+        }
+        tc5::commit(s_full + 8 * w);
+      };
+      auto issue_pv = [&](int w, int j) {  // O_w += P_w . V_j
+        const uint32_t v = v_lo + (j & 1) * STAGE;
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)
+          tc5::mma_ts(tmem + 256 + w * D, tmem + w * 128 + kk * 8, tc5::desc64(v + kk * (2048 >> 4), HI), IDESC_PV,
+                      (j > 0 || kk > 0) ? 1u : 0u);
+      };
+      tc5::mbar_wait_bounded(q_full, 0);
+      tc5::mbar_wait_bounded(k_full, 0);
+      tc5::fence_after_sync();
+      issue_qk(0, 0);
+      if (n1) issue_qk(1, 0);
+      tc5::commit(k_empty);
+      for (int j = 0; j < n; ++j) {
+        const int st = j & 1;
+        tc5::mbar_wait_bounded(v_full + 8 * st, (j >> 1) & 1);
+        bool k_next_seen = false;
+        if (j < n0) {
+          tc5::mbar_wait_bounded(p_ready, j & 1);
+          tc5::fence_after_sync();
+          issue_pv(0, j);
+          if (j == n0 - 1) tc5::commit(o_done);
+          if (j >= n1) tc5::commit(v_empty + 8 * st);   // tile 1 does not read V_j
+          if (j + 1 < n0) {
+            tc5::mbar_wait_bounded(k_full + 8 * (st ^ 1), ((j + 1) >> 1) & 1);
+            tc5::fence_after_sync();
+            k_next_seen = true;
+            issue_qk(0, j + 1);
+            if (j + 1 >= n1) tc5::commit(k_empty + 8 * (st ^ 1));
+          }
+        }
+        if (j < n1) {
+          tc5::mbar_wait_bounded(p_ready + 8, j & 1);
+          tc5::fence_after_sync();
+          issue_pv(1, j);
+          if (j == n1 - 1) tc5::commit(o_done + 8);
+          tc5::commit(v_empty + 8 * st);
+          if (j + 1 < n1) {
+            if (!k_next_seen) {
+              tc5::mbar_wait_bounded(k_full + 8 * (st ^ 1), ((j + 1) >> 1) & 1);
+              tc5::fence_after_sync();
+            }
+            issue_qk(1, j + 1);
+            tc5::commit(k_empty + 8 * (st ^ 1));
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+    const int w = warp >> 2, t = tid & 127;
+    const int nw = w ? n1 : n0;
+    const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    const uint32_t s_addr = lane_base + w * 128, o_addr = lane_base + 256 + w * D;
+    float m_ref = 0.f, l = 0.f;
+    const float qs = p.qscale;
+    for (int j = 0; j < nw; ++j) {
+      tc5::mbar_wait_bounded(s_full + 8 * w, j & 1);  // S_w(j) complete; so is the product of step j-1
+      tc5::fence_after_sync();
+      softmax_step<T, D>(s_addr, o_addr, j == 0, j == nw - 1, t, qs, m_ref, l);
+      tc5::fence_before_sync();
+      tc5::mbar_arrive(p_ready + 8 * w);
+    }
+    if (nw > 0) {
+      tc5::mbar_wait_bounded(o_done + 8 * w, 0);
+      tc5::fence_after_sync();
+      const int row = m0 + w * 128 + t;
+      store_row<T, D>(o_addr, reinterpret_cast<T*>(p.out) + ((long long)(seq_start + row) * p.H + h) * D, 1.f / l,
+                      row < seq_len);
     }
   }
   tc5::fence_before_sync();
   __syncthreads();
-  if (warp == 0) tc5::tmem_dealloc(tmem, C::TMEM_COLS);
+  if (warp == 8) tc5::tmem_dealloc(tmem, C::TMEM_COLS);
+}
+
+template <typename T, int D>
+int launch_pair_td(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const PrefillParams& p,
+                   int num_seqs, int max_seqlen, cudaStream_t s) {
+  using C = PairCfg<D>;
+  auto kern = flash_prefill_tcgen05_pair_kernel<T, D>;
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev >= 64 || !configured[dev]) {
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 64) configured[dev] = true;
+  }
+  dim3 grid((unsigned)((max_seqlen + 255) / 256), (unsigned)p.H, (unsigned)num_seqs);
+  kern<<<grid, 384, C::SMEM, s>>>(mq, mk, mv, p);
+  return (int)cudaGetLastError();
 }
 
 template <typename T, int D>
@@ -233,7 +462,7 @@ int launch_td(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& m
 }  // namespace
 
 int launch_prefill_tcgen05(const PrefillParams& p, int dtype, int head_dim, int num_seqs, int max_seqlen,
-                           cudaStream_t s) {
+                           bool single_tile, cudaStream_t s) {
   CUtensorMap mq, mk, mv;
   int r;
   if ((r = make_packed_map(&mq, p.q, dtype, head_dim, p.H, p.total_tokens, p.q_stride, 128)) != 0)
@@ -242,7 +471,14 @@ int launch_prefill_tcgen05(const PrefillParams& p, int dtype, int head_dim, int 
     return fail_text("prefill tensor map (k)", r);
   if ((r = make_packed_map(&mv, p.v, dtype, head_dim, p.KVH, p.total_tokens, p.v_stride, 128)) != 0)
     return fail_text("prefill tensor map (v)", r);
-  if (dtype == 2)
+  if (!single_tile) {
+    if (dtype == 2)
+      r = head_dim == 64 ? launch_pair_td<__nv_bfloat16, 64>(mq, mk, mv, p, num_seqs, max_seqlen, s)
+                         : launch_pair_td<__nv_bfloat16, 128>(mq, mk, mv, p, num_seqs, max_seqlen, s);
+    else
+      r = head_dim == 64 ? launch_pair_td<__half, 64>(mq, mk, mv, p, num_seqs, max_seqlen, s)
+                         : launch_pair_td<__half, 128>(mq, mk, mv, p, num_seqs, max_seqlen, s);
+  } else if (dtype == 2)
     r = head_dim == 64 ? launch_td<__nv_bfloat16, 64>(mq, mk, mv, p, num_seqs, max_seqlen, s)
                        : launch_td<__nv_bfloat16, 128>(mq, mk, mv, p, num_seqs, max_seqlen, s);
   else

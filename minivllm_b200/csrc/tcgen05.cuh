@@ -38,6 +38,17 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr, uint32_t lbo_
   return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) |
          ((uint64_t)(sbo_bytes >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
+// The same descriptor split in two 32-bit words, so that the issuing thread's loop only adds a
+// byte offset >> 4 to the low word (one uniform add per MMA: the issue loop must stay well under the
+// 64 clocks a 128 x 128 x 16 MMA takes, or the tensor pipe waits for its next instruction).
+__device__ __forceinline__ uint32_t smem_desc_lo(uint32_t addr, uint32_t lbo_bytes) {
+  return ((addr & 0x3FFFFu) >> 4) | ((lbo_bytes >> 4) << 16);
+}
+__host__ __device__ constexpr uint32_t smem_desc_hi_sw128(uint32_t sbo_bytes) {
+  return (sbo_bytes >> 4) | (1u << 14) | (2u << 29);
+}
+__device__ __forceinline__ uint64_t desc64(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; }
+
 // Instruction descriptor of kind::f16: fp32 accumulate (bits 4..5 = 1), A/B format (0 = f16, 1 = bf16)
 // at bits 7..9 / 10..12, A/B major (0 = K, 1 = MN) at bits 15 / 16, N >> 3 at 17..22, M >> 4 at 24..28.
 __host__ __device__ constexpr uint32_t instr_desc_f16(int fmt, int b_mn_major, int m, int n) {
@@ -92,20 +103,31 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
 // mbarrier wait that traps instead of hanging the GPU if the barrier never completes (a lost TMA
 // or MMA completion is a programming error; ~2^28 polls is seconds, far beyond any real wait).
 __device__ __forceinline__ void mbar_wait_bounded(uint32_t bar, uint32_t parity) {
-  uint32_t done = 0;
-  for (uint32_t spins = 0; !done; ++spins) {
-    asm volatile(
-        "{\n.reg .pred p;\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-        "selp.u32 %0, 1, 0, p;\n}\n"
-        : "=r"(done)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    if (spins > (1u << 28)) __trap();
-  }
+  // the loop lives inside one asm block: a C-level spin loop here keeps ptxas from giving the
+  // softmax warpgroups the registers they obtain with setmaxnreg (measured: it then spills)
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .u32 spins;\n"
+      "mov.u32 spins, 0;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "add.u32 spins, spins, 1;\n"
+      "setp.gt.u32 p, spins, 0x10000000;\n"
+      "@p trap;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
 }
 
 }  // namespace tc5

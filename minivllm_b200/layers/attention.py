@@ -226,8 +226,8 @@ def flash_attention_prefill(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, c
     num_kv_heads, head_dim); cu_seqlens (num_seqs + 1) cumulative lengths.  Returns a new
     (total_tokens, num_heads, head_dim) tensor.  ``max_seqlen`` (keyword-only) sizes the grid
     without reading ``cu_seqlens`` back; when omitted it is read from the device, as the
-    reference does (attention.py:263-264).  ``flags``: ``_ext.PREFILL_MMA_SYNC`` forces the mma.sync
-    kernel (the default is the tcgen05 kernel whenever max_seqlen > 64).  bf16 / fp16 only."""
+    reference does (attention.py:263-264).  ``flags``: ``_ext.PREFILL_MMA_SYNC`` / ``PREFILL_ONE_TILE`` /
+    ``PREFILL_PAIR`` force one kernel (default: by max_seqlen, see include/mvl_abi.h).  bf16 / fp16 only."""
     dev = _need_cuda(q=q, k=k, v=v, cu_seqlens=cu_seqlens)
     if q.dim() != 3 or k.dim() != 3 or v.shape != k.shape or q.shape[0] != k.shape[0]:
         raise ValueError("q must be (T, H, D) and k, v (T, KVH, D)")

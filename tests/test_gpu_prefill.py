@@ -28,14 +28,18 @@ def _check(got, want):
     assert np.isfinite(got).all() and excess.max() <= 0, f"max excess {excess.max():.3e}"
 
 
+KERNELS = {"auto": 0, "mma_sync": 1, "tcgen05_one_tile": 2, "tcgen05_pair": 4}   # mvl_flash_prefill flags
+
+
 @pytest.mark.parametrize("name", sorted(PREFILL_CASES))
 @pytest.mark.parametrize("pass_max", [True, False])
-def test_prefill_matches_reference_and_oracle(cuda_device, name, pass_max):
+@pytest.mark.parametrize("kernel", sorted(KERNELS))
+def test_prefill_matches_reference_and_oracle(cuda_device, name, pass_max, kernel):
     inp = make_prefill_inputs(name)
     z = np.load(os.path.join(GOLD, f"prefill_{name}.npz"))
     out = flash_attention_prefill(inp["q"].to(cuda_device), inp["k"].to(cuda_device), inp["v"].to(cuda_device),
                                   inp["cu_seqlens"].to(cuda_device), inp["scale"], inp["H"], inp["KVH"], inp["D"],
-                                  max_seqlen=inp["max_seqlen"] if pass_max else None)
+                                  max_seqlen=inp["max_seqlen"] if pass_max else None, flags=KERNELS[kernel])
     assert out.shape == inp["q"].shape and out.dtype == inp["q"].dtype
     native = torch.from_numpy(z["ref_out_bits"]).view(inp["q"].dtype).float()
     assert (out.float().cpu() - native).abs().max() <= 2e-2
@@ -46,7 +50,8 @@ def test_prefill_matches_reference_and_oracle(cuda_device, name, pass_max):
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("H,KVH,D", [(8, 8, 64), (8, 2, 128), (6, 2, 128), (16, 1, 64)])
-def test_prefill_random_ragged_and_strided(cuda_device, dtype, H, KVH, D):
+@pytest.mark.parametrize("kernel", sorted(KERNELS))
+def test_prefill_random_ragged_and_strided(cuda_device, dtype, H, KVH, D, kernel):
     g = torch.Generator().manual_seed(H * 100 + KVH * 10 + D)
     lens = [int(x) for x in torch.randint(1, 300, (5,), generator=g)] + [64, 128, 1]
     total = sum(lens)
@@ -57,7 +62,7 @@ def test_prefill_random_ragged_and_strided(cuda_device, dtype, H, KVH, D):
     dq = qkv.to(cuda_device)
     a, b, c = dq.split([H * D, KVH * D, KVH * D], dim=-1)
     out = flash_attention_prefill(a.view(total, H, D), b.view(total, KVH, D), c.view(total, KVH, D),
-                                  cu.to(cuda_device), 1.0 / D ** 0.5, H, KVH, D)
+                                  cu.to(cuda_device), 1.0 / D ** 0.5, H, KVH, D, flags=KERNELS[kernel])
     want = prefill_oracle.causal_varlen_attention(q, k, v, cu, 1.0 / D ** 0.5, H, KVH, D)
     _check(out, want)
     # the first token of every sequence attends to itself only: output == its v row
@@ -115,3 +120,47 @@ def test_prefill_rejects_fp32(cuda_device):
     q = torch.zeros(4, 2, 64, device=cuda_device)
     with pytest.raises(NotImplementedError):
         flash_attention_prefill(q, q, q, torch.tensor([0, 4], device=cuda_device), 1.0, 2, 2, 64)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("D", [64, 128])
+def test_prefill_long_sequences_all_kernels(cuda_device, dtype, D):
+    """Sequences long enough for many key tiles per query tile (the tcgen05 kernels' steady state:
+    double-buffered K/V, lazy rescale, ping-pong), with lengths around the 128 / 256 tile edges and a
+    batch whose last tile overhangs the end of the packed tensors.  Every kernel against the oracle;
+    large scores (x4) make the running maximum grow late, which exercises the O rescale in TMEM."""
+    H, KVH = 4, 2
+    g = torch.Generator().manual_seed(D)
+    lens = [1500, 257, 256, 255, 129, 1, 2049]
+    total = sum(lens)
+    q = (torch.randn(total, H, D, generator=g) * 4).to(dtype)
+    k = torch.randn(total, KVH, D, generator=g).to(dtype)
+    v = torch.randn(total, KVH, D, generator=g).to(dtype)
+    cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32)
+    want = prefill_oracle.causal_varlen_attention(q, k, v, cu, 1.0 / D ** 0.5, H, KVH, D)
+    outs = {}
+    for name, flags in KERNELS.items():
+        outs[name] = flash_attention_prefill(q.to(cuda_device), k.to(cuda_device), v.to(cuda_device),
+                                             cu.to(cuda_device), 1.0 / D ** 0.5, H, KVH, D, max_seqlen=max(lens),
+                                             flags=flags)
+        _check(outs[name], want)
+    # same arithmetic in the two tcgen05 kernels, and auto picked the pair kernel here (max_seqlen >= 2048)
+    assert torch.equal(outs["tcgen05_one_tile"], outs["tcgen05_pair"])
+    assert torch.equal(outs["auto"], outs["tcgen05_pair"])
+
+
+def test_prefill_kernel_choice_and_scale_sign(cuda_device):
+    """A non-positive scale cannot use the raw-score maximum of the tcgen05 kernels: the call falls
+    back to the mma.sync kernel and still matches the oracle."""
+    H, KVH, D = 4, 2, 64
+    g = torch.Generator().manual_seed(5)
+    lens = [300, 200]
+    total = sum(lens)
+    q = torch.randn(total, H, D, generator=g).to(torch.bfloat16)
+    k = torch.randn(total, KVH, D, generator=g).to(torch.bfloat16)
+    v = torch.randn(total, KVH, D, generator=g).to(torch.bfloat16)
+    cu = torch.tensor([0, 300, 500], dtype=torch.int32)
+    for scale in (-0.125, 0.0):
+        out = flash_attention_prefill(q.to(cuda_device), k.to(cuda_device), v.to(cuda_device), cu.to(cuda_device),
+                                      scale, H, KVH, D, max_seqlen=300)
+        _check(out, prefill_oracle.causal_varlen_attention(q, k, v, cu, scale, H, KVH, D))
