@@ -12,11 +12,13 @@ FLAGS = 1 if "--mma-sync" in sys.argv else 2 if "--single" in sys.argv else 4 if
 KERNEL = {0: "auto", 1: "flash_prefill_kernel (mma.sync)", 2: "flash_prefill_tcgen05_kernel", 4: "flash_prefill_tcgen05_pair_kernel"}[FLAGS]
 dev = torch.device("cuda", 0)
 peak = json.load(open("MEASURED_PEAKS.json"))["bf16_tflops"] if os.path.exists("MEASURED_PEAKS.json") else 1590.0
-H, KVH, D = 32, 8, 128
+H, KVH = 32, 8
+DT = torch.float16 if "--fp16" in sys.argv else torch.bfloat16
+D = 64 if "--d64" in sys.argv else 128
 for nseq, n in SIZES:
     T = nseq * n
-    q = torch.randn(T, H, D, device=dev).to(torch.bfloat16)
-    k = torch.randn(T, KVH, D, device=dev).to(torch.bfloat16)
+    q = torch.randn(T, H, D, device=dev).to(DT)
+    k = torch.randn(T, KVH, D, device=dev).to(DT)
     v = torch.randn_like(k)
     cu = torch.arange(0, T + 1, n, dtype=torch.int32, device=dev)
     run = lambda: flash_attention_prefill(q, k, v, cu, D ** -0.5, H, KVH, D, max_seqlen=n, flags=FLAGS)
@@ -39,5 +41,5 @@ for nseq, n in SIZES:
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 10
     flops = 4.0 * D * H * nseq * n * (n + 1) / 2
-    print(json.dumps({"kernel": KERNEL, "seqs": nseq, "len": n, "shape": f"{H}Q/{KVH}KV/D{D} bf16",
+    print(json.dumps({"kernel": KERNEL, "seqs": nseq, "len": n, "shape": f"{H}Q/{KVH}KV/D{D} " + ("fp16" if DT == torch.float16 else "bf16"),
                       "ms": ms, "TFLOPs": flops / ms / 1e9, "frac_of_measured_bf16_peak": flops / ms / 1e9 / peak}))
