@@ -135,8 +135,144 @@ __global__ void __launch_bounds__(256) qk_norm_rope_store_kernel(const PreAttnPa
   }
 }
 
+// Token-per-warp variant for large token counts (prefill).  The kernel above recomputes, for every
+// 256-byte row, the row -> (token, head) division, the slot and position look-ups and reloads the
+// 2 x 256 bytes of cos/sin that all rows of a token share; at 262,144 tokens that bookkeeping and
+// the L1 traffic of the table (twice the payload) held it to 73 % of the HBM peak.  Here a warp
+// owns a token: gamma lives in registers for the whole kernel, position / slot / cos / sin are
+// fetched once per token, and the token's H + 2 KVH rows stream through in groups of U x (32/LR)
+// rows with all 2U 128-bit loads of a lane issued before the first is used.
+template <typename T, int D, int U>
+__global__ void __launch_bounds__(256) qk_norm_rope_store_token_kernel(const PreAttnParams p) {
+  constexpr int VEC = Chunk<T>::VEC, NP = Chunk<T>::NP;
+  constexpr int HALF = D / 2, LR = HALF / VEC, RW = 32 / LR;
+  const int lane = threadIdx.x & 31, sub = lane / LR, l = lane % LR;
+  const int rows = p.H + 2 * p.KVH;
+  const long long nwarps = (long long)gridDim.x * 8;
+  const bool norm = p.gamma != nullptr, rope = p.cos_sin != nullptr;
+  float g1[VEC], g2[VEC];
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) {
+    g1[e] = norm ? __ldg(p.gamma + l * VEC + e) : 1.f;
+    g2[e] = norm ? __ldg(p.gamma + HALF + l * VEC + e) : 1.f;
+  }
+  for (long long t = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); t < p.num_tokens; t += nwarps) {
+    float cc[VEC], sn[VEC];
+    if (rope) {
+      long long pos = p.pos_is_i64 ? reinterpret_cast<const long long*>(p.positions)[t]
+                                   : (long long)reinterpret_cast<const int*>(p.positions)[t];
+      pos = pos < 0 ? 0 : (pos >= p.max_position ? p.max_position - 1 : pos);
+      const float* cs = p.cos_sin + pos * D + l * VEC;
+#pragma unroll
+      for (int e = 0; e < VEC; e += 4) {
+        const float4 c = __ldg(reinterpret_cast<const float4*>(cs + e));
+        const float4 s4 = __ldg(reinterpret_cast<const float4*>(cs + HALF + e));
+        cc[e] = c.x, cc[e + 1] = c.y, cc[e + 2] = c.z, cc[e + 3] = c.w;
+        sn[e] = s4.x, sn[e + 1] = s4.y, sn[e + 2] = s4.z, sn[e + 3] = s4.w;
+      }
+    }
+    long long slot = -1;
+    if (p.slots != nullptr) {
+      slot = p.slot_is_i64 ? reinterpret_cast<const long long*>(p.slots)[t]
+                           : (long long)reinterpret_cast<const int*>(p.slots)[t];
+      if (slot >= p.num_slots) slot = -1;  // -1: token has no slot (attention.py:29-30)
+    }
+    const T* qrow = reinterpret_cast<const T*>(p.q) + t * p.q_stride + l * VEC;
+    const T* krow = reinterpret_cast<const T*>(p.k) + t * p.k_stride + l * VEC;
+    const T* vrow = reinterpret_cast<const T*>(p.v) + t * p.v_stride + l * VEC;
+    T* qdst = reinterpret_cast<T*>(p.q_out) + t * p.H * D + l * VEC;
+    T* kdst = reinterpret_cast<T*>(p.k_cache) + slot * p.KVH * D + l * VEC;
+    T* vdst = reinterpret_cast<T*>(p.v_cache) + slot * p.KVH * D + l * VEC;
+    for (int r0 = 0; r0 < rows; r0 += RW * U) {
+      uint4 ra[U], rb[U];
+      T* dst[U];
+      int kind[U];  // 0 q, 1 k, 2 v, -1 nothing to do
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int r = r0 + u * RW + sub;
+        const T* src = qrow;
+        kind[u] = -1, dst[u] = nullptr;
+        if (r < p.H) {
+          kind[u] = 0, src = qrow + r * D, dst[u] = qdst + r * D;
+        } else if (r < rows && slot >= 0) {
+          const bool is_k = r < p.H + p.KVH;
+          const int head = is_k ? r - p.H : r - p.H - p.KVH;
+          kind[u] = is_k ? 1 : 2, src = (is_k ? krow : vrow) + head * D, dst[u] = (is_k ? kdst : vdst) + head * D;
+        }
+        ra[u] = rb[u] = make_uint4(0, 0, 0, 0);
+        if (kind[u] >= 0) {
+          ra[u] = __ldg(reinterpret_cast<const uint4*>(src));
+          rb[u] = __ldg(reinterpret_cast<const uint4*>(src + HALF));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        // every lane walks the same code (the RMS shuffles use the full mask and a group of rows can
+        // mix k and v rows); v rows and idle lanes discard the arithmetic
+        float a[VEC], b[VEC];
+        {
+          u64 pa[NP], pb[NP];
+          Chunk<T>::widen(ra[u], pa);
+          Chunk<T>::widen(rb[u], pb);
+#pragma unroll
+          for (int e = 0; e < NP; ++e) {
+            unpack2(pa[e], a[2 * e], a[2 * e + 1]);
+            unpack2(pb[e], b[2 * e], b[2 * e + 1]);
+          }
+        }
+        if (norm) {  // the shuffles run for every lane of the warp (rows with nothing to do carry zeros)
+          float ss = 0.f;
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) ss += a[e] * a[e] + b[e] * b[e];
+#pragma unroll
+          for (int o = LR / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+          const float inv = 1.0f / sqrtf(ss / (float)D + p.eps);
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) a[e] *= inv * g1[e], b[e] *= inv * g2[e];
+        }
+        if (rope) {
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) {
+            const float x1 = a[e], x2 = b[e];
+            a[e] = x1 * cc[e] - x2 * sn[e];
+            b[e] = x1 * sn[e] + x2 * cc[e];
+          }
+        }
+        if (kind[u] == 2) {  // v row: byte copy
+          *reinterpret_cast<uint4*>(dst[u]) = ra[u];
+          *reinterpret_cast<uint4*>(dst[u] + HALF) = rb[u];
+        } else if (kind[u] >= 0) {
+#pragma unroll
+          for (int e = 0; e < VEC; e += 4) {
+            store4<T>(dst[u] + e, a[e], a[e + 1], a[e + 2], a[e + 3]);
+            store4<T>(dst[u] + HALF + e, b[e], b[e + 1], b[e + 2], b[e + 3]);
+          }
+        }
+      }
+    }
+  }
+}
+
 template <typename T>
 static int launch_pre_t(const PreAttnParams& p, int head_dim, cudaStream_t s) {
+  if (p.num_tokens >= 8192) {  // enough tokens for a warp per token on every SM (8 warps x 8 blocks x 148)
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      return (int)cudaGetLastError();
+    int per_sm = 0;
+    if (head_dim == 64)
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, qk_norm_rope_store_token_kernel<T, 64, 4>, 256, 0);
+    else if (head_dim == 128)
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, qk_norm_rope_store_token_kernel<T, 128, 4>, 256, 0);
+    else
+      return -1000;
+    const long long want = (p.num_tokens + 7) / 8, cap = (long long)sms * (per_sm > 0 ? per_sm : 1);
+    const unsigned blocks = (unsigned)(want < cap ? want : cap);  // persistent: a warp strides over tokens
+    if (head_dim == 64) qk_norm_rope_store_token_kernel<T, 64, 4><<<blocks, 256, 0, s>>>(p);
+    else qk_norm_rope_store_token_kernel<T, 128, 4><<<blocks, 256, 0, s>>>(p);
+    return (int)cudaGetLastError();
+  }
   const long long rows = p.num_tokens * (p.H + 2 * p.KVH);
   const int rw = 32 / ((head_dim / 2) / Chunk<T>::VEC);  // rows per warp
   const unsigned blocks = (unsigned)((rows + 8 * rw - 1) / (8 * rw));

@@ -40,6 +40,6 @@ for n in (256, 4096, 65536, 262144):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / reps
     nbytes = 2 * n * (H + 2 * KVH) * D * 2 + n * (8 + 8) + n * D * 4
-    print(json.dumps({"kernel": "qk_norm_rope_store_kernel", "tokens": n, "shape": f"{H}Q/{KVH}KV/D{D} bf16",
+    print(json.dumps({"kernel": "qk_norm_rope_store_token_kernel" if n >= 8192 else "qk_norm_rope_store_kernel", "tokens": n, "shape": f"{H}Q/{KVH}KV/D{D} bf16",
                       "ms": ms, "algorithmic_bytes": nbytes, "GBps": nbytes / ms / 1e6,
                       "frac_of_measured_peak": nbytes / ms / 1e6 / peak}))

@@ -127,3 +127,48 @@ def test_attention_core_decode_step(cuda_device):
     err = (got - want).abs() - (4e-3 + 2.0 ** -7 * want.abs())   # two bf16 roundings (q, out) + k ulp flips
     assert err.max() <= 0
     assert torch.equal(core.attention.v_cache.cpu().view(torch.uint8), ovc.view(torch.uint8))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("D,norm", [(128, True), (64, True), (128, False)])
+def test_token_per_warp_kernel_equals_row_kernel(cuda_device, dtype, D, norm):
+    """From 8192 tokens the pass runs the token-per-warp kernel; in chunks below that size it runs the
+    row kernel.  Same fp32 operations in the same order -> bit-identical q and caches.  H + 2 KVH = 10
+    rows per token, so the groups of 4 rows a warp handles mix q, k and v rows; some tokens have no
+    slot.  The first tokens are also checked against the float64 oracle."""
+    H, KVH, N, BS = 6, 2, 8192 + 37, 16
+    g = torch.Generator().manual_seed(D + int(norm))
+    q = torch.randn(N, H, D, generator=g).to(dtype)
+    k = torch.randn(N, KVH, D, generator=g).to(dtype)
+    v = torch.randn(N, KVH, D, generator=g).to(dtype)
+    pos = torch.randint(0, 512, (N,), generator=g)
+    nb = (N + BS - 1) // BS + 2
+    slots = torch.randperm(nb * BS, generator=g)[:N]
+    slots[::97] = -1
+    gamma = (1 + 0.1 * torch.randn(D, generator=g)) if norm else None
+    table = pre.rope_table(1e4, D, 512)
+    dq, dk, dv, dpos, dslots = (x.to(cuda_device) for x in (q, k, v, pos, slots))
+    dgamma = gamma.to(cuda_device) if norm else None
+    dtable = table.to(cuda_device)
+
+    def run(chunk):
+        kc = torch.zeros(nb, BS, KVH, D, dtype=dtype, device=cuda_device)
+        vc = torch.zeros_like(kc)
+        outs = [fused_qk_norm_rope_store(dq[s:s + chunk], dk[s:s + chunk], dv[s:s + chunk], dpos[s:s + chunk],
+                                         dgamma, 1e-6, dtable, kc, vc, dslots[s:s + chunk])
+                for s in range(0, N, chunk)]
+        return torch.cat(outs), kc, vc
+
+    q1, kc1, vc1 = run(N)         # token-per-warp kernel
+    q2, kc2, vc2 = run(4096)      # row kernel
+    assert torch.equal(q1.view(torch.uint8), q2.view(torch.uint8))
+    assert torch.equal(kc1.view(torch.uint8), kc2.view(torch.uint8))
+    assert torch.equal(vc1.view(torch.uint8), vc2.view(torch.uint8))
+    M = 64
+    want_kc = torch.zeros(nb, BS, KVH, D, dtype=dtype)
+    want_vc = torch.zeros_like(want_kc)
+    q_want, _ = pre.pre_attention(q[:M], k[:M], v[:M], pos[:M], gamma, 1e-6, table, want_kc, want_vc, slots[:M])
+    _close(q1[:M], q_want, dtype)
+    keep = slots[:M][slots[:M] >= 0]
+    assert torch.equal(vc1.cpu().view(-1, KVH, D)[keep].view(torch.uint8),
+                       want_vc.view(-1, KVH, D)[keep].view(torch.uint8))
