@@ -194,6 +194,33 @@ int mvl_flash_prefill(void* out, const void* q, const void* k, const void* v, in
                       void* stream);
 
 /*
+ * mvl_flash_prefill_paged — prefill attention that also reads cached-prefix pages: what reference
+ * Attention.forward is handed when the block manager found a cached prefix (model_runner.py:209-215
+ * passes block_tables and cu_seqlens_k > cu_seqlens_q) but does not do (attention.py:514-525 attends
+ * over the new tokens only).  Sequence s has context_lens[s] keys in the paged caches —
+ * a cached prefix followed by its n_s = cu_seqlens_q[s+1] - cu_seqlens_q[s] new tokens, whose K/V the
+ * caller has already stored (mvl_store_kvcache / mvl_qk_norm_rope_store) — and query i of the
+ * sequence, at position context_lens[s] - n_s + i, sees keys 0 .. context_lens[s] - n_s + i:
+ *   out[cu_q[s] + i, h, :] = softmax_j( scale * <q[cu_q[s] + i, h], K_s[j, h/G]> ) @ V_s[j, h/G]
+ * with K_s[j] = k_cache.view(-1, KVH, D)[block_tables[s, j / block_size] * block_size + j % block_size].
+ * With no prefix (context_lens[s] == n_s) it equals mvl_flash_prefill on the same tokens.  It also
+ * serves chunked prefill (n_s new tokens of a longer prompt per call).
+ *   q (total_q_tokens, H, D) with a token stride; out (total_q_tokens, H, D) contiguous; caches
+ *   (num_blocks, block_size, KVH, D) contiguous, block_size a power of two >= 16; block_tables int32,
+ *   row stride block_table_stride, entries past a sequence's context unused (may be -1).
+ * tcgen05 kernels only: 16-bit dtypes, scale > 0 (MVL_ERR_SHAPE otherwise); flags as mvl_flash_prefill
+ * (MVL_PREFILL_ONE_TILE / MVL_PREFILL_PAIR).  Page rows past a sequence's context inside its last
+ * page are multiplied by zero probabilities: the cache must hold finite values there (allocate it
+ * zeroed, as the engine does).
+ */
+int mvl_flash_prefill_paged(void* out, const void* q, int64_t q_token_stride, int64_t total_q_tokens,
+                            const int32_t* cu_seqlens_q, const void* k_cache, const void* v_cache,
+                            const int32_t* block_tables, int64_t block_table_stride,
+                            const void* context_lens, int ctx_is_i64, int num_seqs, int max_seqlen_q,
+                            int num_heads, int num_kv_heads, int head_dim, int block_size,
+                            int64_t num_blocks, float scale, int elem_dtype, unsigned flags, void* stream);
+
+/*
  * mvl_qk_norm_rope_store — q/k RMSNorm + rotary embedding + KV-cache write in one pass over the
  * projections' output.  Replaces, per layer, reference models/qwen3.py:104-108 (rms_norm on q and k,
  * layers/layernorm.py:13-15: x / sqrt(mean(x^2) + eps) * gamma; rotary_emb, layers/

@@ -38,6 +38,8 @@ PROTOTYPES = {
                                     _i, _i, _i, _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
     "mvl_flash_prefill": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp, _i, _i, _i, _i, _i, _f, _i, _u,
                                _vp]),
+    "mvl_flash_prefill_paged": (_i, [_vp, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _i64, _vp, _i, _i, _i, _i, _i, _i,
+                                     _i, _i64, _f, _i, _u, _vp]),
     "mvl_qk_norm_rope_store": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _f, _vp, _i64, _vp, _i,
                                     _vp, _vp, _vp, _i, _i64, _i64, _i, _i, _i, _i, _vp]),
     "mvl_decode_step": (_i, [_vp] * 9 + [_i, _i64, _i64, _i64, _i64, _i64, _i, _i, _i, _i, _i64, _f, _i,

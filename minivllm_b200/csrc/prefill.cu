@@ -247,6 +247,8 @@ extern "C" int mvl_flash_prefill(void* out, const void* q, const void* k, const 
   p.out = out; p.q = q; p.k = k; p.v = v; p.cu_seqlens = cu_seqlens;
   p.q_stride = q_token_stride; p.k_stride = k_token_stride; p.v_stride = v_token_stride;
   p.total_tokens = total_tokens;
+  p.block_tables = nullptr; p.bt_stride = 0; p.context_lens = nullptr; p.ctx_is_i64 = 0;
+  p.bs_shift = 0; p.piece_rows = 128; p.num_slots = 0;
   p.H = num_heads; p.KVH = num_kv_heads;
   p.qscale = scale * 1.4426950408889634f;
   cudaStream_t s = (cudaStream_t)stream;
@@ -266,4 +268,45 @@ extern "C" int mvl_flash_prefill(void* out, const void* q, const void* k, const 
     e = head_dim == 64 ? mvl::launch_prefill_td<__half, 64>(p, num_seqs, max_seqlen, s)
                        : mvl::launch_prefill_td<__half, 128>(p, num_seqs, max_seqlen, s);
   return e == 0 ? 0 : mvl::fail_cuda(e, "flash_prefill launch");
+}
+
+extern "C" int mvl_flash_prefill_paged(void* out, const void* q, int64_t q_token_stride, int64_t total_q_tokens,
+                                       const int32_t* cu_seqlens_q, const void* k_cache, const void* v_cache,
+                                       const int32_t* block_tables, int64_t block_table_stride,
+                                       const void* context_lens, int ctx_is_i64, int num_seqs,
+                                       int max_seqlen_q, int num_heads, int num_kv_heads, int head_dim,
+                                       int block_size, int64_t num_blocks, float scale, int elem_dtype,
+                                       unsigned flags, void* stream) {
+  if (elem_dtype != 1 && elem_dtype != 2) return -2;  // MVL_ERR_DTYPE
+  if (total_q_tokens < 0 || num_seqs < 0 || max_seqlen_q < 0 || num_heads <= 0 || num_kv_heads <= 0 ||
+      num_heads % num_kv_heads || num_blocks <= 0)
+    return -3;
+  if (head_dim != 64 && head_dim != 128) return -3;
+  if (block_size < 16 || (block_size & (block_size - 1))) return -3;  // pages of 2^k >= 16 slots
+  if (!(scale > 0.f)) return -3;                                       // tcgen05 kernels only: raw-score maximum
+  if (num_seqs == 0 || max_seqlen_q == 0 || total_q_tokens == 0) return 0;
+  if (num_seqs > 65535 || num_heads > 65535) return -7;
+  if (total_q_tokens >= (1ll << 31) || num_blocks * block_size >= (1ll << 31) - 256) return -7;
+  if (!out || !q || !k_cache || !v_cache || !cu_seqlens_q || !block_tables || !context_lens) return -1;
+  if (q_token_stride < (int64_t)num_heads * head_dim) return -3;
+  const uintptr_t bits = (uintptr_t)out | (uintptr_t)q | (uintptr_t)k_cache | (uintptr_t)v_cache |
+                         (uintptr_t)(q_token_stride * 2);
+  if (bits & 15u) return -4;
+  mvl::PrefillParams p;
+  p.out = out; p.q = q; p.k = k_cache; p.v = v_cache; p.cu_seqlens = cu_seqlens_q;
+  p.q_stride = q_token_stride;
+  p.k_stride = p.v_stride = (long long)num_kv_heads * head_dim;
+  p.total_tokens = total_q_tokens;
+  p.block_tables = block_tables; p.bt_stride = block_table_stride;
+  p.context_lens = context_lens; p.ctx_is_i64 = ctx_is_i64 ? 1 : 0;
+  int shift = 0;
+  while ((1 << shift) < block_size) ++shift;
+  p.bs_shift = shift;
+  p.piece_rows = block_size < 128 ? block_size : 128;
+  p.num_slots = (int)(num_blocks * block_size);
+  p.H = num_heads; p.KVH = num_kv_heads;
+  p.qscale = scale * 1.4426950408889634f;
+  const bool single = (flags & 2u) || (!(flags & 4u) && max_seqlen_q < 2048);
+  return mvl::launch_prefill_tcgen05(p, elem_dtype, head_dim, num_seqs, max_seqlen_q, single,
+                                     (cudaStream_t)stream);
 }

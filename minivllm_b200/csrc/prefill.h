@@ -15,6 +15,15 @@ struct PrefillParams {
   long long total_tokens;
   int H, KVH;
   float qscale;       // scale * log2(e)
+  // paged variant (mvl_flash_prefill_paged): k / v are the paged caches, keys 0..ctx-1 of a sequence
+  // are found through its block-table row, the n new queries sit at positions ctx-n..ctx-1
+  const int* block_tables;  // nullptr: dense variant
+  long long bt_stride;
+  const void* context_lens;
+  int ctx_is_i64;
+  int bs_shift;             // log2(block_size)
+  int piece_rows;           // min(block_size, 128): slots fetched by one TMA box
+  int num_slots;            // num_blocks * block_size (also the out-of-range coordinate that reads zeros)
 };
 
 // Tensor map over a packed (tokens, heads, D) 16-bit tensor with a token stride: box = 64 elements
@@ -28,6 +37,7 @@ int fail_text(const char* where, int code);
 int fail_cuda(int cuda_error, const char* where);
 
 // tcgen05 kernel (bf16 / fp16, D in {64, 128}); returns MVL_OK or MVL_ERR_CUDA (text recorded).
+// Paged variant: p.block_tables != nullptr, p.k / p.v are the caches (num_slots, KVH, D).
 int launch_prefill_tcgen05(const PrefillParams& p, int dtype, int head_dim, int num_seqs, int max_seqlen,
                            bool single_tile, cudaStream_t s);
 

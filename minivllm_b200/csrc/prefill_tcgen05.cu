@@ -47,22 +47,22 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
   return d;
 }
 
-// One softmax step of one query row (thread = row = TMEM lane): S row -> registers, causal mask on the
-// diagonal tile (key c visible iff c <= t), lazy maximum (O rescaled in TMEM only when the row maximum
+// One softmax step of one query row (thread = row = TMEM lane): S row -> registers, causal mask (key
+// column c of this tile is visible iff c <= lim; lim >= 127: nothing to mask), lazy maximum (O rescaled in TMEM only when the row maximum
 // grew by more than 2^8), P = exp2((S - m_ref) * qs) packed to 16 bits over the first 64 S columns.
 // Ends with tcgen05.wait::st: the caller fences and signals.
 template <typename T, int D>
-__device__ __forceinline__ void softmax_step(uint32_t s_addr, uint32_t o_addr, bool first, bool diag, int t,
-                                             float qs, float& m_ref, float& l) {
+__device__ __forceinline__ void softmax_step(uint32_t s_addr, uint32_t o_addr, bool first, int lim, float qs,
+                                             float& m_ref, float& l) {
   using M = MmaType<T>;
   uint32_t su[128];
 #pragma unroll
   for (int c = 0; c < 4; ++c) tc5::tmem_ld32(s_addr + c * 32, su + c * 32);
   tc5::tmem_wait_ld();
-  if (diag) {
+  if (lim < 127) {
 #pragma unroll
     for (int c = 0; c < 128; ++c)
-      if (c > t) su[c] = 0xff800000u;
+      if (c > lim) su[c] = 0xff800000u;
   }
   float mxa[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four chains: the row maximum is latency-bound
 #pragma unroll
@@ -134,7 +134,70 @@ __device__ __forceinline__ void store_row(uint32_t o_addr, T* out, float inv, bo
   }
 }
 
-template <typename T, int D>
+// Which keys a CTA's queries see.  Dense (mvl_flash_prefill): a sequence's n new tokens attend to
+// each other, query i to keys 0..i.  Paged (mvl_flash_prefill_paged): the sequence has ctx >= n keys
+// in the paged cache (a cached prefix of ctx - n tokens, then the n new ones, already stored); query i
+// sits at position ctx - n + i and sees keys 0..ctx - n + i.
+struct SeqGeom {
+  int q_start, n_new, ctx, prefix;
+};
+template <bool PAGED>
+__device__ __forceinline__ SeqGeom seq_geom(const PrefillParams& p, int seq) {
+  SeqGeom g;
+  g.q_start = p.cu_seqlens[seq];
+  g.n_new = p.cu_seqlens[seq + 1] - g.q_start;
+  g.ctx = g.n_new;
+  if (PAGED) {
+    g.ctx = p.ctx_is_i64 ? (int)reinterpret_cast<const long long*>(p.context_lens)[seq]
+                         : reinterpret_cast<const int*>(p.context_lens)[seq];
+    if (g.ctx < g.n_new) g.ctx = g.n_new;
+  }
+  g.prefix = g.ctx - g.n_new;
+  return g;
+}
+// Key tiles a 128-query tile starting at absolute position qa0 needs: through the tile of its last row.
+__device__ __forceinline__ int key_tiles(int qa0, int ctx) { return min((qa0 + 127) / 128 + 1, (ctx + 127) >> 7); }
+
+// TMA loads of key tile j (128 keys x D) into a 128-byte-swizzled shared-memory tile.  Dense: 128
+// consecutive tokens of the packed tensor.  Paged: 128 / piece_rows boxes of piece_rows slots each,
+// located through the block-table row; a piece past the context or with a negative table entry is
+// requested at slot = num_slots, outside the tensor map, which the TMA unit fills with zeros (and
+// still counts as bytes on the barrier).  slots[] is filled by kv_slots once per tile, used for K and V.
+template <int D, bool PAGED>
+__device__ __forceinline__ void kv_slots(const PrefillParams& p, const SeqGeom& g, const int* table, int j,
+                                         int (&slots)[8]) {
+  if (!PAGED) {
+    slots[0] = g.q_start + j * 128;
+    return;
+  }
+  const int pieces = 128 / p.piece_rows;
+  for (int pc = 0; pc < pieces; ++pc) {
+    const int key0 = j * 128 + pc * p.piece_rows;
+    int slot = p.num_slots;
+    if (key0 < g.ctx) {
+      const int e = __ldg(table + (key0 >> p.bs_shift));
+      if (e >= 0) slot = (e << p.bs_shift) | (key0 & ((1 << p.bs_shift) - 1));
+    }
+    slots[pc] = slot;
+  }
+}
+template <int D, bool PAGED>
+__device__ __forceinline__ void kv_load(const PrefillParams& p, const CUtensorMap* map, uint32_t dst, int head,
+                                        const int (&slots)[8], uint32_t bar) {
+  constexpr int PANELS = D / 64, PANEL_BYTES = 128 * 128;
+  if (!PAGED) {
+#pragma unroll
+    for (int pn = 0; pn < PANELS; ++pn) tma_load_3d(dst + pn * PANEL_BYTES, map, pn * 64, head, slots[0], bar);
+    return;
+  }
+  const int pieces = 128 / p.piece_rows;
+  for (int pc = 0; pc < pieces; ++pc)
+#pragma unroll
+    for (int pn = 0; pn < PANELS; ++pn)
+      tma_load_3d(dst + pn * PANEL_BYTES + pc * p.piece_rows * 128, map, pn * 64, head, slots[pc], bar);
+}
+
+template <typename T, int D, bool PAGED>
 __global__ void __launch_bounds__(128, 2)
 flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
                              const __grid_constant__ CUtensorMap mv, const PrefillParams p) {
@@ -152,11 +215,12 @@ flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __gri
   const int mb = gridDim.x - 1 - blockIdx.x;  // heaviest (latest) query tiles first
   const int h = blockIdx.y, seq = blockIdx.z;
   const int kvh = h / (p.H / p.KVH);
-  const int seq_start = p.cu_seqlens[seq];
-  const int seq_len = p.cu_seqlens[seq + 1] - seq_start;
+  const SeqGeom g = seq_geom<PAGED>(p, seq);
   const int m0 = mb * C::BM;
-  if (m0 >= seq_len) return;
-  const int ntiles = mb + 1;  // key tiles 0..mb; the last one holds the diagonal
+  if (m0 >= g.n_new) return;
+  const int qa0 = g.prefix + m0;              // absolute position of the tile's first query
+  const int ntiles = key_tiles(qa0, g.ctx);   // the last one or two hold the causal diagonal
+  const int* table = PAGED ? p.block_tables + (long long)seq * p.bt_stride : nullptr;
 
   if (warp == 0) {
     tc5::tmem_alloc(tmem_slot, C::TMEM_COLS);
@@ -172,10 +236,10 @@ flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __gri
   const uint32_t tmem = lds_u32(tmem_slot);
   const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
 
-  auto load_tile = [&](const CUtensorMap* map, uint32_t dst, int head, int token, uint32_t bar) {
+  int slots[8];
+  auto load_kv = [&](const CUtensorMap* map, uint32_t dst, uint32_t bar) {
     mbar_expect_tx(bar, C::TILE_BYTES);
-#pragma unroll
-    for (int pn = 0; pn < C::PANELS; ++pn) tma_load_3d(dst + pn * C::PANEL_BYTES, map, pn * 64, head, token, bar);
+    kv_load<D, PAGED>(p, map, dst, kvh, slots, bar);
   };
   constexpr uint32_t HI = tc5::smem_desc_hi_sw128(1024);
   const uint32_t q_lo = tc5::smem_desc_lo(sQ, 16), k_lo = tc5::smem_desc_lo(sK, 16),
@@ -197,9 +261,13 @@ flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __gri
   };
 
   if (tid == 0) {
-    load_tile(&mq, sQ, h, seq_start + m0, bar_q);
-    load_tile(&mk, sK, kvh, seq_start, bar_k);
-    load_tile(&mv, sV, kvh, seq_start, bar_v);
+    mbar_expect_tx(bar_q, C::TILE_BYTES);
+#pragma unroll
+    for (int pn = 0; pn < C::PANELS; ++pn)
+      tma_load_3d(sQ + pn * C::PANEL_BYTES, &mq, pn * 64, h, g.q_start + m0, bar_q);
+    kv_slots<D, PAGED>(p, g, table, 0, slots);
+    load_kv(&mk, sK, bar_k);
+    load_kv(&mv, sV, bar_v);
     tc5::mbar_wait_bounded(bar_q, 0);
     tc5::mbar_wait_bounded(bar_k, 0);
     tc5::fence_after_sync();
@@ -212,10 +280,13 @@ flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __gri
     tc5::mbar_wait_bounded(bar_s, j & 1);  // S_j is complete, and so is every MMA issued before it
     tc5::fence_after_sync();
     if (tid == 0) {
-      if (j > 0) load_tile(&mv, sV, kvh, seq_start + j * C::BN, bar_v);               // product j-1 has retired
-      if (j + 1 < ntiles) load_tile(&mk, sK, kvh, seq_start + (j + 1) * C::BN, bar_k);  // S_j no longer reads K_j
+      if (j > 0) load_kv(&mv, sV, bar_v);  // product j-1 has retired; slots[] still describes tile j
+      if (j + 1 < ntiles) {                // S_j no longer reads K_j
+        kv_slots<D, PAGED>(p, g, table, j + 1, slots);
+        load_kv(&mk, sK, bar_k);
+      }
     }
-    softmax_step<T, D>(lane_base, lane_base + C::O_COL, j == 0, j == ntiles - 1, tid, qs, m_ref, l);
+    softmax_step<T, D>(lane_base, lane_base + C::O_COL, j == 0, qa0 + tid - j * 128, qs, m_ref, l);
     tc5::fence_before_sync();
     __syncthreads();  // every row of P_j (and any rescaled O) is in TMEM
     if (tid == 0) {
@@ -234,8 +305,8 @@ flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __gri
 
   // ---- O / l -> out: thread t writes row m0 + t
   const int row = m0 + tid;
-  store_row<T, D>(lane_base + C::O_COL, reinterpret_cast<T*>(p.out) + ((long long)(seq_start + row) * p.H + h) * D,
-                  1.f / l, row < seq_len);
+  store_row<T, D>(lane_base + C::O_COL, reinterpret_cast<T*>(p.out) + ((long long)(g.q_start + row) * p.H + h) * D,
+                  1.f / l, row < g.n_new);
   tc5::fence_before_sync();
   __syncthreads();
   if (warp == 0) tc5::tmem_dealloc(tmem, C::TMEM_COLS);
@@ -260,7 +331,7 @@ struct PairCfg {
   static constexpr int TMEM_COLS = 512;  // S0 [0,128) S1 [128,256) O0 [256,256+D) O1 [256+D, 256+2D)
 };
 
-template <typename T, int D>
+template <typename T, int D, bool PAGED>
 __global__ void __launch_bounds__(384, 1)
 flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const __grid_constant__ CUtensorMap mk,
                                   const __grid_constant__ CUtensorMap mv, const PrefillParams p) {
@@ -279,13 +350,13 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
   const int mb2 = gridDim.x - 1 - blockIdx.x;  // heaviest (latest) query tiles first
   const int h = blockIdx.y, seq = blockIdx.z;
   const int kvh = h / (p.H / p.KVH);
-  const int seq_start = p.cu_seqlens[seq];
-  const int seq_len = p.cu_seqlens[seq + 1] - seq_start;
+  const SeqGeom g = seq_geom<PAGED>(p, seq);
   const int m0 = mb2 * 256;
-  if (m0 >= seq_len) return;
-  const int n0 = 2 * mb2 + 1;                           // key tiles of query tile 0 (last = its diagonal)
-  const int n1 = m0 + 128 < seq_len ? n0 + 1 : 0;       // query tile 1, if the sequence reaches it
-  const int n = n1 ? n1 : n0;
+  if (m0 >= g.n_new) return;
+  const int qa0 = g.prefix + m0;                                        // absolute position of query tile 0
+  const int n0 = key_tiles(qa0, g.ctx);                                 // key tiles of query tile 0
+  const int n1 = m0 + 128 < g.n_new ? key_tiles(qa0 + 128, g.ctx) : 0;  // query tile 1, if the sequence reaches it
+  const int n = n1 ? n1 : n0;                                           // n1 >= n0 when tile 1 is live
 
   if (warp == 8) {
     tc5::tmem_alloc(tmem_slot, C::TMEM_COLS);
@@ -312,22 +383,23 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
     if (tid == 288) {
       // ---- TMA thread: Q once, then K_j / V_j into stage j & 1 as soon as the products that read
       // the previous occupant (tile j - 2) have retired (k_empty / v_empty, signalled by tcgen05.commit)
-      auto load_tile = [&](const CUtensorMap* map, uint32_t dst, int head, int token, uint32_t bar) {
-#pragma unroll
-        for (int pn = 0; pn < C::PANELS; ++pn)
-          tma_load_3d(dst + pn * C::PANEL_BYTES, map, pn * 64, head, token, bar);
-      };
+      const int* table = PAGED ? p.block_tables + (long long)seq * p.bt_stride : nullptr;
       mbar_expect_tx(q_full, (n1 ? 2 : 1) * C::TILE_BYTES);
-      load_tile(&mq, sQ, h, seq_start + m0, q_full);
-      if (n1) load_tile(&mq, sQ + C::TILE_BYTES, h, seq_start + m0 + 128, q_full);
+#pragma unroll
+      for (int pn = 0; pn < C::PANELS; ++pn) {
+        tma_load_3d(sQ + pn * C::PANEL_BYTES, &mq, pn * 64, h, g.q_start + m0, q_full);
+        if (n1) tma_load_3d(sQ + C::TILE_BYTES + pn * C::PANEL_BYTES, &mq, pn * 64, h, g.q_start + m0 + 128, q_full);
+      }
       for (int j = 0; j < n; ++j) {
         const int st = j & 1;
+        int slots[8];
+        kv_slots<D, PAGED>(p, g, table, j, slots);
         if (j >= 2) tc5::mbar_wait_bounded(k_empty + 8 * st, ((j >> 1) - 1) & 1);
         mbar_expect_tx(k_full + 8 * st, C::TILE_BYTES);
-        load_tile(&mk, sK + st * C::TILE_BYTES, kvh, seq_start + j * 128, k_full + 8 * st);
+        kv_load<D, PAGED>(p, &mk, sK + st * C::TILE_BYTES, kvh, slots, k_full + 8 * st);
         if (j >= 2) tc5::mbar_wait_bounded(v_empty + 8 * st, ((j >> 1) - 1) & 1);
         mbar_expect_tx(v_full + 8 * st, C::TILE_BYTES);
-        load_tile(&mv, sV + st * C::TILE_BYTES, kvh, seq_start + j * 128, v_full + 8 * st);
+        kv_load<D, PAGED>(p, &mv, sV + st * C::TILE_BYTES, kvh, slots, v_full + 8 * st);
       }
     } else if (tid == 256) {
       // ---- MMA thread
@@ -404,7 +476,7 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
     for (int j = 0; j < nw; ++j) {
       tc5::mbar_wait_bounded(s_full + 8 * w, j & 1);  // S_w(j) complete; so is the product of step j-1
       tc5::fence_after_sync();
-      softmax_step<T, D>(s_addr, o_addr, j == 0, j == nw - 1, t, qs, m_ref, l);
+      softmax_step<T, D>(s_addr, o_addr, j == 0, qa0 + w * 128 + t - j * 128, qs, m_ref, l);
       tc5::fence_before_sync();
       tc5::mbar_arrive(p_ready + 8 * w);
     }
@@ -412,8 +484,8 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
       tc5::mbar_wait_bounded(o_done + 8 * w, 0);
       tc5::fence_after_sync();
       const int row = m0 + w * 128 + t;
-      store_row<T, D>(o_addr, reinterpret_cast<T*>(p.out) + ((long long)(seq_start + row) * p.H + h) * D, 1.f / l,
-                      row < seq_len);
+      store_row<T, D>(o_addr, reinterpret_cast<T*>(p.out) + ((long long)(g.q_start + row) * p.H + h) * D, 1.f / l,
+                      row < g.n_new);
     }
   }
   tc5::fence_before_sync();
@@ -421,11 +493,11 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
   if (warp == 8) tc5::tmem_dealloc(tmem, C::TMEM_COLS);
 }
 
-template <typename T, int D>
+template <typename T, int D, bool PAGED>
 int launch_pair_td(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const PrefillParams& p,
                    int num_seqs, int max_seqlen, cudaStream_t s) {
   using C = PairCfg<D>;
-  auto kern = flash_prefill_tcgen05_pair_kernel<T, D>;
+  auto kern = flash_prefill_tcgen05_pair_kernel<T, D, PAGED>;
   static bool configured[64] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -440,11 +512,11 @@ int launch_pair_td(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorM
   return (int)cudaGetLastError();
 }
 
-template <typename T, int D>
+template <typename T, int D, bool PAGED>
 int launch_td(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const PrefillParams& p,
               int num_seqs, int max_seqlen, cudaStream_t s) {
   using C = Tc5Cfg<D>;
-  auto kern = flash_prefill_tcgen05_kernel<T, D>;
+  auto kern = flash_prefill_tcgen05_kernel<T, D, PAGED>;
   static bool configured[64] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -459,31 +531,40 @@ int launch_td(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& m
   return (int)cudaGetLastError();
 }
 
+template <typename T, int D>
+int launch_any(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const PrefillParams& p,
+               int num_seqs, int max_seqlen, bool single_tile, cudaStream_t s) {
+  const bool paged = p.block_tables != nullptr;
+  if (single_tile)
+    return paged ? launch_td<T, D, true>(mq, mk, mv, p, num_seqs, max_seqlen, s)
+                 : launch_td<T, D, false>(mq, mk, mv, p, num_seqs, max_seqlen, s);
+  return paged ? launch_pair_td<T, D, true>(mq, mk, mv, p, num_seqs, max_seqlen, s)
+               : launch_pair_td<T, D, false>(mq, mk, mv, p, num_seqs, max_seqlen, s);
+}
+
 }  // namespace
 
 int launch_prefill_tcgen05(const PrefillParams& p, int dtype, int head_dim, int num_seqs, int max_seqlen,
                            bool single_tile, cudaStream_t s) {
+  const bool paged = p.block_tables != nullptr;
+  // K / V source: the packed (T, KVH, D) tensors, or the paged caches (num_slots, KVH, D) in boxes of
+  // piece_rows slots
+  const long long kv_rows = paged ? p.num_slots : p.total_tokens;
+  const int kv_box = paged ? p.piece_rows : 128;
   CUtensorMap mq, mk, mv;
   int r;
   if ((r = make_packed_map(&mq, p.q, dtype, head_dim, p.H, p.total_tokens, p.q_stride, 128)) != 0)
     return fail_text("prefill tensor map (q)", r);
-  if ((r = make_packed_map(&mk, p.k, dtype, head_dim, p.KVH, p.total_tokens, p.k_stride, 128)) != 0)
+  if ((r = make_packed_map(&mk, p.k, dtype, head_dim, p.KVH, kv_rows, p.k_stride, kv_box)) != 0)
     return fail_text("prefill tensor map (k)", r);
-  if ((r = make_packed_map(&mv, p.v, dtype, head_dim, p.KVH, p.total_tokens, p.v_stride, 128)) != 0)
+  if ((r = make_packed_map(&mv, p.v, dtype, head_dim, p.KVH, kv_rows, p.v_stride, kv_box)) != 0)
     return fail_text("prefill tensor map (v)", r);
-  if (!single_tile) {
-    if (dtype == 2)
-      r = head_dim == 64 ? launch_pair_td<__nv_bfloat16, 64>(mq, mk, mv, p, num_seqs, max_seqlen, s)
-                         : launch_pair_td<__nv_bfloat16, 128>(mq, mk, mv, p, num_seqs, max_seqlen, s);
-    else
-      r = head_dim == 64 ? launch_pair_td<__half, 64>(mq, mk, mv, p, num_seqs, max_seqlen, s)
-                         : launch_pair_td<__half, 128>(mq, mk, mv, p, num_seqs, max_seqlen, s);
-  } else if (dtype == 2)
-    r = head_dim == 64 ? launch_td<__nv_bfloat16, 64>(mq, mk, mv, p, num_seqs, max_seqlen, s)
-                       : launch_td<__nv_bfloat16, 128>(mq, mk, mv, p, num_seqs, max_seqlen, s);
+  if (dtype == 2)
+    r = head_dim == 64 ? launch_any<__nv_bfloat16, 64>(mq, mk, mv, p, num_seqs, max_seqlen, single_tile, s)
+                       : launch_any<__nv_bfloat16, 128>(mq, mk, mv, p, num_seqs, max_seqlen, single_tile, s);
   else
-    r = head_dim == 64 ? launch_td<__half, 64>(mq, mk, mv, p, num_seqs, max_seqlen, s)
-                       : launch_td<__half, 128>(mq, mk, mv, p, num_seqs, max_seqlen, s);
+    r = head_dim == 64 ? launch_any<__half, 64>(mq, mk, mv, p, num_seqs, max_seqlen, single_tile, s)
+                       : launch_any<__half, 128>(mq, mk, mv, p, num_seqs, max_seqlen, single_tile, s);
   return r == 0 ? 0 : fail_cuda(r, "flash_prefill_tcgen05 launch");
 }
 

@@ -258,6 +258,54 @@ def flash_attention_prefill(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, c
     return out
 
 
+def flash_attention_prefill_paged(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                                  cu_seqlens_q: torch.Tensor, block_tables: torch.Tensor,
+                                  context_lens: torch.Tensor, scale: float, num_heads: int, num_kv_heads: int,
+                                  head_dim: int, block_size: int, *, max_seqlen_q: Optional[int] = None,
+                                  flags: int = 0) -> torch.Tensor:
+    """Prefill attention over the paged cache: the ``n_s`` new queries of sequence ``s`` (packed in
+    ``q`` and delimited by ``cu_seqlens_q``) attend causally to all ``context_lens[s]`` keys of the
+    sequence — a cached prefix plus the new tokens, whose K/V must already be in the cache.  This is
+    what the reference's prefill branch is handed when a prefix was cached (``block_tables`` set,
+    ``cu_seqlens_k > cu_seqlens_q``, model_runner.py:209-215) and does not do (attention.py:514-525,
+    SURVEY.md A-8); it also serves chunked prefill.  bf16 / fp16, ``scale > 0``.  Returns
+    (total_q_tokens, num_heads, head_dim)."""
+    dev = _need_cuda(q=q, k_cache=k_cache, v_cache=v_cache, cu_seqlens_q=cu_seqlens_q,
+                     block_tables=block_tables, context_lens=context_lens)
+    if q.dim() != 3 or q.shape[1:] != (num_heads, head_dim):
+        raise ValueError("q must be (total_q_tokens, num_heads, head_dim)")
+    if k_cache.dim() != 4 or k_cache.shape != v_cache.shape or k_cache.shape[1:] != (
+            block_size, num_kv_heads, head_dim) or not (k_cache.is_contiguous() and v_cache.is_contiguous()):
+        raise ValueError("caches must be contiguous (num_blocks, block_size, num_kv_heads, head_dim)")
+    if q.dtype not in (torch.bfloat16, torch.float16) or k_cache.dtype != q.dtype or v_cache.dtype != q.dtype:
+        raise NotImplementedError("prefill attention runs on the tensor cores: bf16 or fp16 only")
+    if not scale > 0:
+        raise ValueError("paged prefill needs scale > 0")
+    total, H, D = q.shape
+    dense = q.stride(2) == 1 and q.stride(1) == D and (total <= 1 or q.stride(0) >= H * D)
+    q = q if dense else q.contiguous()
+    qs = q.stride(0) if total > 1 else H * D
+    cu = cu_seqlens_q.to(torch.int32).contiguous()
+    num_seqs = cu.numel() - 1
+    if block_tables.dim() != 2 or block_tables.shape[0] != num_seqs or context_lens.numel() != num_seqs:
+        raise ValueError("block_tables (num_seqs, max_blocks) and context_lens (num_seqs,) must match cu_seqlens_q")
+    bt = block_tables if block_tables.dtype == torch.int32 and block_tables.stride(1) == 1 else \
+        block_tables.to(torch.int32).contiguous()
+    ctx = context_lens.contiguous()
+    out = torch.empty((total, H, D), dtype=q.dtype, device=dev)
+    if total == 0 or num_seqs <= 0:
+        return out
+    if max_seqlen_q is None:
+        max_seqlen_q = int((cu[1:] - cu[:-1]).max())
+    with _on_device(dev):
+        _ext.check(_ext.lib().mvl_flash_prefill_paged(
+            out.data_ptr(), q.data_ptr(), qs, total, cu.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+            bt.data_ptr(), bt.stride(0), ctx.data_ptr(), _index_flag("context_lens", ctx), num_seqs,
+            int(max_seqlen_q), H, num_kv_heads, D, block_size, k_cache.shape[0], float(scale), _dtype_code(q),
+            int(flags), _stream_ptr(dev)))
+    return out
+
+
 def decode_step(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor,
                 v_cache: torch.Tensor, slot_mapping: torch.Tensor, block_tables: torch.Tensor,
                 context_lens: torch.Tensor, scale: float, num_heads: int, num_kv_heads: int,
@@ -338,6 +386,20 @@ class Attention(nn.Module):
                                           "flash_attention_batched here (attention.py:528)")
             if context.cu_seqlens_q is None:
                 raise ValueError("cu_seqlens_q must be provided for varlen attention")
+            if context.block_tables is not None and has_cache:
+                # a prefix of these prompts is already cached (model_runner.py:209-215): attend over
+                # the pages — cached prefix + the rows just stored — not over the new tokens only
+                if context.context_lens is not None:
+                    ctx_lens = context.context_lens
+                elif context.cu_seqlens_k is not None:
+                    ctx_lens = (context.cu_seqlens_k[1:] - context.cu_seqlens_k[:-1]).to(torch.int32)
+                else:
+                    raise ValueError("prefill over cached pages needs cu_seqlens_k (or context_lens)")
+                o = flash_attention_prefill_paged(q, k_cache, v_cache, context.cu_seqlens_q,
+                                                  context.block_tables, ctx_lens, scale, self.num_heads,
+                                                  self.num_kv_heads, self.head_dim, block_size,
+                                                  max_seqlen_q=context.max_seqlen_q or None)
+                return o.reshape(o.shape[0], self.num_heads * self.head_dim)
             o = flash_attention_prefill(q, k, v, context.cu_seqlens_q, scale, self.num_heads,
                                         self.num_kv_heads, self.head_dim,
                                         max_seqlen=context.max_seqlen_q or None)

@@ -164,3 +164,82 @@ def test_prefill_kernel_choice_and_scale_sign(cuda_device):
         out = flash_attention_prefill(q.to(cuda_device), k.to(cuda_device), v.to(cuda_device), cu.to(cuda_device),
                                       scale, H, KVH, D, max_seqlen=300)
         _check(out, prefill_oracle.causal_varlen_attention(q, k, v, cu, scale, H, KVH, D))
+
+
+# ------------------------------------------------------------------ prefill over cached pages (N3 / A-8)
+from minivllm_b200.layers.attention import flash_attention_prefill_paged  # noqa: E402
+from test_oracle_golden import _paged_case  # noqa: E402
+
+PAGED_KERNELS = {"auto": 0, "tcgen05_one_tile": 2, "tcgen05_pair": 4}
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("BS", [16, 64, 256])
+@pytest.mark.parametrize("D", [64, 128])
+def test_paged_prefill_with_cached_prefix(cuda_device, dtype, BS, D):
+    """New queries over the paged cache (cached prefix + their own K/V already stored): prefixes that
+    are page-aligned or not, shorter and longer than a key tile, no prefix at all, one new token
+    (= a decode step), chunks around the 128 / 256 tile edges; both tcgen05 kernels vs the oracle."""
+    H, KVH = 4, 2
+    lens_ctx = [300, 128, 1000, 513, 2049, 77, 640]
+    lens_new = [300, 128, 257, 1, 300, 13, 256]
+    c = _paged_case(D + BS, lens_ctx, lens_new, H, KVH, D, BS, dtype)
+    want = prefill_oracle.causal_paged_attention(c["q"], c["kc"], c["vc"], c["cu_q"], c["bt"], c["ctx"],
+                                                 1.0 / D ** 0.5, H, KVH, D, BS)
+    outs = {}
+    for name, flags in PAGED_KERNELS.items():
+        outs[name] = flash_attention_prefill_paged(
+            c["q"].to(cuda_device), c["kc"].to(cuda_device), c["vc"].to(cuda_device), c["cu_q"].to(cuda_device),
+            c["bt"].to(cuda_device), c["ctx"].to(cuda_device), 1.0 / D ** 0.5, H, KVH, D, BS,
+            max_seqlen_q=max(lens_new), flags=flags)
+        _check(outs[name], want)
+    assert torch.equal(outs["tcgen05_one_tile"], outs["tcgen05_pair"])
+
+
+def test_paged_prefill_without_prefix_equals_dense_prefill(cuda_device):
+    """context_lens == new lengths: the paged entry point must return exactly what the dense one does
+    (same kernels, same tiles, K/V merely fetched through the block table)."""
+    H, KVH, D, BS = 8, 2, 128, 16
+    lens = [700, 129, 256]
+    c = _paged_case(3, lens, lens, H, KVH, D, BS, torch.bfloat16)
+    k = torch.cat(c["k_full"]).to(cuda_device)
+    v = torch.cat(c["v_full"]).to(cuda_device)
+    for flags in (2, 4):
+        a = flash_attention_prefill_paged(c["q"].to(cuda_device), c["kc"].to(cuda_device), c["vc"].to(cuda_device),
+                                          c["cu_q"].to(cuda_device), c["bt"].to(cuda_device), c["ctx"].to(cuda_device),
+                                          1.0 / D ** 0.5, H, KVH, D, BS, flags=flags)
+        b = flash_attention_prefill(c["q"].to(cuda_device), k, v, c["cu_q"].to(cuda_device), 1.0 / D ** 0.5, H, KVH, D,
+                                    flags=flags)
+        assert torch.equal(a, b)
+
+
+def test_attention_forward_prefill_with_cached_prefix(cuda_device):
+    """Attention.forward in the prefill branch with block_tables set (what reference
+    model_runner.py:209-215 builds when the block manager found a cached prefix): the new tokens' K/V
+    are stored, then the queries attend over prefix + new tokens."""
+    H, KVH, D, BS = 8, 2, 128, 16
+    lens_ctx, lens_new = [200, 96], [72, 96]          # 128 cached + 72 new; nothing cached + 96 new
+    c = _paged_case(11, lens_ctx, lens_new, H, KVH, D, BS, torch.bfloat16)
+    # remove the new tokens' rows from the cache: forward() has to store them itself
+    kc, vc = c["kc"].clone(), c["vc"].clone()
+    k_new, v_new, slots = [], [], []
+    for s, (ctx, n) in enumerate(zip(lens_ctx, lens_new)):
+        pos = torch.arange(ctx - n, ctx)
+        sl = c["bt"][s, pos // BS].long() * BS + pos % BS
+        kc.view(-1, KVH, D)[sl] = 0
+        vc.view(-1, KVH, D)[sl] = 0
+        k_new.append(c["k_full"][s][ctx - n:]), v_new.append(c["v_full"][s][ctx - n:]), slots.append(sl)
+    cu_k = torch.tensor([0] + list(np.cumsum(lens_ctx)), dtype=torch.int32)
+    layer = Attention(H, D, scale=1.0, num_kv_heads=KVH, block_size=BS)
+    layer.k_cache, layer.v_cache = kc.to(cuda_device), vc.to(cuda_device)
+    set_context(True, cu_seqlens_q=c["cu_q"].to(cuda_device), cu_seqlens_k=cu_k.to(cuda_device),
+                max_seqlen_q=max(lens_new), max_seqlen_k=max(lens_ctx), slot_mapping=torch.cat(slots).to(cuda_device),
+                block_tables=c["bt"].to(cuda_device))
+    try:
+        out = layer(c["q"].to(cuda_device), torch.cat(k_new).to(cuda_device), torch.cat(v_new).to(cuda_device))
+    finally:
+        reset_context()
+    assert torch.equal(layer.k_cache.cpu().view(torch.uint8), c["kc"].view(torch.uint8))
+    want = prefill_oracle.causal_paged_attention(c["q"], c["kc"], c["vc"], c["cu_q"], c["bt"], c["ctx"],
+                                                 1.0 / D ** 0.5, H, KVH, D, BS)
+    _check(out.view(-1, H, D), want)

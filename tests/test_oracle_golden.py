@@ -148,3 +148,51 @@ def test_prefill_oracle_matches_reference(name):
     assert np.abs(got[::3] - z["ref_out_f32"]).max() <= 1e-5
     native = torch.from_numpy(z["ref_out_bits"]).view(inp["q"].dtype).float().numpy()
     assert np.abs(got - native).max() <= 2e-2
+
+
+def _paged_case(seed, lens_ctx, lens_new, H, KVH, D, BS, dtype=torch.float32):
+    """Random sequences laid out in a paged cache (random page order) + the queries of their last
+    lens_new tokens.  Returns everything both prefill oracles need."""
+    g = torch.Generator().manual_seed(seed)
+    pages = [(c + BS - 1) // BS for c in lens_ctx]
+    nb = sum(pages) + 3
+    order = torch.randperm(nb, generator=g)
+    width = max(pages) + 1
+    bt = torch.full((len(lens_ctx), width), -1, dtype=torch.int32)
+    kc = torch.zeros(nb, BS, KVH, D, dtype=dtype)
+    vc = torch.zeros_like(kc)
+    k_full, v_full, q_new, at = [], [], [], 0
+    for s, (c, n) in enumerate(zip(lens_ctx, lens_new)):
+        bt[s, :pages[s]] = order[at:at + pages[s]].to(torch.int32)
+        at += pages[s]
+        k = torch.randn(c, KVH, D, generator=g).to(dtype)
+        v = torch.randn(c, KVH, D, generator=g).to(dtype)
+        pos = torch.arange(c)
+        slots = bt[s, pos // BS].long() * BS + pos % BS
+        kc.view(-1, KVH, D)[slots] = k
+        vc.view(-1, KVH, D)[slots] = v
+        k_full.append(k), v_full.append(v)
+        q_new.append(torch.randn(n, H, D, generator=g).to(dtype))
+    cu_q = torch.tensor([0] + list(np.cumsum(lens_new)), dtype=torch.int32)
+    return dict(q=torch.cat(q_new), kc=kc, vc=vc, bt=bt, ctx=torch.tensor(lens_ctx, dtype=torch.int32), cu_q=cu_q,
+                k_full=k_full, v_full=v_full, q_new=q_new)
+
+
+@pytest.mark.parametrize("BS", [16, 256])
+def test_paged_prefill_oracle_equals_dense_tail(BS):
+    """causal_paged_attention (no reference implementation exists: the reference's prefill ignores the
+    pages, A-8) is anchored on causal_varlen_attention, which IS pinned to the reference: queries at the
+    last n positions of a sequence give the last n rows of the dense causal attention over all ctx
+    tokens, whatever the queries at earlier positions are.  With no prefix the two coincide."""
+    H, KVH, D = 4, 2, 32
+    lens_ctx, lens_new = [40, 300, 17, 129], [40, 45, 1, 128]     # first sequence: no cached prefix
+    c = _paged_case(7, lens_ctx, lens_new, H, KVH, D, BS)
+    got = prefill_oracle.causal_paged_attention(c["q"], c["kc"], c["vc"], c["cu_q"], c["bt"], c["ctx"], 0.2, H, KVH,
+                                                D, BS)
+    for s, (ctx, n) in enumerate(zip(lens_ctx, lens_new)):
+        q_full = torch.zeros(ctx, H, D)
+        q_full[ctx - n:] = c["q_new"][s]
+        dense = prefill_oracle.causal_varlen_attention(q_full, c["k_full"][s], c["v_full"][s],
+                                                       torch.tensor([0, ctx]), 0.2, H, KVH, D)
+        b = int(c["cu_q"][s])
+        assert (got[b:b + n] - dense[ctx - n:]).abs().max() < 1e-12
