@@ -1,1 +1,2 @@
-from .decode_runner import BlockPool, DecodeRunner, SeqState, prefill_metadata  # noqa: F401
+from .block_manager import PrefixBlockManager, PrefixSeq  # noqa: F401
+from .decode_runner import BlockPool, DecodeRunner, PrefillMeta, SeqState, prefill_metadata  # noqa: F401

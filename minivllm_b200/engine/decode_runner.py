@@ -18,7 +18,7 @@ the per-layer ``q, k, v`` the projections would have produced.
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, List, NamedTuple, Optional, Sequence
 
 import numpy as np
 import torch
@@ -74,29 +74,43 @@ class BlockPool:
         seq.num_tokens = 0
 
 
-def prefill_metadata(seqs: Sequence["SeqState"], block_size: int):
-    """(cu_seqlens int32 (n+1), slot_mapping int64 (T), longest prompt) of a prefill batch —
-    what reference model_runner.py:186-213 builds with per-sequence, per-block Python loops, here a
-    repeat + arange: token ``j`` of a prompt lands in ``table[j // BS] * BS + j % BS``."""
+class PrefillMeta(NamedTuple):
+    cu_seqlens_q: np.ndarray   # (n+1) int32 over the NEW tokens of each prompt
+    cu_seqlens_k: np.ndarray   # (n+1) int32 over all tokens (cached prefix + new)
+    slot_mapping: np.ndarray   # (sum new) int64
+    max_seqlen_q: int
+    max_seqlen_k: int
+    any_cached: bool
+
+
+def prefill_metadata(seqs: Sequence["SeqState"], block_size: int) -> PrefillMeta:
+    """Metadata of a prefill batch — what reference model_runner.py:186-213 builds with per-sequence,
+    per-block Python loops, here a repeat + arange: the tokens of a prompt that are not already cached
+    (``seq.num_cached_tokens``, set by the block manager, a multiple of the block size) are the
+    queries; token ``j`` of a prompt lands in ``table[j // BS] * BS + j % BS``."""
     if not seqs:
         raise ValueError("empty prefill batch")
     BS = block_size
     n = np.fromiter((s.num_tokens for s in seqs), dtype=np.int64, count=len(seqs))
-    if (n <= 0).any():
-        raise ValueError("prefill of an empty sequence")
+    c = np.fromiter((getattr(s, "num_cached_tokens", 0) for s in seqs), dtype=np.int64, count=len(seqs))
+    if (n <= 0).any() or (c < 0).any() or (c >= n).any() or (c % BS).any():
+        raise ValueError("prefill needs 0 <= num_cached_tokens < num_tokens, cached in whole blocks")
     n_pages = (n + BS - 1) // BS
     for s, need in zip(seqs, n_pages):
         if len(s.block_table) < need:
             raise ValueError("a sequence's block table is shorter than its prompt")
-    cu = np.zeros(len(seqs) + 1, dtype=np.int32)
-    np.cumsum(n, out=cu[1:])
-    pos = np.arange(int(cu[-1]), dtype=np.int64) - np.repeat(cu[:-1].astype(np.int64), n)
+    nq = n - c
+    cu_q = np.zeros(len(seqs) + 1, dtype=np.int32)
+    cu_k = np.zeros(len(seqs) + 1, dtype=np.int32)
+    np.cumsum(nq, out=cu_q[1:])
+    np.cumsum(n, out=cu_k[1:])
+    pos = np.arange(int(cu_q[-1]), dtype=np.int64) - np.repeat(cu_q[:-1].astype(np.int64) - c, nq)
     pages = np.concatenate([np.asarray(s.block_table[:need], dtype=np.int64)
                             for s, need in zip(seqs, n_pages)])
     first_page = np.zeros(len(seqs), dtype=np.int64)
     np.cumsum(n_pages[:-1], out=first_page[1:])
-    slots = pages[np.repeat(first_page, n) + pos // BS] * BS + pos % BS
-    return cu, slots, int(n.max())
+    slots = pages[np.repeat(first_page, nq) + pos // BS] * BS + pos % BS
+    return PrefillMeta(cu_q, cu_k, slots, int(nq.max()), int(n.max()), bool(c.any()))
 
 
 class DecodeRunner:
@@ -180,22 +194,28 @@ class DecodeRunner:
         return bucket
 
     def prepare_prefill(self, seqs: Sequence[SeqState]) -> int:
-        """Metadata of a prefill step over whole prompts (reference model_runner.py:180-227):
-        ``cu_seqlens_q == cu_seqlens_k`` (exclusive prefix sums of ``len(seq)``), the longest
-        prompt, and ONE slot per prompt token, ``table[j // BS] * BS + j % BS`` — built with numpy
-        (a repeat + arange, no per-token Python loop) and sent with one H2D copy per array.
-        Prompts with an already-cached prefix (``num_cached_tokens > 0``, row N2) are not part of
-        this path: the reference's prefill kernel attends over the new tokens only and ignores the
-        block tables it is handed, so there is no behaviour to match.  Returns the token count."""
-        cu, slots, longest = prefill_metadata(seqs, self.block_size)
-        total = int(cu[-1])
-        h_cu = torch.from_numpy(cu).pin_memory()
-        h_slot = torch.from_numpy(slots).pin_memory()
-        d_cu = h_cu.to(self.device, non_blocking=True)
-        d_slot = h_slot.to(self.device, non_blocking=True)
-        self._prefill_keep = (h_cu, h_slot)   # pinned sources stay alive until the copies ran
-        set_context(True, cu_seqlens_q=d_cu, cu_seqlens_k=d_cu, max_seqlen_q=longest,
-                    max_seqlen_k=longest, slot_mapping=d_slot)
+        """Metadata of a prefill step (reference model_runner.py:180-227): ``cu_seqlens_q`` over the
+        tokens still to compute, ``cu_seqlens_k`` over whole prompts, one slot per new token, and —
+        when the block manager found cached prefixes — the block tables, so that attention reads the
+        cached pages too (model_runner.py:209-215; the reference's kernel then ignores them, A-8).
+        One H2D copy per array.  Returns the number of new tokens."""
+        m = prefill_metadata(seqs, self.block_size)
+        total = int(m.cu_seqlens_q[-1])
+        host = [torch.from_numpy(m.cu_seqlens_q).pin_memory(), torch.from_numpy(m.cu_seqlens_k).pin_memory(),
+                torch.from_numpy(m.slot_mapping).pin_memory()]
+        tables = None
+        if m.any_cached:
+            width = max(len(s.block_table) for s in seqs)
+            tab = np.full((len(seqs), width), -1, dtype=np.int32)
+            for i, s in enumerate(seqs):
+                tab[i, :len(s.block_table)] = s.block_table
+            host.append(torch.from_numpy(tab).pin_memory())
+        dev = [h.to(self.device, non_blocking=True) for h in host]
+        if m.any_cached:
+            tables = dev[3]
+        self._prefill_keep = host   # pinned sources stay alive until the copies ran
+        set_context(True, cu_seqlens_q=dev[0], cu_seqlens_k=dev[1], max_seqlen_q=m.max_seqlen_q,
+                    max_seqlen_k=m.max_seqlen_k, slot_mapping=dev[2], block_tables=tables)
         return total
 
     @torch.inference_mode()

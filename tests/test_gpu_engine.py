@@ -118,3 +118,77 @@ def test_prefill_then_decode(cuda_device, block_size):
                                          1.0 / D ** 0.5, H, KVH, D, block_size)
             err = (out[layer].view(len(seqs), H, D) - want).abs() - (1e-3 + 2.0 ** -8 * want.abs())
             assert err.max() <= 0
+
+
+def test_prefix_cached_prefill_through_manager_and_runner(cuda_device):
+    """N2 + N3 together: the prefix block manager gives three prompts with a common 64-token prefix
+    aliased pages; the first prompt is prefilled whole, the others only past their cached blocks
+    (attention over the cached pages), and every prompt's outputs equal those of an engine without
+    prefix caching (every prompt prefilled whole into private pages).  A decode step follows."""
+    from minivllm_b200.engine import PrefixBlockManager, PrefixSeq
+    from oracle import prefill_oracle as pf
+    BS, nb = 16, 64
+    g = torch.Generator().manual_seed(5)
+    common = torch.randint(0, 1000, (64,), generator=g).tolist()
+    prompts = [common + torch.randint(0, 1000, (n,), generator=g).tolist() for n in (23, 40, 1)]
+    # token -> (q, k, v) per layer: a deterministic "model" so equal tokens at equal positions give equal K/V
+    emb = torch.randn(1000 + 200, L, H + 2 * KVH, D, generator=g)
+
+    def acts(tokens, start):
+        x = torch.stack([emb[t] + 0.01 * emb[1000 + start + i] for i, t in enumerate(tokens)])   # (n, L, H+2KVH, D)
+        x = x.to(torch.bfloat16).permute(1, 0, 2, 3)
+        return x[:, :, :H], x[:, :, H:H + KVH], x[:, :, H + KVH:]
+
+    def run(prefix_caching):
+        r = DecodeRunner(L, H, KVH, D, BS, nb, MAXBS, 256, torch.bfloat16, cuda_device, enforce_eager=True)
+        mgr = PrefixBlockManager(nb, BS)
+        seqs = [PrefixSeq(p) for p in prompts]
+        outs = []
+        for s in seqs:                       # one prefill step per prompt, in arrival order
+            mgr.allocate(s)
+            if not prefix_caching:
+                s.num_cached_tokens = 0      # same tables, but recompute (and re-store) everything
+            c = s.num_cached_tokens
+            q, k, v = acts(s.token_ids[c:], c)
+            assert r.prepare_prefill([s]) == len(s) - c
+            outs.append(r.run_prefill(q.to(cuda_device), k.to(cuda_device), v.to(cuda_device)).float().cpu())
+        return r, mgr, seqs, outs
+
+    r1, mgr1, seqs1, out1 = run(True)
+    r0, _, seqs0, out0 = run(False)
+    assert [s.num_cached_tokens for s in seqs1] == [0, 64, 64] and mgr1.hits == 8
+    assert seqs1[1].block_table[:4] == seqs1[0].block_table[:4] == seqs1[2].block_table[:4]
+    assert torch.equal(r1.kv_cache.cpu().view(torch.uint8), r0.kv_cache.cpu().view(torch.uint8))
+    for s, a, b in zip(seqs1, out1, out0):
+        c = s.num_cached_tokens
+        assert (a - b[:, c:]).abs().max() <= 2e-2          # same attention, the cached run read from pages
+    # and against the exact oracle for the second prompt
+    s = seqs1[1]
+    q, _, _ = acts(s.token_ids[64:], 64)
+    tab = torch.tensor([s.block_table], dtype=torch.int32)
+    for layer in range(L):
+        want = pf.causal_paged_attention(q[layer], r1.kv_cache[0, layer].cpu(), r1.kv_cache[1, layer].cpu(),
+                                         torch.tensor([0, len(s) - 64]), tab, torch.tensor([len(s)]),
+                                         1.0 / D ** 0.5, H, KVH, D, BS)
+        err = (out1[1][layer].view(-1, H, D) - want).abs() - (4e-3 + 2.0 ** -7 * want.abs())
+        assert err.max() <= 0
+    # one decode step over the aliased tables
+    for s in seqs1:
+        s.append_token(7)
+        mgr1.append(s)
+    bucket = r1.prepare_decode(seqs1)
+    qd = torch.randn(L, bucket, H, D, generator=g).to(torch.bfloat16)
+    kd = torch.randn(L, bucket, KVH, D, generator=g).to(torch.bfloat16)
+    vd = torch.randn(L, bucket, KVH, D, generator=g).to(torch.bfloat16)
+    r1.q[:, :bucket].copy_(qd), r1.k[:, :bucket].copy_(kd), r1.v[:, :bucket].copy_(vd)
+    out = r1.run().float().cpu()
+    cache = r1.kv_cache.cpu()
+    n = torch.tensor([len(s) for s in seqs1])
+    width = max(len(s.block_table) for s in seqs1)
+    tab = torch.full((len(seqs1), width), -1, dtype=torch.int32)
+    for i, s in enumerate(seqs1):
+        tab[i, :len(s.block_table)] = torch.tensor(s.block_table, dtype=torch.int32)
+    for layer in range(L):
+        want = c_oracle.paged_decode(qd[layer], cache[0, layer], cache[1, layer], tab, n, 1.0 / D ** 0.5, H, KVH, D, BS)
+        err = (out[layer].view(len(seqs1), H, D) - want).abs() - (1e-3 + 2.0 ** -8 * want.abs())
+        assert err.max() <= 0

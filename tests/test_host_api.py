@@ -142,12 +142,63 @@ def test_prefill_metadata_matches_per_token_loop():
     seqs = [SeqState() for _ in lens]
     for s, n in zip(seqs, lens):
         pool.allocate(s, n)
-    cu, slots, longest = prefill_metadata(seqs, BS)
-    assert cu.tolist() == np.concatenate([[0], np.cumsum(lens)]).tolist() and longest == 48
+    m = prefill_metadata(seqs, BS)
+    assert m.cu_seqlens_q.tolist() == np.concatenate([[0], np.cumsum(lens)]).tolist()
+    assert m.cu_seqlens_k.tolist() == m.cu_seqlens_q.tolist() and not m.any_cached
+    assert (m.max_seqlen_q, m.max_seqlen_k) == (48, 48)
     want = [s.block_table[j // BS] * BS + j % BS for s in seqs for j in range(len(s))]
-    assert slots.tolist() == want and len(set(want)) == len(want)
+    assert m.slot_mapping.tolist() == want and len(set(want)) == len(want)
     with pytest.raises(ValueError):
         prefill_metadata([], BS)
     seqs[0].block_table = []
     with pytest.raises(ValueError):
         prefill_metadata(seqs, BS)
+
+
+def test_prefix_block_manager_shares_and_frees_pages():
+    """N2: leading full blocks of a prompt that are already resident are shared (ref-counted), the
+    block of the last token never is, the chain hash makes a block's identity depend on its whole
+    prefix, pages return when their last user leaves and can be revived by a later prompt."""
+    from minivllm_b200.engine import PrefixBlockManager, PrefixSeq, prefill_metadata
+    BS = 4
+    mgr = PrefixBlockManager(16, BS)
+    base = list(range(100, 110))                       # 10 tokens: 2 full blocks + 2
+    a = PrefixSeq(base)
+    assert mgr.can_allocate(a)
+    mgr.allocate(a)
+    assert a.num_cached_tokens == 0 and len(a.block_table) == 3 and len(mgr.free_block_ids) == 13
+    b = PrefixSeq(base[:8] + [7, 8, 9])                # same first two blocks, different tail
+    mgr.allocate(b)
+    assert b.num_cached_tokens == 8 and b.block_table[:2] == a.block_table[:2] and b.block_table[2] != a.block_table[2]
+    assert [mgr.blocks[i].ref_count for i in a.block_table[:2]] == [2, 2]
+    c = PrefixSeq(base[:8])                            # exactly two full blocks: the last one is recomputed
+    mgr.allocate(c)
+    assert c.num_cached_tokens == 4 and c.block_table[0] == a.block_table[0] and c.block_table[1] != a.block_table[1]
+    d = PrefixSeq([1, 2, 3, 4] + base[4:8] + [5])      # second block has the same tokens, different prefix
+    mgr.allocate(d)
+    assert d.num_cached_tokens == 0 and not set(d.block_table) & set(a.block_table)
+    # metadata of a batch with cached prefixes: queries = the uncached tokens, slots at their positions
+    m = prefill_metadata([b, d], BS)
+    assert m.any_cached and m.cu_seqlens_q.tolist() == [0, 3, 12] and m.cu_seqlens_k.tolist() == [0, 11, 20]
+    assert m.slot_mapping.tolist()[:3] == [b.block_table[2] * BS + j for j in range(3)]
+    # generated tokens: a page is opened when a token starts a block, the hash is published when one fills
+    for t in (50, 51):
+        a.append_token(t)
+        assert mgr.can_append(a)
+        mgr.append(a)
+    assert len(a) == 12 and len(a.block_table) == 3 and mgr.blocks[a.block_table[2]].hash is not None
+    a.append_token(52)
+    mgr.append(a)
+    assert len(a.block_table) == 4
+    e = PrefixSeq(base + [50, 51, 99])                 # reuses a's three full blocks, incl. the one filled by appends
+    mgr.allocate(e)
+    assert e.num_cached_tokens == 12 and e.block_table[:3] == a.block_table[:3]
+    # release everything: all pages come back, and a cached page on the free list is revived on a hit
+    for s in (a, b, c, d, e):
+        mgr.deallocate(s)
+    assert len(mgr.free_block_ids) == 16 and all(blk.ref_count == 0 for blk in mgr.blocks)
+    f = PrefixSeq(base)
+    mgr.allocate(f)
+    assert f.num_cached_tokens == 8
+    with pytest.raises(MemoryError):
+        mgr.allocate(PrefixSeq(list(range(1000, 1000 + 4 * 20))))
