@@ -208,8 +208,8 @@ int mvl_flash_prefill(void* out, const void* q, const void* k, const void* v, in
  *   q (total_q_tokens, H, D) with a token stride; out (total_q_tokens, H, D) contiguous; caches
  *   (num_blocks, block_size, KVH, D) contiguous, block_size a power of two >= 16; block_tables int32,
  *   row stride block_table_stride, entries past a sequence's context unused (may be -1).
- * tcgen05 kernels only: 16-bit dtypes, scale > 0 (MVL_ERR_SHAPE otherwise); flags as mvl_flash_prefill
- * (MVL_PREFILL_ONE_TILE / MVL_PREFILL_PAIR).  Page rows past a sequence's context inside its last
+ * tcgen05 kernels only: 16-bit dtypes, scale > 0 (MVL_ERR_SHAPE otherwise); the pair kernel whenever
+ * max_seqlen_q > 128; flags as mvl_flash_prefill (MVL_PREFILL_ONE_TILE / MVL_PREFILL_PAIR).  Page rows past a sequence's context inside its last
  * page are multiplied by zero probabilities: the cache must hold finite values there (allocate it
  * zeroed, as the engine does).
  */

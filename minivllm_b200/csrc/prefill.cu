@@ -306,7 +306,10 @@ extern "C" int mvl_flash_prefill_paged(void* out, const void* q, int64_t q_token
   p.num_slots = (int)(num_blocks * block_size);
   p.H = num_heads; p.KVH = num_kv_heads;
   p.qscale = scale * 1.4426950408889634f;
-  const bool single = (flags & 2u) || (!(flags & 4u) && max_seqlen_q < 2048);
+  // with a cached prefix (or chunked prefill) a query tile walks many key tiles however few queries
+  // there are, which is where the pair kernel's ping-pong pays: 8 x 1024 new tokens over 8k-token
+  // contexts 1,087 vs 573 TFLOP/s.  One query tile per sequence leaves nothing to pair.
+  const bool single = (flags & 2u) || (!(flags & 4u) && max_seqlen_q <= 128);
   return mvl::launch_prefill_tcgen05(p, elem_dtype, head_dim, num_seqs, max_seqlen_q, single,
                                      (cudaStream_t)stream);
 }

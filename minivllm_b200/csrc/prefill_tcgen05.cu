@@ -158,43 +158,32 @@ __device__ __forceinline__ SeqGeom seq_geom(const PrefillParams& p, int seq) {
 // Key tiles a 128-query tile starting at absolute position qa0 needs: through the tile of its last row.
 __device__ __forceinline__ int key_tiles(int qa0, int ctx) { return min((qa0 + 127) / 128 + 1, (ctx + 127) >> 7); }
 
-// TMA loads of key tile j (128 keys x D) into a 128-byte-swizzled shared-memory tile.  Dense: 128
-// consecutive tokens of the packed tensor.  Paged: 128 / piece_rows boxes of piece_rows slots each,
-// located through the block-table row; a piece past the context or with a negative table entry is
-// requested at slot = num_slots, outside the tensor map, which the TMA unit fills with zeros (and
-// still counts as bytes on the barrier).  slots[] is filled by kv_slots once per tile, used for K and V.
+// TMA loads of key tile j (128 keys x D) into a 128-byte-swizzled shared-memory tile, issued
+// cooperatively: lane li of the calling warp issues box li of the tile's D/64 panels x pieces.  Dense:
+// one piece, 128 consecutive tokens of the packed tensor.  Paged: 128 / piece_rows pieces of
+// piece_rows slots each, located through the block-table row (each lane reads its own entry); a piece
+// past the context or with a negative table entry is requested at slot = num_slots, outside the
+// tensor map, which the TMA unit fills with zeros (and still counts as bytes on the barrier).
+// The caller posts expect_tx(TILE_BYTES) on the barrier first.
 template <int D, bool PAGED>
-__device__ __forceinline__ void kv_slots(const PrefillParams& p, const SeqGeom& g, const int* table, int j,
-                                         int (&slots)[8]) {
-  if (!PAGED) {
-    slots[0] = g.q_start + j * 128;
-    return;
-  }
-  const int pieces = 128 / p.piece_rows;
-  for (int pc = 0; pc < pieces; ++pc) {
-    const int key0 = j * 128 + pc * p.piece_rows;
-    int slot = p.num_slots;
+__device__ __forceinline__ void kv_load(const PrefillParams& p, const SeqGeom& g, const int* table,
+                                        const CUtensorMap* map, uint32_t dst, int head, int j, int li,
+                                        uint32_t bar) {
+  constexpr int PANELS = D / 64, PANEL_BYTES = 128 * 128;
+  const int pieces = PAGED ? 128 / p.piece_rows : 1;
+  if (li >= pieces * PANELS) return;
+  const int pc = li / PANELS, pn = li % PANELS;
+  int slot = g.q_start + j * 128, rows = 0;
+  if (PAGED) {
+    rows = pc * p.piece_rows;
+    const int key0 = j * 128 + rows;
+    slot = p.num_slots;
     if (key0 < g.ctx) {
       const int e = __ldg(table + (key0 >> p.bs_shift));
       if (e >= 0) slot = (e << p.bs_shift) | (key0 & ((1 << p.bs_shift) - 1));
     }
-    slots[pc] = slot;
   }
-}
-template <int D, bool PAGED>
-__device__ __forceinline__ void kv_load(const PrefillParams& p, const CUtensorMap* map, uint32_t dst, int head,
-                                        const int (&slots)[8], uint32_t bar) {
-  constexpr int PANELS = D / 64, PANEL_BYTES = 128 * 128;
-  if (!PAGED) {
-#pragma unroll
-    for (int pn = 0; pn < PANELS; ++pn) tma_load_3d(dst + pn * PANEL_BYTES, map, pn * 64, head, slots[0], bar);
-    return;
-  }
-  const int pieces = 128 / p.piece_rows;
-  for (int pc = 0; pc < pieces; ++pc)
-#pragma unroll
-    for (int pn = 0; pn < PANELS; ++pn)
-      tma_load_3d(dst + pn * PANEL_BYTES + pc * p.piece_rows * 128, map, pn * 64, head, slots[pc], bar);
+  tma_load_3d(dst + pn * PANEL_BYTES + rows * 128, map, pn * 64, head, slot, bar);
 }
 
 template <typename T, int D, bool PAGED>
@@ -236,10 +225,11 @@ flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __gri
   const uint32_t tmem = lds_u32(tmem_slot);
   const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
 
-  int slots[8];
-  auto load_kv = [&](const CUtensorMap* map, uint32_t dst, uint32_t bar) {
-    mbar_expect_tx(bar, C::TILE_BYTES);
-    kv_load<D, PAGED>(p, map, dst, kvh, slots, bar);
+  // warp 0 issues the TMA boxes of a tile together (up to 16 of them for 16-slot pages)
+  auto load_kv = [&](const CUtensorMap* map, uint32_t dst, int j, uint32_t bar) {
+    if (tid == 0) mbar_expect_tx(bar, C::TILE_BYTES);
+    __syncwarp();
+    kv_load<D, PAGED>(p, g, table, map, dst, kvh, j, tid, bar);
   };
   constexpr uint32_t HI = tc5::smem_desc_hi_sw128(1024);
   const uint32_t q_lo = tc5::smem_desc_lo(sQ, 16), k_lo = tc5::smem_desc_lo(sK, 16),
@@ -260,18 +250,22 @@ flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __gri
     tc5::commit(bar_o);
   };
 
-  if (tid == 0) {
-    mbar_expect_tx(bar_q, C::TILE_BYTES);
+  if (warp == 0) {
+    if (tid == 0) {
+      mbar_expect_tx(bar_q, C::TILE_BYTES);
 #pragma unroll
-    for (int pn = 0; pn < C::PANELS; ++pn)
-      tma_load_3d(sQ + pn * C::PANEL_BYTES, &mq, pn * 64, h, g.q_start + m0, bar_q);
-    kv_slots<D, PAGED>(p, g, table, 0, slots);
-    load_kv(&mk, sK, bar_k);
-    load_kv(&mv, sV, bar_v);
-    tc5::mbar_wait_bounded(bar_q, 0);
-    tc5::mbar_wait_bounded(bar_k, 0);
-    tc5::fence_after_sync();
-    issue_qk();
+      for (int pn = 0; pn < C::PANELS; ++pn)
+        tma_load_3d(sQ + pn * C::PANEL_BYTES, &mq, pn * 64, h, g.q_start + m0, bar_q);
+    }
+    load_kv(&mk, sK, 0, bar_k);
+    load_kv(&mv, sV, 0, bar_v);
+    if (tid == 0) {
+      tc5::mbar_wait_bounded(bar_q, 0);
+      tc5::mbar_wait_bounded(bar_k, 0);
+      tc5::fence_after_sync();
+      issue_qk();
+    }
+    __syncwarp();
   }
 
   float m_ref = 0.f, l = 0.f;
@@ -279,12 +273,9 @@ flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __gri
   for (int j = 0; j < ntiles; ++j) {
     tc5::mbar_wait_bounded(bar_s, j & 1);  // S_j is complete, and so is every MMA issued before it
     tc5::fence_after_sync();
-    if (tid == 0) {
-      if (j > 0) load_kv(&mv, sV, bar_v);  // product j-1 has retired; slots[] still describes tile j
-      if (j + 1 < ntiles) {                // S_j no longer reads K_j
-        kv_slots<D, PAGED>(p, g, table, j + 1, slots);
-        load_kv(&mk, sK, bar_k);
-      }
+    if (warp == 0) {
+      if (j > 0) load_kv(&mv, sV, j, bar_v);                // product j-1 has retired
+      if (j + 1 < ntiles) load_kv(&mk, sK, j + 1, bar_k);   // S_j no longer reads K_j
     }
     softmax_step<T, D>(lane_base, lane_base + C::O_COL, j == 0, qa0 + tid - j * 128, qs, m_ref, l);
     tc5::fence_before_sync();
@@ -380,26 +371,31 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
   if (warp >= 8) {
     // issue warpgroup: hands most of its registers to the two softmax warpgroups
     asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
-    if (tid == 288) {
-      // ---- TMA thread: Q once, then K_j / V_j into stage j & 1 as soon as the products that read
-      // the previous occupant (tile j - 2) have retired (k_empty / v_empty, signalled by tcgen05.commit)
+    if (warp == 9) {
+      // ---- TMA warp: Q once, then K_j / V_j into stage j & 1 as soon as the products that read the
+      // previous occupant (tile j - 2) have retired (k_empty / v_empty, signalled by tcgen05.commit).
+      // The boxes of a tile (2 dense, up to 16 for 16-slot pages) are issued by as many lanes at once.
+      const int lane = tid & 31;
       const int* table = PAGED ? p.block_tables + (long long)seq * p.bt_stride : nullptr;
-      mbar_expect_tx(q_full, (n1 ? 2 : 1) * C::TILE_BYTES);
+      if (lane == 0) {
+        mbar_expect_tx(q_full, (n1 ? 2 : 1) * C::TILE_BYTES);
 #pragma unroll
-      for (int pn = 0; pn < C::PANELS; ++pn) {
-        tma_load_3d(sQ + pn * C::PANEL_BYTES, &mq, pn * 64, h, g.q_start + m0, q_full);
-        if (n1) tma_load_3d(sQ + C::TILE_BYTES + pn * C::PANEL_BYTES, &mq, pn * 64, h, g.q_start + m0 + 128, q_full);
+        for (int pn = 0; pn < C::PANELS; ++pn) {
+          tma_load_3d(sQ + pn * C::PANEL_BYTES, &mq, pn * 64, h, g.q_start + m0, q_full);
+          if (n1)
+            tma_load_3d(sQ + C::TILE_BYTES + pn * C::PANEL_BYTES, &mq, pn * 64, h, g.q_start + m0 + 128, q_full);
+        }
       }
       for (int j = 0; j < n; ++j) {
         const int st = j & 1;
-        int slots[8];
-        kv_slots<D, PAGED>(p, g, table, j, slots);
         if (j >= 2) tc5::mbar_wait_bounded(k_empty + 8 * st, ((j >> 1) - 1) & 1);
-        mbar_expect_tx(k_full + 8 * st, C::TILE_BYTES);
-        kv_load<D, PAGED>(p, &mk, sK + st * C::TILE_BYTES, kvh, slots, k_full + 8 * st);
+        if (lane == 0) mbar_expect_tx(k_full + 8 * st, C::TILE_BYTES);
+        __syncwarp();
+        kv_load<D, PAGED>(p, g, table, &mk, sK + st * C::TILE_BYTES, kvh, j, lane, k_full + 8 * st);
         if (j >= 2) tc5::mbar_wait_bounded(v_empty + 8 * st, ((j >> 1) - 1) & 1);
-        mbar_expect_tx(v_full + 8 * st, C::TILE_BYTES);
-        kv_load<D, PAGED>(p, &mv, sV + st * C::TILE_BYTES, kvh, slots, v_full + 8 * st);
+        if (lane == 0) mbar_expect_tx(v_full + 8 * st, C::TILE_BYTES);
+        __syncwarp();
+        kv_load<D, PAGED>(p, g, table, &mv, sV + st * C::TILE_BYTES, kvh, j, lane, v_full + 8 * st);
       }
     } else if (tid == 256) {
       // ---- MMA thread
