@@ -64,6 +64,8 @@ def parse_args():
     ap.add_argument("--cpu-seqs", type=int, default=8, help="sequences in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-neighbours", action="store_true",
+                    help="skip the prefill / pre-attention kernels measured after the headline (N=1, c3 only)")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="N>1: how the per-rank heads are gathered (fused peer stores, or NCCL)")
     return ap.parse_args()
@@ -75,6 +77,78 @@ def measured_peaks():
         with open(path) as f:
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def neighbour_kernels(dev):
+    """The kernels either side of the hot path, each timed alone
+    after the headline measurement: 3 warm-up + 10 timed launches, CUDA events, inputs larger than L2.
+    Reported next to the headline line, not part of it."""
+    from minivllm_b200.layers.attention import flash_attention_prefill, flash_attention_prefill_paged
+    from minivllm_b200.layers.pre_attention import fused_qk_norm_rope_store, rope_cache
+    tf_burst, tf_sust = 1590.0, 1400.0
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            mp = json.load(f)
+        tf_burst, tf_sust = float(mp.get("bf16_tflops", tf_burst)), float(mp.get("bf16_tflops_sustained", tf_sust))
+    hbm, _ = measured_peaks()
+    H, KVH, D = 32, 8, 128
+
+    def timed(run):
+        for _ in range(3):
+            run()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(dev)
+        e0.record()
+        for _ in range(10):
+            run()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        return e0.elapsed_time(e1) / 10
+
+    out = {"shape": f"{H}Q/{KVH}KV/D{D} bf16", "timing": "3 warm-up + 10 launches, CUDA events",
+           "tensor_peak_tflops": {"burst": tf_burst, "sustained": tf_sust, "source": "MEASURED_PEAKS.json (cuBLAS bf16)"}}
+    # prefill, dense: 2 sequences x 16384 tokens, causal
+    nseq, n = 2, 16384
+    q = torch.randn(nseq * n, H, D, device=dev).to(torch.bfloat16)
+    k = torch.randn(nseq * n, KVH, D, device=dev).to(torch.bfloat16)
+    v = torch.randn_like(k)
+    cu = torch.arange(0, nseq * n + 1, n, dtype=torch.int32, device=dev)
+    ms = timed(lambda: flash_attention_prefill(q, k, v, cu, D ** -0.5, H, KVH, D, max_seqlen=n))
+    fl = 4.0 * D * H * nseq * n * (n + 1) / 2
+    out["prefill"] = {"kernel": "flash_prefill_tcgen05_pair_kernel", "workload": "2 x 16384 tokens, causal",
+                      "ms": ms, "tflops": fl / ms / 1e9, "frac_of_burst_peak": fl / ms / 1e9 / tf_burst}
+    # prefill over cached pages: 4 sequences, 2048 new tokens each on top of a 14336-token cached prefix
+    nseq, ctx, new, BS = 4, 16384, 2048, 16
+    pages = ctx // BS
+    kc = torch.randn(nseq * pages, BS, KVH, D, device=dev).to(torch.bfloat16)
+    vc = torch.randn_like(kc)
+    bt = torch.randperm(nseq * pages, device=dev).to(torch.int32).view(nseq, pages)
+    qn = q[:nseq * new]
+    cuq = torch.arange(0, nseq * new + 1, new, dtype=torch.int32, device=dev)
+    cl = torch.full((nseq,), ctx, dtype=torch.int32, device=dev)
+    ms = timed(lambda: flash_attention_prefill_paged(qn, kc, vc, cuq, bt, cl, D ** -0.5, H, KVH, D, BS, max_seqlen_q=new))
+    fl = 4.0 * D * H * nseq * sum(ctx - new + i + 1 for i in range(new))
+    out["prefill_cached_prefix"] = {"kernel": "flash_prefill_tcgen05_pair_kernel (paged K/V)",
+                                    "workload": "4 x 2048 new tokens over 14336 cached, 16-slot pages", "ms": ms,
+                                    "tflops": fl / ms / 1e9, "frac_of_burst_peak": fl / ms / 1e9 / tf_burst}
+    del kc, vc, bt, k, v
+    # pre-attention pass: q/k RMSNorm + RoPE + KV store over 262144 tokens
+    nt = 262144
+    qkv = torch.randn(nt, (H + 2 * KVH) * D, device=dev).to(torch.bfloat16)
+    qq, kk, vv = (x.view(nt, -1, D) for x in qkv.split([H * D, KVH * D, KVH * D], dim=-1))
+    kc = torch.zeros(nt // 16, 16, KVH, D, dtype=torch.bfloat16, device=dev)
+    vc = torch.zeros_like(kc)
+    slots = torch.randperm(nt, device=dev)
+    pos = torch.randint(0, 32768, (nt,), device=dev)
+    table = rope_cache(1e6, D, 32768, device=dev)
+    gamma = torch.ones(D, device=dev)
+    q_out = torch.empty(nt, H, D, dtype=torch.bfloat16, device=dev)
+    ms = timed(lambda: fused_qk_norm_rope_store(qq, kk, vv, pos, gamma, 1e-5, table, kc, vc, slots, q_out=q_out))
+    nbytes = 2 * nt * (H + 2 * KVH) * D * 2 + nt * 16 + nt * D * 4   # in + out + (pos, slot) + table rows
+    out["pre_attention"] = {"kernel": "qk_norm_rope_store_token_kernel", "workload": "262144 tokens", "ms": ms,
+                            "GBps": nbytes / ms / 1e6, "frac_of_hbm_peak": nbytes / ms / 1e6 / hbm}
+    return out
 
 
 # ------------------------------------------------------------------ clocks during the timed region
@@ -398,6 +472,11 @@ def run_ours(args, rank, world, local_rank):
         "gpu_launches": K * ((3 if multi_split else 2) if args.unfused else 1),
         "clocks": clocks.summary(),
     }
+    if world == 1 and args.workload == "c3" and args.shard_of == 1 and not args.no_neighbours:
+        try:
+            line["neighbours"] = neighbour_kernels(dev)
+        except Exception as exc:   # the headline line must not depend on them
+            line["neighbours"] = {"error": repr(exc)}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
