@@ -176,8 +176,9 @@ int mvl_paged_decode_peers(void* const* out_peers, int num_peers, int total_head
  * (attention.py:136-138); max_seqlen >= the longest one sizes the grid (the reference reads it
  * back from the device each call, :263-264; the engine already has it, model_runner.py:219).
  * total_tokens = T, the packed tensors' first dimension (bounds the TMA loads: rows past it read
- * as zero).  16-bit element types only (tensor-core path); MVL_ERR_DTYPE for fp32.  Like the
- * reference it attends over the new tokens only, not over cached-prefix pages.
+ * as zero).  Like the reference it attends over the new tokens only, not over cached-prefix pages
+ * (mvl_flash_prefill_paged does).  fp32 tensors run on a CUDA-core kernel (fp32 products and
+ * accumulation: the 1e-4 the reference's fp32 default asks for), 16-bit ones on the tensor cores:
  * Kernels: two on tcgen05 (TMA tiles, both products on the 5th-generation tensor cores, accumulators
  * and probabilities in tensor memory) — a pair kernel (256 queries per CTA, two tiles in ping-pong,
  * taken from max_seqlen >= 2048) and a one-tile kernel (64 < max_seqlen < 2048) — and an mma.sync
@@ -208,7 +209,8 @@ int mvl_flash_prefill(void* out, const void* q, const void* k, const void* v, in
  *   q (total_q_tokens, H, D) with a token stride; out (total_q_tokens, H, D) contiguous; caches
  *   (num_blocks, block_size, KVH, D) contiguous, block_size a power of two >= 16; block_tables int32,
  *   row stride block_table_stride, entries past a sequence's context unused (may be -1).
- * tcgen05 kernels only: 16-bit dtypes, scale > 0 (MVL_ERR_SHAPE otherwise); the pair kernel whenever
+ * 16-bit dtypes: tcgen05 kernels only, scale > 0 (MVL_ERR_SHAPE otherwise); fp32: the CUDA-core kernel,
+ * any scale.  The pair kernel whenever
  * max_seqlen_q > 128; flags as mvl_flash_prefill (MVL_PREFILL_ONE_TILE / MVL_PREFILL_PAIR).  Page rows past a sequence's context inside its last
  * page are multiplied by zero probabilities: the cache must hold finite values there (allocate it
  * zeroed, as the engine does).

@@ -229,7 +229,8 @@ extern "C" int mvl_flash_prefill(void* out, const void* q, const void* k, const 
                                  int64_t total_tokens, const int32_t* cu_seqlens, int num_seqs,
                                  int max_seqlen, int num_heads, int num_kv_heads, int head_dim, float scale,
                                  int elem_dtype, unsigned flags, void* stream) {
-  if (elem_dtype != 1 && elem_dtype != 2) return -2;  // MVL_ERR_DTYPE: 16-bit types only
+  if (elem_dtype < 0 || elem_dtype > 2) return -2;  // MVL_ERR_DTYPE
+  const int es = elem_dtype == 0 ? 4 : 2;
   if (total_tokens < 0 || num_seqs < 0 || max_seqlen < 0 || num_heads <= 0 || num_kv_heads <= 0 || num_heads % num_kv_heads)
     return -3;
   if (head_dim != 64 && head_dim != 128) return -3;
@@ -240,8 +241,8 @@ extern "C" int mvl_flash_prefill(void* out, const void* q, const void* k, const 
       v_token_stride < (int64_t)num_kv_heads * head_dim)
     return -3;
   const uintptr_t bits = (uintptr_t)out | (uintptr_t)q | (uintptr_t)k | (uintptr_t)v |
-                         (uintptr_t)(q_token_stride * 2) | (uintptr_t)(k_token_stride * 2) |
-                         (uintptr_t)(v_token_stride * 2);
+                         (uintptr_t)(q_token_stride * es) | (uintptr_t)(k_token_stride * es) |
+                         (uintptr_t)(v_token_stride * es);
   if (bits & 15u) return -4;
   mvl::PrefillParams p;
   p.out = out; p.q = q; p.k = k; p.v = v; p.cu_seqlens = cu_seqlens;
@@ -252,6 +253,7 @@ extern "C" int mvl_flash_prefill(void* out, const void* q, const void* k, const 
   p.H = num_heads; p.KVH = num_kv_heads;
   p.qscale = scale * 1.4426950408889634f;
   cudaStream_t s = (cudaStream_t)stream;
+  if (elem_dtype == 0) return mvl::launch_prefill_f32(p, head_dim, num_seqs, max_seqlen, s);
   // tcgen05 kernels: 128-query tiles, maximum taken on raw scores (needs scale > 0).  The pair kernel
   // (256 queries per CTA, ping-pong) wins from ~2k tokens per sequence, the one-tile kernel below
   // (1024: 582 vs 549 TFLOP/s; 4096: 904 vs 976); batches of short sequences keep mma.sync.
@@ -277,20 +279,21 @@ extern "C" int mvl_flash_prefill_paged(void* out, const void* q, int64_t q_token
                                        int max_seqlen_q, int num_heads, int num_kv_heads, int head_dim,
                                        int block_size, int64_t num_blocks, float scale, int elem_dtype,
                                        unsigned flags, void* stream) {
-  if (elem_dtype != 1 && elem_dtype != 2) return -2;  // MVL_ERR_DTYPE
+  if (elem_dtype < 0 || elem_dtype > 2) return -2;  // MVL_ERR_DTYPE
+  const int es = elem_dtype == 0 ? 4 : 2;
   if (total_q_tokens < 0 || num_seqs < 0 || max_seqlen_q < 0 || num_heads <= 0 || num_kv_heads <= 0 ||
       num_heads % num_kv_heads || num_blocks <= 0)
     return -3;
   if (head_dim != 64 && head_dim != 128) return -3;
   if (block_size < 16 || (block_size & (block_size - 1))) return -3;  // pages of 2^k >= 16 slots
-  if (!(scale > 0.f)) return -3;                                       // tcgen05 kernels only: raw-score maximum
+  if (elem_dtype != 0 && !(scale > 0.f)) return -3;                    // tcgen05 kernels: raw-score maximum
   if (num_seqs == 0 || max_seqlen_q == 0 || total_q_tokens == 0) return 0;
   if (num_seqs > 65535 || num_heads > 65535) return -7;
   if (total_q_tokens >= (1ll << 31) || num_blocks * block_size >= (1ll << 31) - 256) return -7;
   if (!out || !q || !k_cache || !v_cache || !cu_seqlens_q || !block_tables || !context_lens) return -1;
   if (q_token_stride < (int64_t)num_heads * head_dim) return -3;
   const uintptr_t bits = (uintptr_t)out | (uintptr_t)q | (uintptr_t)k_cache | (uintptr_t)v_cache |
-                         (uintptr_t)(q_token_stride * 2);
+                         (uintptr_t)(q_token_stride * es);
   if (bits & 15u) return -4;
   mvl::PrefillParams p;
   p.out = out; p.q = q; p.k = k_cache; p.v = v_cache; p.cu_seqlens = cu_seqlens_q;
@@ -306,6 +309,7 @@ extern "C" int mvl_flash_prefill_paged(void* out, const void* q, int64_t q_token
   p.num_slots = (int)(num_blocks * block_size);
   p.H = num_heads; p.KVH = num_kv_heads;
   p.qscale = scale * 1.4426950408889634f;
+  if (elem_dtype == 0) return mvl::launch_prefill_f32(p, head_dim, num_seqs, max_seqlen_q, (cudaStream_t)stream);
   // with a cached prefix (or chunked prefill) a query tile walks many key tiles however few queries
   // there are, which is where the pair kernel's ping-pong pays: 8 x 1024 new tokens over 8k-token
   // contexts 1,087 vs 573 TFLOP/s.  One query tile per sequence leaves nothing to pair.

@@ -41,4 +41,7 @@ int fail_cuda(int cuda_error, const char* where);
 int launch_prefill_tcgen05(const PrefillParams& p, int dtype, int head_dim, int num_seqs, int max_seqlen,
                            bool single_tile, cudaStream_t s);
 
+// fp32 tensors: CUDA-core kernel (prefill_f32.cu), dense or paged; returns MVL_OK or MVL_ERR_CUDA.
+int launch_prefill_f32(const PrefillParams& p, int head_dim, int num_seqs, int max_seqlen, cudaStream_t s);
+
 }  // namespace mvl

@@ -227,15 +227,16 @@ def flash_attention_prefill(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, c
     (total_tokens, num_heads, head_dim) tensor.  ``max_seqlen`` (keyword-only) sizes the grid
     without reading ``cu_seqlens`` back; when omitted it is read from the device, as the
     reference does (attention.py:263-264).  ``flags``: ``_ext.PREFILL_MMA_SYNC`` / ``PREFILL_ONE_TILE`` /
-    ``PREFILL_PAIR`` force one kernel (default: by max_seqlen, see include/mvl_abi.h).  bf16 / fp16 only."""
+    ``PREFILL_PAIR`` force one kernel (default: by max_seqlen, see include/mvl_abi.h).  bf16 / fp16 on the
+    tensor cores; fp32 (the reference's default dtype) on a CUDA-core kernel."""
     dev = _need_cuda(q=q, k=k, v=v, cu_seqlens=cu_seqlens)
     if q.dim() != 3 or k.dim() != 3 or v.shape != k.shape or q.shape[0] != k.shape[0]:
         raise ValueError("q must be (T, H, D) and k, v (T, KVH, D)")
     total, H, D = q.shape
     if (H, D) != (num_heads, head_dim) or k.shape[1:] != (num_kv_heads, head_dim):
         raise ValueError("tensor shapes do not match num_heads / num_kv_heads / head_dim")
-    if q.dtype not in (torch.bfloat16, torch.float16) or k.dtype != q.dtype or v.dtype != q.dtype:
-        raise NotImplementedError("prefill attention runs on the tensor cores: bf16 or fp16 inputs only")
+    if q.dtype not in (torch.bfloat16, torch.float16, torch.float32) or k.dtype != q.dtype or v.dtype != q.dtype:
+        raise NotImplementedError("prefill attention takes bf16 / fp16 (tensor cores) or fp32 (CUDA cores) inputs")
 
     def rows(x, heads):
         dense = x.stride(2) == 1 and x.stride(1) == D and (total <= 1 or x.stride(0) >= heads * D)
@@ -268,7 +269,7 @@ def flash_attention_prefill_paged(q: torch.Tensor, k_cache: torch.Tensor, v_cach
     sequence — a cached prefix plus the new tokens, whose K/V must already be in the cache.  This is
     what the reference's prefill branch is handed when a prefix was cached (``block_tables`` set,
     ``cu_seqlens_k > cu_seqlens_q``, model_runner.py:209-215) and does not do (attention.py:514-525,
-    SURVEY.md A-8); it also serves chunked prefill.  bf16 / fp16, ``scale > 0``.  Returns
+    SURVEY.md A-8); it also serves chunked prefill.  bf16 / fp16 (``scale > 0``) or fp32.  Returns
     (total_q_tokens, num_heads, head_dim)."""
     dev = _need_cuda(q=q, k_cache=k_cache, v_cache=v_cache, cu_seqlens_q=cu_seqlens_q,
                      block_tables=block_tables, context_lens=context_lens)
@@ -277,10 +278,11 @@ def flash_attention_prefill_paged(q: torch.Tensor, k_cache: torch.Tensor, v_cach
     if k_cache.dim() != 4 or k_cache.shape != v_cache.shape or k_cache.shape[1:] != (
             block_size, num_kv_heads, head_dim) or not (k_cache.is_contiguous() and v_cache.is_contiguous()):
         raise ValueError("caches must be contiguous (num_blocks, block_size, num_kv_heads, head_dim)")
-    if q.dtype not in (torch.bfloat16, torch.float16) or k_cache.dtype != q.dtype or v_cache.dtype != q.dtype:
-        raise NotImplementedError("prefill attention runs on the tensor cores: bf16 or fp16 only")
-    if not scale > 0:
-        raise ValueError("paged prefill needs scale > 0")
+    if q.dtype not in (torch.bfloat16, torch.float16, torch.float32) or k_cache.dtype != q.dtype or \
+            v_cache.dtype != q.dtype:
+        raise NotImplementedError("prefill attention takes bf16 / fp16 (tensor cores) or fp32 (CUDA cores) inputs")
+    if q.dtype != torch.float32 and not scale > 0:
+        raise ValueError("paged prefill on the tensor cores needs scale > 0")
     total, H, D = q.shape
     dense = q.stride(2) == 1 and q.stride(1) == D and (total <= 1 or q.stride(0) >= H * D)
     q = q if dense else q.contiguous()

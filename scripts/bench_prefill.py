@@ -9,11 +9,11 @@ for a in sys.argv:   # --lib=NAME: use minivllm_b200/csrc/NAME (experiment build
 SIZES = ((2, 16384),) if "--long" in sys.argv else ((8, 1024), (4, 4096), (2, 16384))
 from minivllm_b200.layers.attention import flash_attention_prefill
 FLAGS = 1 if "--mma-sync" in sys.argv else 2 if "--single" in sys.argv else 4 if "--pair" in sys.argv else 0
-KERNEL = {0: "auto", 1: "flash_prefill_kernel (mma.sync)", 2: "flash_prefill_tcgen05_kernel", 4: "flash_prefill_tcgen05_pair_kernel"}[FLAGS]
+KERNEL = "flash_prefill_f32_kernel" if "--fp32" in sys.argv else {0: "auto", 1: "flash_prefill_kernel (mma.sync)", 2: "flash_prefill_tcgen05_kernel", 4: "flash_prefill_tcgen05_pair_kernel"}[FLAGS]
 dev = torch.device("cuda", 0)
 peak = json.load(open("MEASURED_PEAKS.json"))["bf16_tflops"] if os.path.exists("MEASURED_PEAKS.json") else 1590.0
 H, KVH = 32, 8
-DT = torch.float16 if "--fp16" in sys.argv else torch.bfloat16
+DT = torch.float16 if "--fp16" in sys.argv else torch.float32 if "--fp32" in sys.argv else torch.bfloat16
 D = 64 if "--d64" in sys.argv else 128
 for nseq, n in SIZES:
     T = nseq * n
@@ -41,5 +41,5 @@ for nseq, n in SIZES:
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 10
     flops = 4.0 * D * H * nseq * n * (n + 1) / 2
-    print(json.dumps({"kernel": KERNEL, "seqs": nseq, "len": n, "shape": f"{H}Q/{KVH}KV/D{D} " + ("fp16" if DT == torch.float16 else "bf16"),
+    print(json.dumps({"kernel": KERNEL, "seqs": nseq, "len": n, "shape": f"{H}Q/{KVH}KV/D{D} " + {torch.float16: "fp16", torch.float32: "fp32", torch.bfloat16: "bf16"}[DT],
                       "ms": ms, "TFLOPs": flops / ms / 1e9, "frac_of_measured_bf16_peak": flops / ms / 1e9 / peak}))

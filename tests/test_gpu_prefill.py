@@ -116,10 +116,13 @@ def test_attention_forward_prefill_then_decode(cuda_device):
     assert err.max() <= 0
 
 
-def test_prefill_rejects_fp32(cuda_device):
-    q = torch.zeros(4, 2, 64, device=cuda_device)
+def test_prefill_rejects_unsupported_dtypes(cuda_device):
+    q = torch.zeros(4, 2, 64, device=cuda_device, dtype=torch.float64)
     with pytest.raises(NotImplementedError):
         flash_attention_prefill(q, q, q, torch.tensor([0, 4], device=cuda_device), 1.0, 2, 2, 64)
+    q16 = q.to(torch.bfloat16)
+    with pytest.raises(NotImplementedError):   # mixed dtypes
+        flash_attention_prefill(q16, q16, q.float(), torch.tensor([0, 4], device=cuda_device), 1.0, 2, 2, 64)
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
@@ -243,3 +246,76 @@ def test_attention_forward_prefill_with_cached_prefix(cuda_device):
     want = prefill_oracle.causal_paged_attention(c["q"], c["kc"], c["vc"], c["cu_q"], c["bt"], c["ctx"],
                                                  1.0 / D ** 0.5, H, KVH, D, BS)
     _check(out.view(-1, H, D), want)
+
+
+# ------------------------------------------------------------------ fp32 (the reference's default dtype)
+def _check_f32(got, want):
+    got, want = got.double().cpu().numpy(), want.double().cpu().numpy()
+    excess = np.abs(got - want) - (2e-5 + 1e-5 * np.abs(want))
+    assert np.isfinite(got).all() and excess.max() <= 0, f"max excess {excess.max():.3e}"
+
+
+@pytest.mark.parametrize("H,KVH,D", [(8, 2, 128), (6, 6, 64)])
+@pytest.mark.parametrize("scale_sign", [1.0, -1.0])
+def test_prefill_fp32(cuda_device, H, KVH, D, scale_sign):
+    """fp32 q/k/v through the CUDA-core kernel, inside north_star's 1e-4 for fp32 (here 2e-5 + 1e-5 |w|
+    against the float64 oracle): ragged lengths around the 64-row tile edges, strided views of a fused
+    projection, either scale sign (the maximum is taken on scaled scores)."""
+    g = torch.Generator().manual_seed(H + D)
+    lens = [1, 63, 64, 65, 130, 700]
+    total = sum(lens)
+    qkv = torch.randn(total, (H + 2 * KVH) * D, generator=g)
+    q, k, v = (x.view(total, -1, D) for x in qkv.split([H * D, KVH * D, KVH * D], dim=-1))
+    cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32)
+    scale = scale_sign / D ** 0.5
+    dq, dk, dv = (x.view(total, -1, D) for x in qkv.to(cuda_device).split([H * D, KVH * D, KVH * D], dim=-1))
+    out = flash_attention_prefill(dq, dk, dv, cu.to(cuda_device), scale, H, KVH, D)
+    assert out.dtype == torch.float32
+    _check_f32(out, prefill_oracle.causal_varlen_attention(q, k, v, cu, scale, H, KVH, D))
+
+
+@pytest.mark.parametrize("BS", [16, 256])
+def test_paged_prefill_fp32(cuda_device, BS):
+    H, KVH, D = 4, 2, 128
+    lens_ctx, lens_new = [300, 128, 1000, 65, 77], [300, 64, 257, 1, 13]
+    c = _paged_case(BS, lens_ctx, lens_new, H, KVH, D, BS, torch.float32)
+    out = flash_attention_prefill_paged(c["q"].to(cuda_device), c["kc"].to(cuda_device), c["vc"].to(cuda_device),
+                                        c["cu_q"].to(cuda_device), c["bt"].to(cuda_device), c["ctx"].to(cuda_device),
+                                        1.0 / D ** 0.5, H, KVH, D, BS)
+    _check_f32(out, prefill_oracle.causal_paged_attention(c["q"], c["kc"], c["vc"], c["cu_q"], c["bt"], c["ctx"],
+                                                          1.0 / D ** 0.5, H, KVH, D, BS))
+
+
+def test_attention_forward_prefill_fp32_then_decode(cuda_device):
+    """The reference's default dtype end to end through Attention.forward: fp32 prefill (store + causal
+    attention), then an fp32 decode step over what it stored."""
+    from oracle import c_oracle
+    H, KVH, D, BS = 4, 2, 64, 16
+    g = torch.Generator().manual_seed(21)
+    lens = [50, 17]
+    total = sum(lens)
+    q, k, v = (torch.randn(total, n, D, generator=g) for n in (H, KVH, KVH))
+    cu = torch.tensor([0, 50, 67], dtype=torch.int32)
+    tables = torch.tensor([[3, 0, 5, 6], [2, 4, -1, -1]], dtype=torch.int32)
+    slots = torch.cat([tables[b, torch.arange(n) // BS].long() * BS + torch.arange(n) % BS for b, n in enumerate(lens)])
+    layer = Attention(H, D, scale=1.0, num_kv_heads=KVH, block_size=BS)
+    layer.k_cache = torch.zeros(8, BS, KVH, D, device=cuda_device)
+    layer.v_cache = torch.zeros_like(layer.k_cache)
+    set_context(True, cu_seqlens_q=cu.to(cuda_device), cu_seqlens_k=cu.to(cuda_device), max_seqlen_q=50,
+                max_seqlen_k=50, slot_mapping=slots.to(cuda_device))
+    try:
+        out = layer(q.to(cuda_device), k.to(cuda_device), v.to(cuda_device))
+    finally:
+        reset_context()
+    _check_f32(out.view(total, H, D), prefill_oracle.causal_varlen_attention(q, k, v, cu, 1.0 / D ** 0.5, H, KVH, D))
+    qd, kd, vd = (torch.randn(2, n, D, generator=g) for n in (H, KVH, KVH))
+    ctx = torch.tensor([51, 18])
+    dslots = tables[torch.arange(2), (ctx - 1) // BS].long() * BS + (ctx - 1) % BS
+    set_context(False, slot_mapping=dslots.to(cuda_device), context_lens=ctx.to(cuda_device),
+                block_tables=tables.to(cuda_device))
+    try:
+        od = layer(qd.to(cuda_device), kd.to(cuda_device), vd.to(cuda_device))
+    finally:
+        reset_context()
+    wd = c_oracle.paged_decode(qd, layer.k_cache.cpu(), layer.v_cache.cpu(), tables, ctx, 1.0 / D ** 0.5, H, KVH, D, BS)
+    assert (od.cpu().view(2, H, D) - wd).abs().max() <= 1e-4
