@@ -145,3 +145,35 @@ def test_nccl_gather_on_real_ranks(cuda_device):
         ret = mgr.dict()
         mp.spawn(_nccl_worker, args=(world, port, ret), nprocs=world, join=True)
         assert dict(ret) == {r: True for r in range(world)}
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_prefill_equals_unsharded_bitwise(cuda_device, world):
+    """The prefill branch shards the same way (heads are independent; strided head slices of q/k/v go
+    straight to the kernels as views): per-rank outputs concatenated over heads == the unsharded run,
+    dense and over cached pages."""
+    from minivllm_b200.layers.attention import flash_attention_prefill, flash_attention_prefill_paged
+    from test_oracle_golden import _paged_case
+    H, KVH, D, BS = 16, 4, 128, 16
+    lens_ctx, lens_new = [700, 300, 129], [700, 44, 129]
+    c = _paged_case(world, lens_ctx, lens_new, H, KVH, D, BS, torch.bfloat16)
+    dev = cuda_device
+    q, kc, vc = c["q"].to(dev), c["kc"].to(dev), c["vc"].to(dev)
+    cu_q, bt, ctx = c["cu_q"].to(dev), c["bt"].to(dev), c["ctx"].to(dev)
+    scale = 1.0 / D ** 0.5
+    full_p = flash_attention_prefill_paged(q, kc, vc, cu_q, bt, ctx, scale, H, KVH, D, BS)
+    k_all = torch.cat(c["k_full"]).to(dev)
+    v_all = torch.cat(c["v_full"]).to(dev)
+    q_all = torch.randn(sum(lens_ctx), H, D, generator=torch.Generator().manual_seed(1)).to(torch.bfloat16).to(dev)
+    cu_k = torch.tensor([0, 700, 1000, 1129], dtype=torch.int32, device=dev)
+    full_d = flash_attention_prefill(q_all, k_all, v_all, cu_k, scale, H, KVH, D)
+    parts_p, parts_d = [], []
+    for r in range(world):
+        sh = shard_plan(H, KVH, world, r)
+        parts_p.append(flash_attention_prefill_paged(q[:, sh.q_heads], kc[:, :, sh.kv_heads].contiguous(),
+                                                     vc[:, :, sh.kv_heads].contiguous(), cu_q, bt, ctx, scale,
+                                                     sh.num_heads, sh.num_kv_heads, D, BS))
+        parts_d.append(flash_attention_prefill(q_all[:, sh.q_heads], k_all[:, sh.kv_heads], v_all[:, sh.kv_heads],
+                                               cu_k, scale, sh.num_heads, sh.num_kv_heads, D))
+    assert torch.equal(torch.cat(parts_p, dim=1), full_p)
+    assert torch.equal(torch.cat(parts_d, dim=1), full_d)
