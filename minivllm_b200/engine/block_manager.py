@@ -105,6 +105,23 @@ class PrefixBlockManager:
     def can_allocate(self, seq: PrefixSeq) -> bool:
         return len(self.free_block_ids) >= self._blocks_needed(len(seq))
 
+    def cached_prefix_tokens(self, seq: PrefixSeq) -> int:
+        """How many leading tokens ``allocate`` would serve from the cache — a look-up with no side
+        effects (the scheduler budgets a prefill step by the tokens that still have to be computed)."""
+        bs, n = self.block_size, len(seq)
+        h: Optional[int] = None
+        cached = 0
+        for i in range(self._blocks_needed(n)):
+            tokens = seq.token_ids[i * bs:(i + 1) * bs]
+            if len(tokens) < bs or (i + 1) * bs >= n:
+                break
+            h = self.compute_hash(tokens, h)
+            cand = self.hash_to_block_id.get(h, -1)
+            if cand == -1 or self.blocks[cand].token_ids != tokens:
+                break
+            cached += bs
+        return cached
+
     def allocate(self, seq: PrefixSeq) -> None:
         """Give every block of the prompt a page; leading full blocks found in the cache are shared
         (``seq.num_cached_tokens`` counts their tokens)."""

@@ -202,3 +202,50 @@ def test_prefix_block_manager_shares_and_frees_pages():
     assert f.num_cached_tokens == 8
     with pytest.raises(MemoryError):
         mgr.allocate(PrefixSeq(list(range(1000, 1000 + 4 * 20))))
+
+
+def test_scheduler_prefill_first_decode_preempt_finish():
+    """N1: the reference's scheduling policy (scheduler.py:25-82) over the prefix block manager —
+    prefill first under the token budget (counting only uncached tokens), then one token per running
+    sequence, preemption of the youngest when the pool runs dry, retirement at max_tokens / EOS —
+    with lengths and tables that actually advance (A-3)."""
+    from minivllm_b200.engine import EngineSeq, Scheduler
+    BS = 4
+    sch = Scheduler(max_num_sequences=3, max_num_batched_tokens=16, max_cached_blocks=9, block_size=BS, eos=99)
+    a = EngineSeq(list(range(10)), max_tokens=3)
+    b = EngineSeq(list(range(8)) + [50, 51], max_tokens=8)      # shares two blocks with a
+    c = EngineSeq(list(range(200, 207)), max_tokens=2)
+    for s in (a, b, c):
+        sch.add_sequence(s)
+    seqs, is_prefill = sch.schedule()
+    # a: 10 new tokens; b: 2 new (8 cached, published by a's allocation) -> 12 <= 16; c: 7 more would exceed 16
+    assert is_prefill and seqs == [a, b] and b.num_cached_tokens == 8 and b.block_table[:2] == a.block_table[:2]
+    sch.postprocess(seqs, [1, 2])
+    assert len(a) == 11 and len(b) == 11 and a.num_completion_tokens == 1
+    seqs, is_prefill = sch.schedule()
+    assert is_prefill and seqs == [c]                           # prefill goes first while anything waits
+    sch.postprocess(seqs, [3])
+    seqs, is_prefill = sch.schedule()                           # decode: a, b, c in admission order
+    assert not is_prefill and seqs == [a, b, c]
+    assert [len(s.block_table) for s in seqs] == [3, 3, 2]      # 11 tokens -> 3 pages, 8 tokens -> 2 pages
+    sch.postprocess(seqs, [4, 5, 99])                           # c hits EOS
+    assert c.status == "finished" and c not in sch.running and not c.block_table
+    seqs, _ = sch.schedule()
+    assert seqs == [a, b] and len(a) == 12
+    sch.postprocess(seqs, [6, 7])                               # a reaches max_tokens = 3
+    assert a.status == "finished" and sch.block_manager.blocks[b.block_table[0]].ref_count == 1
+    # b (grows to 18 tokens, 5 pages) and d (to 32 tokens, 8 pages) cannot both stay in 9 pages: preemption
+    d = EngineSeq(list(range(300, 312)), max_tokens=20)
+    sch.add_sequence(d)
+    seqs, is_prefill = sch.schedule()
+    assert is_prefill and seqs == [d]
+    sch.postprocess(seqs, [8])
+    steps = 0
+    while not sch.is_finished() and steps < 200:
+        seqs, is_prefill = sch.schedule()
+        assert seqs
+        sch.postprocess(seqs, [9] * len(seqs))
+        steps += 1
+    assert sch.is_finished() and sch.num_preemptions >= 1
+    assert b.num_completion_tokens == 8 and d.num_completion_tokens == 20
+    assert len(sch.block_manager.free_block_ids) == 9
