@@ -53,7 +53,7 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
 // Ends with tcgen05.wait::st: the caller fences and signals.
 template <typename T, int D>
 __device__ __forceinline__ void softmax_step(uint32_t s_addr, uint32_t o_addr, bool first, int lim, float qs,
-                                             float& m_ref, float& l) {
+                                             float& m_ref, float& l, uint32_t half_bar = 0) {
   using M = MmaType<T>;
   uint32_t su[128];
 #pragma unroll
@@ -94,20 +94,30 @@ __device__ __forceinline__ void softmax_step(uint32_t s_addr, uint32_t o_addr, b
   const float neg = -m_ref * qs;
   const u64 qs2 = pack2(qs, qs), neg2 = pack2(neg, neg);
   u64 acc[4] = {0ull, 0ull, 0ull, 0ull};
-  uint32_t pk[64];
+  // P in two halves of 64 keys: with half_bar set, the first half is published as soon as it is in
+  // TMEM, so that the first four MMAs of P.V run while the second half's exponentials do
 #pragma unroll
-  for (int c = 0; c < 64; ++c) {
-    float x0, x1;
-    unpack2(ffma2(pack2(__uint_as_float(su[2 * c]), __uint_as_float(su[2 * c + 1])), qs2, neg2), x0, x1);
-    // MUFU.EX2 for every element: a polynomial 2^x on the FMA pipe for 1, 2 or 3 of every 4 column
-    // pairs was measured slower (1175 / 1104 / 1023 vs 1202 TFLOP/s at 2 x 16k tokens)
-    const float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
-    acc[c & 3] = fadd2(acc[c & 3], pack2(p0, p1));
-    pk[c] = M::pack(p0, p1);
+  for (int half = 0; half < 2; ++half) {
+    uint32_t pk[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) {
+      const int cc = half * 32 + c;
+      float x0, x1;
+      unpack2(ffma2(pack2(__uint_as_float(su[2 * cc]), __uint_as_float(su[2 * cc + 1])), qs2, neg2), x0, x1);
+      // MUFU.EX2 for every element: a polynomial 2^x on the FMA pipe for 1, 2 or 3 of every 4 column
+      // pairs was measured slower (1175 / 1104 / 1023 vs 1202 TFLOP/s at 2 x 16k tokens)
+      const float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
+      acc[c & 3] = fadd2(acc[c & 3], pack2(p0, p1));
+      pk[c] = M::pack(p0, p1);
+    }
+    tc5::tmem_st32(s_addr + half * 32, pk);
+    if (half == 0 && half_bar != 0) {
+      tc5::tmem_wait_st();
+      tc5::fence_before_sync();
+      tc5::mbar_arrive(half_bar);
+    }
   }
   l += hsum2(fadd2(fadd2(acc[0], acc[1]), fadd2(acc[2], acc[3])));
-  tc5::tmem_st32(s_addr, pk);
-  tc5::tmem_st32(s_addr + 32, pk + 32);
   tc5::tmem_wait_st();
 }
 
@@ -316,7 +326,7 @@ template <int D>
 struct PairCfg {
   static constexpr int PANELS = D / 64, PANEL_BYTES = 128 * 128, TILE_BYTES = PANELS * PANEL_BYTES;
   static constexpr int OFF_K = 2 * TILE_BYTES, OFF_V = 4 * TILE_BYTES, OFF_BAR = 6 * TILE_BYTES;
-  static constexpr int NEED = OFF_BAR + 128 + 1024;
+  static constexpr int NEED = OFF_BAR + 160 + 1024;
   // one CTA per SM (it allocates all 512 TMEM columns): ask for more than half the SM's shared memory
   static constexpr int SMEM = NEED > 120 * 1024 ? NEED : 120 * 1024;
   static constexpr int TMEM_COLS = 512;  // S0 [0,128) S1 [128,256) O0 [256,256+D) O1 [256+D, 256+2D)
@@ -334,8 +344,8 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sQ = base, sK = base + C::OFF_K, sV = base + C::OFF_V, bars = base + C::OFF_BAR;
   const uint32_t q_full = bars, k_full = bars + 8, v_full = bars + 24, s_full = bars + 40, p_ready = bars + 56,
-                 o_done = bars + 72, k_empty = bars + 88, v_empty = bars + 104,
-                 tmem_slot = bars + 120;  // pairs of barriers: [i] at + 8 * i
+                 o_done = bars + 72, k_empty = bars + 88, v_empty = bars + 104, p_half = bars + 120,
+                 tmem_slot = bars + 136;  // pairs of barriers: [i] at + 8 * i
 
   const int tid = threadIdx.x, warp = tid >> 5;
   const int mb2 = gridDim.x - 1 - blockIdx.x;  // heaviest (latest) query tiles first
@@ -359,7 +369,7 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
     for (int i = 0; i < 2; ++i) {
       mbar_init(k_full + 8 * i, 1), mbar_init(v_full + 8 * i, 1), mbar_init(s_full + 8 * i, 1);
       mbar_init(p_ready + 8 * i, 128), mbar_init(o_done + 8 * i, 1);
-      mbar_init(k_empty + 8 * i, 1), mbar_init(v_empty + 8 * i, 1);
+      mbar_init(k_empty + 8 * i, 1), mbar_init(v_empty + 8 * i, 1), mbar_init(p_half + 8 * i, 128);
     }
     mbar_fence_init();
   }
@@ -412,12 +422,19 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
         }
         tc5::commit(s_full + 8 * w);
       };
-      auto issue_pv = [&](int w, int j) {  // O_w += P_w . V_j
+      auto issue_pv = [&](int w, int j) {  // O_w += P_w . V_j, the first 64 keys as soon as their P is in TMEM
         const uint32_t v = v_lo + (j & 1) * STAGE;
+        tc5::mbar_wait_bounded(p_half + 8 * w, j & 1);
+        tc5::fence_after_sync();
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk)
+        for (int kk = 0; kk < 4; ++kk)
           tc5::mma_ts(tmem + 256 + w * D, tmem + w * 128 + kk * 8, tc5::desc64(v + kk * (2048 >> 4), HI), IDESC_PV,
                       (j > 0 || kk > 0) ? 1u : 0u);
+        tc5::mbar_wait_bounded(p_ready + 8 * w, j & 1);
+        tc5::fence_after_sync();
+#pragma unroll
+        for (int kk = 4; kk < 8; ++kk)
+          tc5::mma_ts(tmem + 256 + w * D, tmem + w * 128 + kk * 8, tc5::desc64(v + kk * (2048 >> 4), HI), IDESC_PV, 1u);
       };
       tc5::mbar_wait_bounded(q_full, 0);
       tc5::mbar_wait_bounded(k_full, 0);
@@ -430,8 +447,6 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
         tc5::mbar_wait_bounded(v_full + 8 * st, (j >> 1) & 1);
         bool k_next_seen = false;
         if (j < n0) {
-          tc5::mbar_wait_bounded(p_ready, j & 1);
-          tc5::fence_after_sync();
           issue_pv(0, j);
           if (j == n0 - 1) tc5::commit(o_done);
           if (j >= n1) tc5::commit(v_empty + 8 * st);   // tile 1 does not read V_j
@@ -444,8 +459,6 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
           }
         }
         if (j < n1) {
-          tc5::mbar_wait_bounded(p_ready + 8, j & 1);
-          tc5::fence_after_sync();
           issue_pv(1, j);
           if (j == n1 - 1) tc5::commit(o_done + 8);
           tc5::commit(v_empty + 8 * st);
@@ -472,7 +485,7 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
     for (int j = 0; j < nw; ++j) {
       tc5::mbar_wait_bounded(s_full + 8 * w, j & 1);  // S_w(j) complete; so is the product of step j-1
       tc5::fence_after_sync();
-      softmax_step<T, D>(s_addr, o_addr, j == 0, qa0 + w * 128 + t - j * 128, qs, m_ref, l);
+      softmax_step<T, D>(s_addr, o_addr, j == 0, qa0 + w * 128 + t - j * 128, qs, m_ref, l, p_half + 8 * w);
       tc5::fence_before_sync();
       tc5::mbar_arrive(p_ready + 8 * w);
     }
