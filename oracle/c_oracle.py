@@ -5,7 +5,6 @@ import ctypes as C
 import os
 import subprocess
 
-import numpy as np
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))

@@ -1,5 +1,5 @@
 """Step-time, SM-clock and power trajectory of a long C3 run (is the sustained regime power-capped?)."""
-import os, sys, threading, time, json
+import os, sys, threading, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch, pynvml
 import workloads

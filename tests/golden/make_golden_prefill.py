@@ -4,7 +4,6 @@ container.  Writes tests/golden/prefill_<case>.npz: ref_out_bits (the reference 
 dtype, raw 16-bit patterns), ref_out_f32 (reference fed fp32-upcast inputs, every third token),
 digest of the seeded inputs.
     python tests/golden/make_golden_prefill.py"""
-import hashlib
 import os
 import sys
 
