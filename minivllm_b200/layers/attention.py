@@ -218,6 +218,11 @@ def paged_attention_decode(query: torch.Tensor, k_cache: torch.Tensor, v_cache: 
     return out
 
 
+# the reference's benchmarks import the decode operator under this name (benchmark_decoding.py:107-118,
+# benchmark_models.py:118); same signature, same kernel
+paged_attention_decode_triton = paged_attention_decode
+
+
 def flash_attention_prefill(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens: torch.Tensor,
                             scale: float, num_heads: int, num_kv_heads: int, head_dim: int,
                             *, max_seqlen: Optional[int] = None, flags: int = 0) -> torch.Tensor:
