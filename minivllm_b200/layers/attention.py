@@ -59,7 +59,15 @@ def _index_flag(name: str, t: torch.Tensor) -> int:
     raise ValueError(f"{name} must be int32 or int64, got {t.dtype}")
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream_ptr(dev: torch.device) -> int:
+    """cudaStream_t of torch's current stream on ``dev``.  The raw getter avoids building a
+    torch.cuda.Stream object per call (~3 us each, twice per operator call, out of ~23 us of host time
+    for a decode step at a tiny shape)."""
+    if _raw_stream is not None:
+        return _raw_stream(dev.index if dev.index is not None else torch.cuda.current_device())
     return torch.cuda.current_stream(dev).cuda_stream
 
 
