@@ -13,8 +13,10 @@
 // causal diagonal (the reference walks every block and masks).  Scores and P.V run on the tensor
 // cores (mma.sync m16n8k16, fp32 accumulate) with the FlashAttention-2 register layout: q as A
 // fragments, K via ldmatrix, online softmax on the accumulator rows (quad shuffles), P re-packed to
-// 16-bit A fragments, V via ldmatrix.trans.  First version: functional and parity-tested; it is
-// compute-bound work whose B200-native form is tcgen05/TMEM (next round).
+// 16-bit A fragments, V via ldmatrix.trans.  This mma.sync kernel serves batches of short sequences
+// (max_seqlen <= 64) and non-positive scales; longer ones go to the tcgen05 kernels
+// (prefill_tcgen05.cu, 3-4x faster), fp32 tensors to prefill_f32.cu.  This file also holds the two
+// C entry points, mvl_flash_prefill and mvl_flash_prefill_paged, and the kernel choice.
 #include "common.cuh"
 #include "host.h"
 #include "paged_decode_mma.cuh"
