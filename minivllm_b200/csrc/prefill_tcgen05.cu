@@ -1,19 +1,23 @@
 // prefill_tcgen05.cu — varlen causal GQA flash attention on the 5th-generation tensor cores.
 //
-// SURVEY.md §8(f) row N3, second version: the same contract as prefill.cu (reference
-// src/myvllm/layers/attention.py:111-209 and :212-280) with both matrix products on tcgen05.mma:
+// the contract of reference src/myvllm/layers/attention.py:111-209 and
+// :212-280 (and, with PAGED, of the cached-prefix case the reference sets up in
+// model_runner.py:209-215 but does not compute, A-8) with both matrix products on tcgen05.mma:
 //   S (128 x 128, fp32, TMEM)  = Q (128 x D, smem, K-major)  . K^T (128 keys x D, smem, K-major)
 //   O (128 x D,  fp32, TMEM) += P (128 x 128, 16-bit, TMEM)  . V   (128 keys x D, smem, MN-major)
-// One CTA = 128 queries of one sequence for one query head, 128 threads, thread t owns query row t
-// (TMEM lane t): a whole score row arrives in its registers with tcgen05.ld, so the softmax needs
-// no shuffles.  Q, K and V tiles are brought in by TMA (tensor maps over the packed tensors, 128-byte
-// swizzle, rows past the tensor end zero-filled) and signal mbarriers; thread 0 issues the TMA loads
-// and the MMAs, tcgen05.commit signals their completion.  P overwrites the first 64 columns of S
-// (two 16-bit values per column) and is the A operand of the second product straight from TMEM.
-// The running maximum is lazy: the reference exponent m_ref is refreshed (and O rescaled in TMEM)
-// only when a row's maximum grows by more than 2^8, which after the first tile is rare.
-// Two CTAs per SM (96 KB shared memory and 256 TMEM columns each): one CTA's softmax overlaps the
-// other's MMAs.  K tile j+1 is loaded during softmax j, V tile j as soon as product j-1 has retired.
+// Thread t of a 128-thread group owns query row t (TMEM lane t): a whole score row arrives in its
+// registers with tcgen05.ld, so the softmax needs no shuffles.  Q, K and V tiles are brought in by TMA
+// (tensor maps over the packed tensors or over the paged cache, 128-byte swizzle, rows outside the
+// map zero-filled) and signal mbarriers; tcgen05.commit signals MMA completion.  P overwrites the first
+// 64 columns of S (two 16-bit values per column) and is the A operand of the second product straight
+// from TMEM.  The running maximum is lazy: the reference exponent m_ref is refreshed (and O rescaled
+// in TMEM) only when a row's maximum grows by more than 2^8, which after the first tile is rare.
+// Two kernels share the softmax step and the tile loads:
+//   flash_prefill_tcgen05_kernel       one 128-query tile per CTA, 128 threads, two CTAs per SM (96 KB
+//                                      shared memory, 256 TMEM columns each): one CTA's softmax overlaps
+//                                      the other's MMAs; warp 0 issues loads, thread 0 the MMAs
+//   flash_prefill_tcgen05_pair_kernel  two tiles per CTA in ping-pong, one CTA per SM, dedicated TMA and
+//                                      MMA warps, setmaxnreg (described at its definition)
 #include "common.cuh"
 #include "paged_decode_mma.cuh"
 #include "prefill.h"
