@@ -32,6 +32,18 @@ def activations(toks, pos):
     return x[:, :, :H], x[:, :, H:H + KVH], x[:, :, H + KVH:]
 
 
+# warm-up on a throw-away engine: first-use costs (kernel attributes, module load, pinned buffers)
+_r = DecodeRunner(L, H, KVH, D, BS, 16, 4, 4 * BS, torch.bfloat16, dev, enforce_eager=True)
+_s = Scheduler(4, 16384, 16, BS, eos=-1)
+_e = AttentionEngine(_r, _s, activations, lambda seqs, out: [1] * len(seqs))
+_p = torch.randint(0, 30000, (2 * BS,), generator=g).tolist()
+for tail in (5, 300):
+    _e.add_prompt(_p + list(range(tail)), max_tokens=3, ignore_eos=True)
+    _e.step()
+_e.run_to_completion()
+torch.cuda.synchronize()
+del _r, _s, _e
+
 eng = AttentionEngine(runner, sch, activations, lambda seqs, out: [1] * len(seqs))
 shared = torch.randint(0, 30000, (SHARED,), generator=g).tolist()
 for i in range(NSEQ):
@@ -49,6 +61,8 @@ while not sch.is_finished():
     dt = time.perf_counter() - t0
     if is_prefill:
         t_prefill += dt; n_prefill_steps += 1
+        if "--verbose" in sys.argv:
+            print(f"prefill step: {len(seqs)} prompts, {1e3 * dt:.2f} ms", file=sys.stderr)
     else:
         t_decode += dt; n_decode_steps += 1; decode_seqs += len(seqs)
 wall = time.perf_counter() - t_all0
