@@ -224,9 +224,11 @@ class DecodeRunner:
         ``q`` (L, T, H, D), ``k``/``v`` (L, T, KVH, D) as the projections would have produced them.
         Stores K/V into the pages and returns (L, T, H*D).  Eager, as in the reference (graphs are
         for decode only, model_runner.py:292-300)."""
-        outs = [layer(q[i], k[i], v[i]) for i, layer in enumerate(self.layers)]
+        out = torch.empty(self.L, q.shape[1], self.H * self.D, dtype=q.dtype, device=q.device)
+        for i, layer in enumerate(self.layers):
+            layer(q[i], k[i], v[i], out=out[i].view(-1, self.H, self.D))
         reset_context()
-        return torch.stack(outs)
+        return out
 
     # ------------------------------------------------------------------ the layer loop
     def _forward_layers(self, bucket: int) -> None:

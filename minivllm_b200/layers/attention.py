@@ -233,7 +233,8 @@ paged_attention_decode_triton = paged_attention_decode
 
 def flash_attention_prefill(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens: torch.Tensor,
                             scale: float, num_heads: int, num_kv_heads: int, head_dim: int,
-                            *, max_seqlen: Optional[int] = None, flags: int = 0) -> torch.Tensor:
+                            *, max_seqlen: Optional[int] = None, flags: int = 0,
+                            out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Causal attention over packed variable-length sequences (prefill), reference signature
     (attention.py:212-221).  q (total_tokens, num_heads, head_dim); k, v (total_tokens,
     num_kv_heads, head_dim); cu_seqlens (num_seqs + 1) cumulative lengths.  Returns a new
@@ -259,7 +260,10 @@ def flash_attention_prefill(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, c
     (q, qs), (k, ks), (v, vs) = rows(q, H), rows(k, num_kv_heads), rows(v, num_kv_heads)
     cu = cu_seqlens.to(torch.int32).contiguous()
     num_seqs = cu.numel() - 1
-    out = torch.empty((total, H, D), dtype=q.dtype, device=dev)
+    if out is None:
+        out = torch.empty((total, H, D), dtype=q.dtype, device=dev)
+    elif out.shape != (total, H, D) or out.dtype != q.dtype or out.device != dev or not out.is_contiguous():
+        raise ValueError("out must be a contiguous (total_tokens, num_heads, head_dim) tensor like q")
     if total == 0 or num_seqs <= 0:
         return out
     if max_seqlen is None:
@@ -276,7 +280,7 @@ def flash_attention_prefill_paged(q: torch.Tensor, k_cache: torch.Tensor, v_cach
                                   cu_seqlens_q: torch.Tensor, block_tables: torch.Tensor,
                                   context_lens: torch.Tensor, scale: float, num_heads: int, num_kv_heads: int,
                                   head_dim: int, block_size: int, *, max_seqlen_q: Optional[int] = None,
-                                  flags: int = 0) -> torch.Tensor:
+                                  flags: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Prefill attention over the paged cache: the ``n_s`` new queries of sequence ``s`` (packed in
     ``q`` and delimited by ``cu_seqlens_q``) attend causally to all ``context_lens[s]`` keys of the
     sequence — a cached prefix plus the new tokens, whose K/V must already be in the cache.  This is
@@ -307,7 +311,10 @@ def flash_attention_prefill_paged(q: torch.Tensor, k_cache: torch.Tensor, v_cach
     bt = block_tables if block_tables.dtype == torch.int32 and block_tables.stride(1) == 1 else \
         block_tables.to(torch.int32).contiguous()
     ctx = context_lens.contiguous()
-    out = torch.empty((total, H, D), dtype=q.dtype, device=dev)
+    if out is None:
+        out = torch.empty((total, H, D), dtype=q.dtype, device=dev)
+    elif out.shape != (total, H, D) or out.dtype != q.dtype or out.device != dev or not out.is_contiguous():
+        raise ValueError("out must be a contiguous (total_tokens, num_heads, head_dim) tensor like q")
     if total == 0 or num_seqs <= 0:
         return out
     if max_seqlen_q is None:
@@ -380,8 +387,9 @@ class Attention(nn.Module):
 
     def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *,
                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """``out`` (keyword-only, optional): a preallocated (batch, num_heads, head_dim) result
-        buffer, for callers that run under CUDA-graph capture with static buffers."""
+        """``out`` (keyword-only, optional): a preallocated (tokens, num_heads, head_dim) result
+        buffer, for callers that run under CUDA-graph capture with static buffers (decode) or that
+        collect the layers' results in one tensor (prefill)."""
         context = get_context()
         k_cache, v_cache = self.k_cache, self.v_cache
         block_size = self._effective_block_size()
@@ -413,11 +421,11 @@ class Attention(nn.Module):
                 o = flash_attention_prefill_paged(q, k_cache, v_cache, context.cu_seqlens_q,
                                                   context.block_tables, ctx_lens, scale, self.num_heads,
                                                   self.num_kv_heads, self.head_dim, block_size,
-                                                  max_seqlen_q=context.max_seqlen_q or None)
+                                                  max_seqlen_q=context.max_seqlen_q or None, out=out)
                 return o.reshape(o.shape[0], self.num_heads * self.head_dim)
             o = flash_attention_prefill(q, k, v, context.cu_seqlens_q, scale, self.num_heads,
                                         self.num_kv_heads, self.head_dim,
-                                        max_seqlen=context.max_seqlen_q or None)
+                                        max_seqlen=context.max_seqlen_q or None, out=out)
             return o.reshape(o.shape[0], self.num_heads * self.head_dim)
         if q.dim() == 4:  # (B, 1, H, D) -> (B, H, D)
             q = q.squeeze(1)
