@@ -79,6 +79,39 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def reference_triton_decode(w, alg_bytes, our_ms):
+    """Secondary GPU baseline: the reference's own Triton decode kernel — the
+    only pre-existing GPU implementation of the path — on this step's tensors, when the unmodified
+    reference package is installed under baseline/_ref (git-ignored).  Not the reference arm (that is
+    the CPU path, --impl reference); reported beside the headline, 2 warm-up + 5 timed launches."""
+    ref_root = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref_root, "myvllm")):
+        return {"unavailable": "baseline/_ref/myvllm not installed"}
+    sys.path.insert(0, ref_root)
+    try:
+        from myvllm.layers import attention as ref
+    finally:
+        sys.path.remove(ref_root)
+    call = lambda: ref.paged_attention_decode(w["q"], w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"],
+                                              w["scale"], w["H"], w["KVH"], w["D"], w["BS"])
+    for _ in range(2):
+        o_ref = call()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(5):
+        call()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 5
+    from minivllm_b200.layers.attention import paged_attention_decode
+    ours = paged_attention_decode(w["q"], w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"],
+                                  w["H"], w["KVH"], w["D"], w["BS"])
+    return {"kernel": "myvllm.layers.attention.paged_attention_decode (Triton, JIT for this GPU)", "ms_per_step": ms,
+            "GBps": alg_bytes / ms / 1e6, "ours_faster_by": ms / our_ms,
+            "max_abs_diff_ours_vs_reference_triton": float((ours.float() - o_ref.float()).abs().max())}
+
+
 def neighbour_kernels(dev):
     """The kernels either side of the hot path, each timed alone
     after the headline measurement: 3 warm-up + 10 timed launches, CUDA events, inputs larger than L2.
@@ -473,6 +506,10 @@ def run_ours(args, rank, world, local_rank):
         "clocks": clocks.summary(),
     }
     if world == 1 and args.workload == "c3" and args.shard_of == 1 and not args.no_neighbours:
+        try:
+            line["reference_triton"] = reference_triton_decode(w, alg_unique, ms_step)
+        except Exception as exc:
+            line["reference_triton"] = {"unavailable": repr(exc)[:200]}
         try:
             line["neighbours"] = neighbour_kernels(dev)
         except Exception as exc:   # the headline line must not depend on them
