@@ -319,3 +319,55 @@ def test_attention_forward_prefill_fp32_then_decode(cuda_device):
         reset_context()
     wd = c_oracle.paged_decode(qd, layer.k_cache.cpu(), layer.v_cache.cpu(), tables, ctx, 1.0 / D ** 0.5, H, KVH, D, BS)
     assert (od.cpu().view(2, H, D) - wd).abs().max() <= 1e-4
+
+
+def test_prefill_full_size_properties(cuda_device):
+    """At a size the CPU oracle cannot finish (2 x 8192 tokens, 32Q/8KV/D128 bf16: the bench shape),
+    properties that hold at any size: (1) V = 1 gives 1 (the weights of a row sum to one, up to the
+    16-bit rounding of P); (2) causality — changing the second half of a sequence leaves the outputs of
+    its first half bit-identical; (3) sequences are independent — the batch equals the sequences run
+    alone; (4) the paged entry point over a randomly permuted cache equals the dense one bit for bit;
+    (5) a strided sample of rows against the float64 oracle evaluated on those rows only."""
+    H, KVH, D, n, BS = 32, 8, 128, 8192, 16
+    dev = cuda_device
+    g = torch.Generator(device=dev).manual_seed(8)
+    q = torch.randn(2 * n, H, D, device=dev, generator=g).to(torch.bfloat16)
+    k = torch.randn(2 * n, KVH, D, device=dev, generator=g).to(torch.bfloat16)
+    v = torch.randn(2 * n, KVH, D, device=dev, generator=g).to(torch.bfloat16)
+    cu = torch.tensor([0, n, 2 * n], dtype=torch.int32, device=dev)
+    scale = 1.0 / D ** 0.5
+    base = flash_attention_prefill(q, k, v, cu, scale, H, KVH, D, max_seqlen=n)
+    assert torch.isfinite(base.float()).all()
+    # (1)
+    ones = flash_attention_prefill(q, k, torch.ones_like(v), cu, scale, H, KVH, D, max_seqlen=n)
+    assert (ones.float() - 1).abs().max().item() <= 4e-3
+    # (2)
+    k2, v2 = k.clone(), v.clone()
+    k2[n // 2:n].normal_(generator=g)
+    v2[n // 2:n].normal_(generator=g)
+    pert = flash_attention_prefill(q, k2, v2, cu, scale, H, KVH, D, max_seqlen=n)
+    assert torch.equal(pert[:n // 2], base[:n // 2]) and torch.equal(pert[n:], base[n:])
+    assert not torch.equal(pert[n // 2:n], base[n // 2:n])
+    # (3)
+    alone = flash_attention_prefill(q[n:], k[n:], v[n:], cu[:2], scale, H, KVH, D, max_seqlen=n)
+    assert torch.equal(alone, base[n:])
+    # (4)
+    nb = 2 * n // BS
+    perm = torch.randperm(nb, device=dev, generator=g)
+    kc = torch.empty(nb, BS, KVH, D, dtype=torch.bfloat16, device=dev)
+    vc = torch.empty_like(kc)
+    kc[perm] = k.view(nb, BS, KVH, D)
+    vc[perm] = v.view(nb, BS, KVH, D)
+    bt = perm.to(torch.int32).view(2, n // BS)
+    ctx = torch.tensor([n, n], dtype=torch.int32, device=dev)
+    paged = flash_attention_prefill_paged(q, kc, vc, cu, bt, ctx, scale, H, KVH, D, BS, max_seqlen_q=n)
+    assert torch.equal(paged, base)
+    # (5) rows 0, 127, 128, 4095, 8191 of sequence 1, heads 0 and 31
+    for row in (0, 127, 128, 4095, n - 1):
+        for h in (0, H - 1):
+            kk = k[n:n + row + 1, h // (H // KVH)].double().cpu()
+            vv = v[n:n + row + 1, h // (H // KVH)].double().cpu()
+            s = (kk @ q[n + row, h].double().cpu()) * scale
+            want = torch.softmax(s, 0) @ vv
+            err = (base[n + row, h].double().cpu() - want).abs() - (4e-3 + 2.0 ** -7 * want.abs())
+            assert err.max() <= 0
