@@ -118,10 +118,10 @@ __device__ __forceinline__ void mbar_wait_bounded(uint32_t bar, uint32_t parity)
       ".reg .u32 spins;\n"
       "mov.u32 spins, 0;\n"
       "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\n"
-      "add.u32 spins, spins, 1;\n"
-      "setp.gt.u32 p, spins, 0x10000000;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, 0x989680;\n"   // suspend-time hint: the
+      "@p bra DONE_%=;\n"                                                   // thread sleeps in hardware
+      "add.u32 spins, spins, 1;\n"                                         // instead of polling
+      "setp.gt.u32 p, spins, 0x100000;\n"
       "@p trap;\n"
       "bra WAIT_%=;\n"
       "DONE_%=:\n"
