@@ -225,6 +225,7 @@ flash_prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap mq, const __gri
   const int ntiles = key_tiles(qa0, g.ctx);   // the last one or two hold the causal diagonal
   const int* table = PAGED ? p.block_tables + (long long)seq * p.bt_stride : nullptr;
 
+  if (tid == 64) tc5::prefetch_tensormap(&mq), tc5::prefetch_tensormap(&mk), tc5::prefetch_tensormap(&mv);
   if (warp == 0) {
     tc5::tmem_alloc(tmem_slot, C::TMEM_COLS);
     tc5::tmem_relinquish();
@@ -363,6 +364,7 @@ flash_prefill_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap mq, const 
   const int n1 = m0 + 128 < g.n_new ? key_tiles(qa0 + 128, g.ctx) : 0;  // query tile 1, if the sequence reaches it
   const int n = n1 ? n1 : n0;                                           // n1 >= n0 when tile 1 is live
 
+  if (tid == 288) tc5::prefetch_tensormap(&mq), tc5::prefetch_tensormap(&mk), tc5::prefetch_tensormap(&mv);
   if (warp == 8) {
     tc5::tmem_alloc(tmem_slot, C::TMEM_COLS);
     tc5::tmem_relinquish();
