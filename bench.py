@@ -47,7 +47,7 @@ def parse_args():
                     help="c1..c5: one attention call per step; c2e: 28-layer engine-shaped decode "
                          "loop of config 2 under CUDA-graph replay")
     ap.add_argument("--eager", action="store_true", help="c2e: no CUDA graphs")
-    ap.add_argument("--share-prefix", choices=["auto", "on", "off"], default="auto",
+    ap.add_argument("--share-prefix", choices=["auto", "on", "off", "narrow"], default="auto",
                     help="score sequences with aliased block-table prefixes together "
                          "(MVL_DECODE_SHARE_PREFIX); auto = on for the shared-prefix workload c5")
     ap.add_argument("--cuda-cores", action="store_true",
@@ -345,9 +345,10 @@ def run_ours(args, rank, world, local_rank):
     dec_args = (w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"], w["H"],
                 w["KVH"], w["D"], w["BS"])
     lib = _ext.lib()
-    share = args.share_prefix == "on" or (args.share_prefix == "auto" and args.workload == "c5")
+    share = args.share_prefix in ("on", "narrow") or (args.share_prefix == "auto" and args.workload == "c5")
     tma = ((_ext.DECODE_LOAD_TMA if args.tma else 0) | (_ext.DECODE_CUDA_CORES if args.cuda_cores else 0) |
-           (_ext.DECODE_SHARE_PREFIX if share else 0))
+           (_ext.DECODE_SHARE_PREFIX if share else 0) |
+           (_ext.DECODE_SHARE_NARROW if args.share_prefix == "narrow" else 0))
     if tma:
         from minivllm_b200.layers import attention as att_mod
         att_mod.DEFAULT_DECODE_FLAGS |= tma

@@ -75,7 +75,12 @@ typedef enum mvl_dtype {
                                        against ONE copy of the shared K/V pages: with G <= 4 query
                                        heads per KV head the tensor-core tile's 8 columns hold 8/G
                                        sequences.  Same results bit for bit.  Needs the tensor-core
-                                       kernel, G <= 4 and a workspace; ignored otherwise. */
+                                       kernel, G <= 4 and a workspace; ignored otherwise.
+                                       Sub-groups hold up to 4 x 8/G sequences: chunks shared by more
+                                       than 8/G of them go to a second kernel whose four warps hold
+                                       different sequences and read each K/V tile once for all. */
+#define MVL_DECODE_SHARE_NARROW 64u /* with SHARE_PREFIX: sub-groups of 8/G sequences only, no second
+                                       kernel (measurement switch) */
 
 /* Library / ABI identification.  No reference counterpart (the reference has no native layer). */
 int mvl_abi_version(void);

@@ -381,6 +381,8 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
   p.max_splits = pl.max_splits;
   p.qscale = scale * 1.4426950408889634f;
   p.gp_shift = 3;  // 8 columns = 8 heads of one sequence unless prefix sharing packs several
+  p.mm_narrow = 1;
+  p.wide = 0;
 
   cudaStream_t s = (cudaStream_t)stream;
   // Prefix sharing: tensor-core kernel, fewer than 8 heads per KV head (spare columns), more than
@@ -390,9 +392,14 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
     int gp = 1;
     while (gp < p.G) gp <<= 1;
     p.gp_shift = gp == 1 ? 0 : (gp == 2 ? 1 : 2);
+    p.mm_narrow = 8 / gp;
+    // wide form: sub-groups of up to 4 x (8 / gp) sequences, one CTA per shared chunk reads its tiles
+    // once for all of them (paged_decode_group.cuh); needs whole 16-token tiles inside a page
+    p.wide = (!(flags & MVL_DECODE_SHARE_NARROW) && block_size % 16 == 0 && pl.chunk % 64 == 0) ? 1 : 0;
     int* meta = reinterpret_cast<int*>(reinterpret_cast<char*>(workspace) + kCounterBytes);
     const int e = mvl::launch_prefix_share(block_tables, block_table_stride, context_lens, p.ctx_is_i64,
-                                           batch, pl.max_ctx, pl.bs_shift, pl.chunk, 8 / gp, meta, s);
+                                           batch, pl.max_ctx, pl.bs_shift, pl.chunk,
+                                           p.wide ? 4 * p.mm_narrow : p.mm_narrow, meta, s);
     if (e != 0) return cuda_fail((cudaError_t)e, "prefix_share launch");
     p.share_meta = meta;
   }
@@ -421,6 +428,12 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
     }
     if (e == -1000) return MVL_ERR_SHAPE;
     if (e != 0) return cuda_fail((cudaError_t)e, "paged_decode_split launch");
+    if (mma && p.share_meta != nullptr && p.wide) {
+      e = elem_dtype == MVL_DTYPE_F16 ? mvl::launch_decode_group_mma<__half>(p, head_dim, grid, s)
+                                      : mvl::launch_decode_group_mma<__nv_bfloat16>(p, head_dim, grid, s);
+      if (e == -1000) return MVL_ERR_SHAPE;
+      if (e != 0) return cuda_fail((cudaError_t)e, "paged_decode_group launch");
+    }
   }
   if (pl.max_splits > 1 && !(flags & MVL_DECODE_SKIP_COMBINE) && p.counters == nullptr) {
     const long long bh = (long long)batch * num_heads;

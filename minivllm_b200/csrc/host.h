@@ -25,6 +25,9 @@ int launch_decode_split(const DecodeParams& p, const CUtensorMap* maps, int head
 // Tensor-core variant (16-bit element types only): 8 heads per CTA, 16-token warp tiles.
 template <typename T>
 int launch_decode_split_mma(const DecodeParams& p, int head_dim, dim3 grid, cudaStream_t s);
+// Prefix sharing, wide form (paged_decode_group.cuh): same grid as the split kernel, after it.
+template <typename T>
+int launch_decode_group_mma(const DecodeParams& p, int head_dim, dim3 grid, cudaStream_t s);
 template <typename T>
 int launch_decode_combine(const DecodeParams& p, int head_dim, long long rows, cudaStream_t s);
 // Rows of one warp tile for (T, head_dim, gt): the chunk must be a multiple of 4 warps x this.

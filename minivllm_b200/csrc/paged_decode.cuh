@@ -54,6 +54,9 @@ struct DecodeParams {
   // columns hold 8/Gp sequences x Gp heads).  meta = leader[B], gsize[B], gshare[B], lcpt[B].
   const int* share_meta;    // nullptr = every sequence on its own
   int gp_shift;             // log2(Gp), Gp = heads per sequence in the 8 columns (8 when not sharing)
+  int mm_narrow;            // sequences the split kernel packs into its 8 columns = 8 / Gp
+  int wide;                 // 1: sub-groups hold up to 4 * mm_narrow sequences and the chunks shared by
+                            // more than mm_narrow of them are left to paged_decode_group_mma_kernel
   const void* q;
   const void* kc;
   const void* vc;

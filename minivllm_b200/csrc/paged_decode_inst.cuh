@@ -3,6 +3,7 @@
 
 #include "host.h"
 #include "paged_decode_mma.cuh"
+#include "paged_decode_group.cuh"
 
 namespace mvl {
 
@@ -94,6 +95,46 @@ int launch_decode_split_mma<MVL_T>(const DecodeParams& p, int head_dim, dim3 gri
       return uniform ? launch_mma_u<MVL_T, 128, true>(p, grid, s) : launch_mma_u<MVL_T, 128, false>(p, grid, s);
   }
   return -1000;
+}
+#endif
+
+#ifdef MVL_T_IS_16BIT
+template <>
+int launch_decode_group_mma<MVL_T>(const DecodeParams& p, int head_dim, dim3 grid, cudaStream_t s) {
+  static bool configured[64][2] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev >= 64) return (int)cudaErrorInvalidDevice;
+  const int di = head_dim == 64 ? 0 : 1;
+  if (head_dim != 64 && head_dim != 128) return -1000;
+  if (!configured[dev][di]) {
+    e = di == 0 ? cudaFuncSetAttribute(paged_decode_group_mma_kernel<MVL_T, 64>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, GroupCfg<MVL_T, 64>::SMEM)
+                : cudaFuncSetAttribute(paged_decode_group_mma_kernel<MVL_T, 128>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, GroupCfg<MVL_T, 128>::SMEM);
+    if (e != cudaSuccess) return (int)e;
+    configured[dev][di] = true;
+  }
+  // programmatic dependent launch: may start while the split kernel (launched just before on this
+  // stream) is still running
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(128);
+  cfg.stream = s;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (di == 0) {
+    cfg.dynamicSmemBytes = GroupCfg<MVL_T, 64>::SMEM;
+    e = cudaLaunchKernelEx(&cfg, paged_decode_group_mma_kernel<MVL_T, 64>, p);
+  } else {
+    cfg.dynamicSmemBytes = GroupCfg<MVL_T, 128>::SMEM;
+    e = cudaLaunchKernelEx(&cfg, paged_decode_group_mma_kernel<MVL_T, 128>, p);
+  }
+  return (int)e;
 }
 #endif
 

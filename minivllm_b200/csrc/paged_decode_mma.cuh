@@ -117,6 +117,10 @@ __global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_k
   constexpr int GT = C::GT, NW = C::NW, TR = C::TR, ROWB = C::ROWB, CPRW = C::CPRW, RPP = C::RPP,
                 R = C::R, TILEB = C::TILEB, KS = C::KS, RING = C::RING;
   extern __shared__ __align__(1024) unsigned char smem[];
+  // With prefix sharing in its wide form a second kernel (paged_decode_group.cuh) takes the chunks
+  // shared by large sub-groups; it depends on nothing this kernel writes, so it may start at once
+  // (programmatic dependent launch; a no-op when no dependent launch is configured).
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t = lane & 3;  // fragment coordinates: group (row) and thread-in-group
@@ -165,7 +169,7 @@ __global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_k
     const int lead = p.share_meta[b];
     const int sz = p.share_meta[nb + lead];
     if (sz > 1 && start + p.chunk <= p.share_meta[2 * nb + lead]) {
-      if (b != lead) return;
+      if (b != lead || sz > p.mm_narrow) return;  // larger sub-groups: the group kernel's chunk
       nmem = sz;
     }
   }

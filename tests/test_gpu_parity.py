@@ -512,18 +512,25 @@ def test_prefix_sharing_is_bit_identical(cuda_device, H, KVH, D, chunk):
     whole context is the shared part plus one token, identical twins, and G = 8 (flag ignored)."""
     from minivllm_b200 import _ext
     groups = [(256, [300, 257, 700, 290, 512]), (0, [130]), (128, [129, 129]), (384, [385, 1000, 400]),
-              (64, [200]), (512, [600, 520])]
+              (64, [200]), (512, [600, 520]), (320, [330, 321, 400, 900, 350, 322, 640, 333, 500, 321])]
     inp = _aliased_case(900 + H + D, torch.bfloat16, H, KVH, D, 16, groups)
     dev = _dev(inp, cuda_device)
     base = _run(dev, chunk_tokens=chunk, flags=_ext.DECODE_FUSED_COMBINE)
-    for flags in (_ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX, _ext.DECODE_SHARE_PREFIX):
+    want = _oracle(inp).numpy()
+    narrow = _ext.DECODE_SHARE_PREFIX | _ext.DECODE_SHARE_NARROW
+    for flags in (_ext.DECODE_FUSED_COMBINE | narrow, narrow,
+                  _ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX, _ext.DECODE_SHARE_PREFIX):
         for _ in range(2):  # twice: the arrival counters must come back to zero
             got = _run(dev, chunk_tokens=chunk, flags=flags)
-            if flags & _ext.DECODE_FUSED_COMBINE:
+            if flags == _ext.DECODE_FUSED_COMBINE | narrow:
+                # sub-groups of 8/G sequences: the same warps add the same tiles in the same order
                 assert torch.equal(got, base)
-            else:  # separate combine kernel merges in another order
+            else:
+                # separate combine kernel, or the group kernel (one warp walks a shared chunk's tiles
+                # that four warps split otherwise): another summation order, same tolerance
                 assert (got.float() - base.float()).abs().max() <= 2e-2
-    _assert_close(base.float().cpu().numpy(), _oracle(inp).numpy(), torch.bfloat16)
+                _assert_close(got.float().cpu().numpy(), want, torch.bfloat16)
+    _assert_close(base.float().cpu().numpy(), want, torch.bfloat16)
 
 
 def test_prefix_sharing_golden_and_fused_step(cuda_device):
@@ -545,9 +552,14 @@ def test_prefix_sharing_golden_and_fused_step(cuda_device):
     slots = inp["block_tables"][torch.arange(B), last // BS].long() * BS + last % BS
     dev = _dev(inp, cuda_device)
     outs = []
-    for fl in (_ext.DECODE_FUSED_COMBINE, flags):
+    for fl in (_ext.DECODE_FUSED_COMBINE, flags | _ext.DECODE_SHARE_NARROW):
         kc, vc = dev["k_cache"].clone(), dev["v_cache"].clone()
         outs.append(decode_step(dev["q"], k.to(cuda_device), v.to(cuda_device), kc, vc, slots.to(cuda_device),
                                 dev["block_tables"], dev["context_lens"], inp["scale"], inp["H"], KVH, D, BS,
                                 chunk_tokens=64, flags=fl))
     assert torch.equal(outs[0], outs[1])
+    kc, vc = dev["k_cache"].clone(), dev["v_cache"].clone()
+    wide = decode_step(dev["q"], k.to(cuda_device), v.to(cuda_device), kc, vc, slots.to(cuda_device),
+                       dev["block_tables"], dev["context_lens"], inp["scale"], inp["H"], KVH, D, BS,
+                       chunk_tokens=64, flags=flags)     # 4 sequences > 8/G = 2: the group kernel's case
+    assert (wide.float() - outs[0].float()).abs().max() <= 2e-2
