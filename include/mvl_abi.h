@@ -74,11 +74,12 @@ typedef enum mvl_dtype {
                                        by a device pre-pass (two small launches) and scored together
                                        against ONE copy of the shared K/V pages: with G <= 4 query
                                        heads per KV head the tensor-core tile's 8 columns hold 8/G
-                                       sequences.  Same results bit for bit.  Needs the tensor-core
+                                       sequences (bit-identical results in that form).  Needs the tensor-core
                                        kernel, G <= 4 and a workspace; ignored otherwise.
                                        Sub-groups hold up to 4 x 8/G sequences: chunks shared by more
                                        than 8/G of them go to a second kernel whose four warps hold
-                                       different sequences and read each K/V tile once for all. */
+                                       different sequences and read each K/V tile once for all;
+                                       there results agree with the unshared run to rounding. */
 #define MVL_DECODE_SHARE_NARROW 64u /* with SHARE_PREFIX: sub-groups of 8/G sequences only, no second
                                        kernel (measurement switch) */
 
