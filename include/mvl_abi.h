@@ -10,7 +10,9 @@
  * Conventions
  *   - Every function returns MVL_OK (0) or a negative mvl_status; nothing throws or aborts.
  *   - The library never allocates, frees or retains device memory.  Scratch memory ("workspace")
- *     is owned by the caller and sized with mvl_paged_decode_workspace_bytes().
+ *     is owned by the caller and sized with mvl_paged_decode_workspace_bytes().  The one exception
+ *     is mvl_paged_decode_static (end of this file), whose scratch is a fixed array in the
+ *     library's own device image.
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  All work is
  *     enqueued on it; no call synchronises the device or reads device memory on the host, and the
  *     grid depends only on host-known sizes, so calls may be captured in a CUDA graph
@@ -321,7 +323,9 @@ int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_h
  *     mvl_static_last_error() then says how many bytes were needed.  A larger chunk_tokens
  *     (fewer chunks per sequence) or a smaller batch shrinks the need.
  *   - First call on each device looks up the array's device address (cudaGetSymbolAddress, with
- *     that device current).  Make that first call outside any stream capture.
+ *     that device current).  Make that first call outside any stream capture.  The address is
+ *     kept until the process exits; after a cudaDeviceReset() on that device it is stale, so do
+ *     not call this function on a device you have reset.
  *   - All calls on a device share the one array and it keeps whatever the previous call left;
  *     nothing in it needs to start at zero, so nothing is cleared.  Two calls that may run at the
  *     same time on one GPU (different streams, or different host threads) race on it: keep calls
@@ -339,7 +343,9 @@ int mvl_paged_decode_static(void* out, const void* query, const void* k_cache, c
 /* MVL_STATIC_SCRATCH_BYTES as seen by the built library. */
 size_t mvl_static_scratch_bytes(void);
 
-/* Text explaining the last failure of mvl_paged_decode_static on the calling thread ("" if none). */
+/* Text explaining the last failure of mvl_paged_decode_static on the calling thread ("" if none):
+ * the size that did not fit, the failed address look-up, or the status text (and CUDA error string)
+ * of the shared decode path when that refused the arguments or the launch. */
 const char* mvl_static_last_error(void);
 
 #ifdef __cplusplus

@@ -14,7 +14,9 @@
 //
 // The array below is a __device__ symbol.  In host code its name does not denote a device address;
 // the address is looked up with cudaGetSymbolAddress, once per device, while that device is
-// current, and the looked-up pointer is what reaches the kernels.
+// current, and the looked-up pointer is what reaches the kernels.  The looked-up address is kept
+// for the life of the process: a cudaDeviceReset() unloads the device image and makes it stale,
+// so a process that resets a device must not call this entry point on that device afterwards.
 #include <stdio.h>
 
 #include <mutex>
@@ -89,10 +91,18 @@ int mvl_paged_decode_static(void* out, const void* query, const void* k_cache, c
   // Nothing in the scratch has to start at zero: the combine kernel reads exactly the partials the
   // split kernel of THIS call wrote (the chunks each sequence really has), so leftovers of an
   // earlier call are never read and no clearing pass is launched.
-  return mvl_paged_decode(out, query, k_cache, v_cache, block_tables, context_lens, ctx_is_i64,
-                          batch, max_num_blocks, block_table_stride, num_heads, num_kv_heads,
-                          head_dim, block_size, num_blocks, scale, elem_dtype, scratch,
-                          (size_t)MVL_STATIC_SCRATCH_BYTES, chunk_tokens, 0u, stream);
+  const int rc = mvl_paged_decode(out, query, k_cache, v_cache, block_tables, context_lens,
+                                  ctx_is_i64, batch, max_num_blocks, block_table_stride, num_heads,
+                                  num_kv_heads, head_dim, block_size, num_blocks, scale, elem_dtype,
+                                  scratch, (size_t)MVL_STATIC_SCRATCH_BYTES, chunk_tokens, 0u,
+                                  stream);
+  if (rc != MVL_OK) {  // argument check or launch failure of the shared decode path
+    const char* cuda = mvl_last_cuda_error();
+    snprintf(g_static_err, sizeof(g_static_err), "%s%s%s", mvl_strerror(rc),
+             (rc == MVL_ERR_CUDA && cuda && cuda[0]) ? ": " : "",
+             (rc == MVL_ERR_CUDA && cuda) ? cuda : "");
+  }
+  return rc;
 }
 
 }  // extern "C"

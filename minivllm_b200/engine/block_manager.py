@@ -16,17 +16,17 @@ can_append / append``).  Repairs, each where the reference cannot run as written
   least one query (a fully cached prompt leaves the reference with an empty prefill batch);
 * a page that is recycled for other content drops its stale hash entry; free pages are popped from a
   deque in O(1) (the reference calls ``deque.remove``, O(free pages), per block);
-* the 64-bit key is BLAKE2b-64 of (previous key, int32 token ids): xxhash (the reference's choice) is
-  not installed in this image, and any collision is caught by the token comparison the reference also
-  does (:76).
+* the 64-bit key is the reference's own (:38-43): xxh64 over (previous key as 8 little-endian bytes,
+  int32 token ids), so keys computed here and by the reference agree; any collision is caught by the
+  token comparison the reference also does (:76).
 """
 from __future__ import annotations
 
-import hashlib
 from collections import deque
 from typing import Dict, List, Optional, Sequence
 
 import numpy as np
+import xxhash
 
 
 class PrefixSeq:
@@ -73,11 +73,11 @@ class PrefixBlockManager:
     # ------------------------------------------------------------------ hashing
     @staticmethod
     def compute_hash(token_ids: Sequence[int], prefix_hash: Optional[int]) -> int:
-        h = hashlib.blake2b(digest_size=8)
+        h = xxhash.xxh64()
         if prefix_hash is not None:
             h.update(prefix_hash.to_bytes(8, "little"))
         h.update(np.asarray(token_ids, dtype=np.int32).tobytes())
-        return int.from_bytes(h.digest(), "little")
+        return h.intdigest()
 
     # ------------------------------------------------------------------ pages
     def _take(self, block_id: Optional[int] = None) -> int:

@@ -22,10 +22,18 @@ from .attention import (Attention, _dtype_code, _index_flag, _need_cuda, _on_dev
 
 
 def rope_cache(base: float, rotary_dim: int, max_position: int, device=None) -> torch.Tensor:
-    """(max_position, rotary_dim) fp32 table, row p = [cos(p * inv_freq) | sin(p * inv_freq)]."""
-    inv_freq = 1.0 / (base ** (torch.arange(0, rotary_dim, 2, dtype=torch.float32) / rotary_dim))
-    freqs = torch.outer(torch.arange(max_position, dtype=torch.float32), inv_freq)
-    return torch.cat([freqs.cos(), freqs.sin()], dim=-1).to(device)
+    """(max_position, rotary_dim) fp32 table, row p = [cos(p * inv_freq) | sin(p * inv_freq)].
+
+    Same quantities as the reference's ``cos_sin_cache`` (rotary_embedding.py:61-71): fp32
+    ``inv_freq``, fp32 angles ``p * inv_freq`` (one IEEE product each, the same on every host).  The
+    reference then takes cos / sin with the host's fp32 vector math, whose last bits differ from CPU
+    to CPU; here they are evaluated in float64 on those fp32 angles and rounded once, so the table is
+    the correctly rounded value of the reference's expression and does not depend on the host.
+    """
+    exponent = torch.arange(0, rotary_dim, 2, dtype=torch.float64) / rotary_dim
+    inv_freq = (1.0 / (torch.tensor(float(base), dtype=torch.float64) ** exponent)).float()
+    freqs = (torch.arange(max_position, dtype=torch.float32)[:, None] * inv_freq[None, :]).double()
+    return torch.cat([freqs.cos(), freqs.sin()], dim=-1).float().to(device)
 
 
 def fused_qk_norm_rope_store(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, positions: torch.Tensor,

@@ -23,6 +23,13 @@ GOLD = os.path.join(os.path.dirname(__file__), "golden")
 ROUND = {torch.float32: (2e-5, 2e-6), torch.bfloat16: (1e-3, 2.0 ** -8), torch.float16: (2e-4, 2.0 ** -11)}
 
 
+def _rope_table_f64(base, d, max_position):
+    """rotary_embedding.py:61-71 evaluated entirely in float64 (no fp32 rounding of the angles)."""
+    inv_freq = 1.0 / (float(base) ** (torch.arange(0, d, 2, dtype=torch.float64) / d))
+    freqs = torch.arange(max_position, dtype=torch.float64)[:, None] * inv_freq[None, :]
+    return torch.cat([freqs.cos(), freqs.sin()], dim=-1)
+
+
 def _close(got, want, dtype):
     got, want = got.double().cpu().numpy(), want.double().cpu().numpy()
     a, r = ROUND[dtype]
@@ -43,7 +50,13 @@ def test_pre_attention_matches_reference_and_oracle(cuda_device, name):
     kc0 = torch.randn(NB, BS, KVH, D, generator=g).to(dt)
     vc0 = torch.randn(NB, BS, KVH, D, generator=g).to(dt)
     table = pre.rope_table(c["base"], D, c["max_position"])
-    assert torch.equal(rope_cache(c["base"], D, c["max_position"]), table)
+    # the product's own table: same expression, cos/sin correctly rounded (host-independent).  The
+    # reference's fp32 host cos/sin (and powf) may be off by an fp32 ulp of the angle: <= ulp(max_position)
+    own = rope_cache(c["base"], D, c["max_position"])
+    assert own.dtype == torch.float32 and own.shape == table.shape
+    assert (own - table).abs().max().item() <= 2.0 ** -23 * c["max_position"]
+    exact = _rope_table_f64(c["base"], D, c["max_position"])
+    assert (own.double() - exact).abs().max().item() <= 2.0 ** -23 * c["max_position"]
     gamma = inp["gamma"] if c["norm"] else None
     want_kc, want_vc = kc0.clone(), vc0.clone()
     q_want, k_want = pre.pre_attention(inp["q"], inp["k"], inp["v"], inp["positions"], gamma, c["eps"],

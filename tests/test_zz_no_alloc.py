@@ -8,12 +8,15 @@ inside the library instead.
 What is checked, through the C ABI (ctypes, raw pointers):
   * two calls in a row (different shapes and dtypes, so the second one finds the first one's
     leftovers in the shared array) each match the ordinary entry point, mvl_paged_decode with a
-    caller-owned workspace, within the tolerance the parity tests use;
+    caller-owned workspace, within the tolerance the parity tests use, and the reference's own
+    golden outputs for the same two cases;
   * between the two calls neither the device's free memory nor torch's allocator moves;
   * a problem whose partials exceed the array is refused with MVL_ERR_LIMIT and a message that
     states both sizes, and nothing is written.
 The file is self-contained so it passes alone in a fresh process as well as after the others.
 """
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -23,6 +26,7 @@ from minivllm_b200 import _ext
 from minivllm_b200.layers.attention import paged_attention_decode
 
 pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
 
 # same bound as tests/test_gpu_parity.py: |err| <= A + R * |want|
 TOL = {torch.float32: (1e-4, 0.0), torch.bfloat16: (1e-3, 2.0 ** -8), torch.float16: (2e-4, 2.0 ** -11)}
@@ -89,6 +93,12 @@ def test_static_entry_matches_workspace_entry_twice_in_a_row(cuda_device):
 
     assert _close(out_first, want_first, torch.float32)
     assert _close(out_second, want_second, torch.bfloat16)
+    # and against the reference's own outputs for these two cases (tests/golden/make_golden.py):
+    # 1e-4 abs with both sides fp32, 2e-2 abs against the reference run in bf16
+    ref_first = np.load(os.path.join(GOLD, "long_split.npz"))["ref_out"]
+    ref_second = np.load(os.path.join(GOLD, "ragged_bf16.npz"))["ref_out"]
+    assert np.abs(out_first.float().cpu().numpy() - ref_first).max() <= 1e-4
+    assert np.abs(out_second.float().cpu().numpy() - ref_second).max() <= 2e-2
     # and once more with the first problem, now over call 2's leftovers
     out_again = torch.full_like(first["q"], float("nan"))
     assert _static_call(first, out_again) == 0
