@@ -66,9 +66,29 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-neighbours", action="store_true",
                     help="skip the prefill / pre-attention kernels measured after the headline (N=1, c3 only)")
+    ap.add_argument("--kernel", default="auto", choices=["auto", "grid", "stream"],
+                    help="tensor-core decode kernel: one CTA per chunk (grid), the persistent evenly cut "
+                         "stream (stream), or the library's own choice (auto)")
+    ap.add_argument("--sustain-s", type=float, default=2.0,
+                    help="seconds of back-to-back steps for the 'sustained' sub-record (0 = skip)")
+    ap.add_argument("--parity-seqs", type=int, default=4, help="sequences checked against the oracle after timing")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="N>1: how the per-rank heads are gathered (fused peer stores, or NCCL)")
     return ap.parse_args()
+
+
+def workload_config(args, t, world):
+    """The `config` object of the JSON line: what was measured, identical for both arms (--impl ours /
+    reference).  How each arm ran it goes under `implementation`."""
+    sp = t.spec
+    unique = workloads.algorithmic_bytes(t, unique=True)
+    return {"workload": args.workload, "shape": f"{sp.H}Q/{sp.KVH}KV/D{sp.D}", "batch": len(t.ctx),
+            "block_size": sp.BS, "context_tokens": int(t.ctx.sum()),
+            "context_range": [int(t.ctx.min()), int(t.ctx.max())],
+            "parallelism": f"kv-head-shard x{world}" if args.shard_of == 1 else
+            f"rank 0's shard of a {args.shard_of}-way head split, alone on one GPU",
+            "l2": "inputs larger than L2 (KV bytes per step >> 126 MB); no flush needed"
+                  if unique / max(world, args.shard_of) > 4 * 126e6 else "KV fits in L2: number is L2-assisted"}
 
 
 def measured_peaks():
@@ -267,10 +287,13 @@ def cpu_step(s):
                                       s["context_lens"], s["scale"], s["H"], s["KVH"], s["D"], s["BS"])
 
 
-def time_cpu(s, steps: int, warmup: int, budget_s: float = 1e9):
+def time_cpu(s, steps: int, warmup: int, budget_s: float = 1e9, warm_budget_s: float = 1e9):
     torch.set_num_threads(os.cpu_count() or 1)
+    t0 = time.perf_counter()
     for _ in range(warmup):
         cpu_step(s)
+        if time.perf_counter() - t0 > warm_budget_s:
+            break
     t0 = time.perf_counter()
     done = 0
     for _ in range(steps):
@@ -286,18 +309,18 @@ def run_reference(args, rank):
         return
     t = workloads.build_tables(args.workload)
     s = cpu_sample(t, args.cpu_seqs)
-    warm = max(args.warmup, 1)
-    per_step, done = time_cpu(s, args.steps, min(warm, 3), budget_s=240.0)
+    warm = max(args.warmup, 0)
+    per_step, done = time_cpu(s, args.steps, warm, budget_s=240.0, warm_budget_s=120.0)
     value = s["n"] / per_step
     sample = (f"{s['n']} of {len(t.ctx)} sequences of workload {args.workload} (evenly strided, "
               f"{s['tokens']} context tokens) per step; {done} steps")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": args.gpus,
-        "steps": done, "warmup": min(warm, 3), "ms_per_step": per_step * 1e3, "higher_is_better": True,
+        "steps": done, "warmup": warm, "ms_per_step": per_step * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": t.spec.dtype, "data": "synthetic",
-        "config": {"workload": args.workload, "shape": f"{t.spec.H}Q/{t.spec.KVH}KV/D{t.spec.D}",
-                   "block_size": t.spec.BS, "batch": len(t.ctx), "path": "oracle port of "
-                   "decode_torch_optimized (vectorised PyTorch, CPU)"},
+        "config": workload_config(args, t, args.gpus),
+        "implementation": {"path": "oracle port of decode_torch_optimized (vectorised PyTorch, CPU), unsharded, "
+                                   "rank 0's host cores"},
         "cpu_baseline": {"value": value, "unit": "tokens/s", "cores": torch.get_num_threads(),
                          "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -348,7 +371,8 @@ def run_ours(args, rank, world, local_rank):
     share = args.share_prefix in ("on", "narrow") or (args.share_prefix == "auto" and args.workload == "c5")
     tma = ((_ext.DECODE_LOAD_TMA if args.tma else 0) | (_ext.DECODE_CUDA_CORES if args.cuda_cores else 0) |
            (_ext.DECODE_SHARE_PREFIX if share else 0) |
-           (_ext.DECODE_SHARE_NARROW if args.share_prefix == "narrow" else 0))
+           (_ext.DECODE_SHARE_NARROW if args.share_prefix == "narrow" else 0) |
+           {"auto": 0, "grid": _ext.DECODE_SPLIT_GRID, "stream": _ext.DECODE_STREAM}[args.kernel])
     if tma:
         from minivllm_b200.layers import attention as att_mod
         att_mod.DEFAULT_DECODE_FLAGS |= tma
@@ -426,6 +450,58 @@ def run_ours(args, rank, world, local_rank):
     ms_step = ms_total / K
     value = B / (ms_step * 1e-3)
 
+    # ---- sustained sub-measurement: back-to-back steps for >= sustain_s seconds, its own clocks
+    sustained = None
+    if args.sustain_s > 0:
+        n_sus = max(int(args.sustain_s * 1e3 / ms_step) + 1, K)
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local_rank) as sclocks:
+            barrier()
+            s0.record()
+            for _ in range(n_sus):
+                step()
+            s1.record()
+            barrier()
+        sus_ms = s0.elapsed_time(s1) / n_sus
+        if world > 1:
+            red = torch.tensor([sus_ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(red, op=dist.ReduceOp.MAX)
+            sus_ms = float(red[0])
+        sustained = {"steps": n_sus, "seconds": sus_ms * n_sus / 1e3, "ms_per_step": sus_ms,
+                     "value": B / (sus_ms * 1e-3), "unit": "tokens/s", "vs_burst": ms_step / sus_ms,
+                     "clocks": sclocks.summary()}
+
+    # ---- output check: the last step's result against the oracle on sampled sequences (every rank
+    # checks the heads it computed; worst error over ranks), and at N > 1 the gathered buffer
+    # against an NCCL all-gather of the local results, bit for bit.
+    parity = None
+    if args.parity_seqs > 0:
+        from oracle import c_oracle  # the checker; nothing timed goes through it
+        res = step()
+        torch.cuda.synchronize()
+        if world > 1:
+            barrier()
+        local = res[:, sh.q_heads] if world > 1 else res
+        pick = sorted(set(np.linspace(0, B - 1, args.parity_seqs).astype(int).tolist() +
+                          workloads.highest_page_sequences(t, 1)))
+        smp = workloads.oracle_sample(t, w, pick)
+        want = c_oracle.paged_decode(smp["q"], smp["k_cache"], smp["v_cache"], smp["block_tables"],
+                                     smp["context_lens"], smp["scale"], smp["H"], smp["KVH"], smp["D"], smp["BS"])
+        err = float((local[pick].float().cpu() - want).abs().max())
+        tol = 1e-4 if sp.dtype == "f32" else 2e-2
+        gather_ok = None
+        if world > 1:
+            mine = local.contiguous()
+            ref_gather = gather_heads(mine)
+            gather_ok = bool(torch.equal(ref_gather, res))
+            red = torch.tensor([err, 0.0 if gather_ok else 1.0], device=dev, dtype=torch.float64)
+            dist.all_reduce(red, op=dist.ReduceOp.MAX)
+            err, gather_ok = float(red[0]), bool(red[1] == 0.0)
+        parity = {"max_abs_err": err, "tol": tol, "ok": bool(err <= tol), "sequences": pick,
+                  "heads": "every rank checks its own heads; max over ranks" if world > 1 else "all",
+                  "checked_against": "oracle/paged_oracle.c (float64 accumulation) on the rows' own pages",
+                  "gather_verified": gather_ok}
+
     # ---- end-to-end through the host-buffer C-ABI entry (pinned H2D + D2H inside the timed region)
     e2e = None
     if not args.no_e2e:
@@ -470,11 +546,16 @@ def run_ours(args, rank, world, local_rank):
             "algorithmic_bytes_per_launch": alg_unique, "logical_bytes_per_launch": alg,
             "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / ms_step,
             "frac_of_nominal_8TBs": achieved / 8000.0}
+    # measured DRAM bytes per launch exist only for the exact (workload, shard, kernel) ncu captured
+    shard_n = world if world > 1 else args.shard_of
+    math_key = "ffma2" if (args.cuda_cores or args.tma or sp.dtype == "f32") else "mma"
+    traffic_key = f"{args.workload}/shard{shard_n}/{math_key}/{args.kernel}" + ("/share" if share else "")
+    roof["traffic_key"] = traffic_key
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof):
         try:
             with open(prof) as f:
-                roof["traffic"] = json.load(f).get(args.workload)
+                roof["traffic"] = json.load(f).get(traffic_key)
         except Exception:
             pass
 
@@ -491,18 +572,13 @@ def run_ours(args, rank, world, local_rank):
         "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": world, "steps": K,
         "warmup": warm, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": sp.dtype, "data": "synthetic",
-        "config": {"workload": args.workload, "shape": f"{sp.H}Q/{sp.KVH}KV/D{sp.D}", "batch": B,
-                   "block_size": sp.BS, "context_tokens": int(t.ctx.sum()),
-                   "context_range": [int(t.ctx.min()), int(t.ctx.max())], "chunk_tokens": int(chunk),
-                   "parallelism": f"kv-head-shard x{world}" if args.shard_of == 1 else
-                   f"rank 0's shard of a {args.shard_of}-way head split, alone on one GPU",
-                   "gather": gather_kind, "prefix_sharing": bool(share), "kv_load": "tensor-map TMA" if args.tma else "cp.async",
-                   "math": "FFMA2 (CUDA cores)" if (args.cuda_cores or args.tma or sp.dtype == "f32")
-                   else "mma.sync m16n8k16 (tensor cores)",
-                   "l2": "inputs larger than L2 (KV bytes per step >> 126 MB); no flush needed"
-                         if alg_unique > 4 * 126e6 else "KV fits in L2: number is L2-assisted"},
+        "config": workload_config(args, t, world),
+        "implementation": {"chunk_tokens": int(chunk), "gather": gather_kind, "prefix_sharing": bool(share),
+                           "kv_load": "tensor-map TMA" if args.tma else "cp.async", "kernel": args.kernel,
+                           "math": "FFMA2 (CUDA cores)" if (args.cuda_cores or args.tma or sp.dtype == "f32")
+                           else "mma.sync m16n8k16 (tensor cores)"},
         "hbm_gbs_step": alg_unique / (ms_step * 1e-3) / 1e9,
-        "roofline": roof, "cpu_baseline": cpu, "e2e": e2e,
+        "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "parity": parity, "sustained": sustained,
         "gpu_launches": K * ((3 if multi_split else 2) if args.unfused else 1),
         "clocks": clocks.summary(),
     }

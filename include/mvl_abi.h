@@ -84,6 +84,16 @@ typedef enum mvl_dtype {
                                        there results agree with the unshared run to rounding. */
 #define MVL_DECODE_SHARE_NARROW 64u /* with SHARE_PREFIX: sub-groups of 8/G sequences only, no second
                                        kernel (measurement switch) */
+#define MVL_DECODE_SPLIT_GRID 128u /* 16-bit caches, chunk_tokens == 0: never use the persistent
+                                       stream kernel (below), always one CTA per chunk */
+#define MVL_DECODE_STREAM 256u     /* 16-bit caches, chunk_tokens == 0: always use the persistent
+                                       stream kernel when its conditions hold.  Without either flag
+                                       the library picks: with chunk_tokens == 0, FUSED_COMBINE set and
+                                       batch <= 1024 it cuts the launch's whole token stream into equal
+                                       pieces, one per resident CTA (4 x SMs), when the chunk grid
+                                       would be too few waves to balance; otherwise one CTA per
+                                       (sequence, kv head, chunk).  Same arithmetic either way; the
+                                       split points differ, so results agree to fp32 rounding. */
 
 /* Library / ABI identification.  No reference counterpart (the reference has no native layer). */
 int mvl_abi_version(void);
@@ -285,6 +295,43 @@ int mvl_decode_step_peers(void* const* out_peers, int num_peers, int total_heads
                           int chunk_tokens, unsigned flags, void* stream);
 
 /*
+ * mvl_decode_step_peers_sync / mvl_peer_wait — the peer-store gather with its own completion
+ * protocol, for use between steps WITHOUT a barrier collective.  No reference counterpart (the
+ * reference gathers nothing: it all-reduces after a row-parallel o_proj, layers/linear.py:216-221).
+ *
+ * mvl_paged_decode_peers / mvl_decode_step_peers leave two things to the caller: telling when every
+ * rank's rows have landed (a barrier after the launch), and making sure no rank starts its next step
+ * while another still reads this step's rows (the next step's stores go into the same buffer).  The
+ * _sync form settles both:
+ *   - each rank owns a CONTROL BLOCK of 64 bytes (16 x uint32, zero before the first step, peer-mapped
+ *     like the result buffers); sync_peers[r] is rank r's block as mapped on this device.  When the
+ *     launch's last rows are stored, this rank's step count goes up by one and is written to slot
+ *     [my_rank] of every rank's block (from the persistent kernel's own epilogue where that kernel
+ *     runs, else by a one-thread launch behind the decode kernels).
+ *   - mvl_peer_wait(own block) enqueues a one-warp kernel that returns once all num_peers slots have
+ *     reached this rank's own step count, i.e. once every rank's rows of this step are in this rank's
+ *     buffer.  Put it on the stream in front of whatever consumes the buffer.  Every rank must make
+ *     the same sequence of calls.  If a rank never arrives within timeout_ms (<= 0: 10 s) the wait
+ *     gives up and writes 1 + (rank) into word [10] of the block instead of hanging the GPU.
+ *   - use TWO result buffers per rank and alternate them step by step (pass the step's set in
+ *     out_peers): a rank that has passed the wait of step s may store step s+1 while a slower rank
+ *     still reads step s, but nobody can reach step s+2 — the next to write step s's buffer — before
+ *     its own wait of step s+1, which every rank signals only behind its step-s consumer.
+ * key / value / slot_mapping all NULL = no fused KV-cache write (mvl_paged_decode_peers); otherwise
+ * as mvl_decode_step_peers.
+ */
+int mvl_decode_step_peers_sync(void* const* out_peers, void* const* sync_peers, int num_peers, int my_rank,
+                               int total_heads, int head_offset, const void* query, const void* key,
+                               const void* value, void* k_cache, void* v_cache, const void* slot_mapping,
+                               const int32_t* block_tables, const void* context_lens, int idx_is_i64,
+                               int64_t batch, int64_t max_num_blocks, int64_t block_table_stride,
+                               int64_t key_token_stride, int64_t value_token_stride, int num_heads,
+                               int num_kv_heads, int head_dim, int block_size, int64_t num_blocks,
+                               float scale, int elem_dtype, void* workspace, size_t workspace_bytes,
+                               int chunk_tokens, unsigned flags, void* stream);
+int mvl_peer_wait(void* sync_local, int num_peers, int64_t timeout_ms, void* stream);
+
+/*
  * mvl_decode_step_host — one decode-attention step of a layer driven from HOST buffers:
  * async H2D of the step's inputs (pinned host memory recommended) into caller-provided device
  * staging buffers, mvl_store_kvcache, mvl_paged_decode, async D2H of the result.  The caller
@@ -304,6 +351,37 @@ int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_h
                          int num_kv_heads, int head_dim, int block_size, int64_t num_blocks,
                          float scale, int elem_dtype, void* workspace, size_t workspace_bytes,
                          int chunk_tokens, unsigned flags, void* stream);
+
+/*
+ * mvl_decode_step_host_overlapped — mvl_decode_step_host with the copies hidden under the kernels.
+ * The batch is cut into `pieces` (1..8) runs of consecutive sequences; each piece's host-to-device
+ * copies, its decode launch and the device-to-host copy of its rows go to one of the library's own
+ * streams, so piece i+1's inputs travel while piece i computes and piece i's rows return while piece
+ * i+1 computes (reference model_runner.py:231-256 + attention.py:493-557 are strictly serial).
+ * Ordering seen by the caller is that of mvl_decode_step_host: everything starts after the work
+ * already on `stream` and `stream` waits for all of it, so one synchronisation of `stream` makes
+ * out_host valid.  Same arguments as mvl_decode_step_host plus `pieces`; one cudaMemcpyAsync per
+ * array and piece (6 in, 1 out).
+ *   - The library creates its streams and events (no device memory) on the first call on each
+ *     device; make that first call outside any stream capture.
+ *   - The workspace is cut into `pieces` equal regions: size it with
+ *     mvl_decode_step_host_workspace_bytes() and zero it before the first call.
+ *   - Calls on one device share those internal streams: issue them from one host thread at a time.
+ * No reference counterpart.
+ */
+size_t mvl_decode_step_host_workspace_bytes(int64_t batch, int num_heads, int num_kv_heads, int head_dim,
+                                            int64_t max_num_blocks, int block_size, int elem_dtype,
+                                            int chunk_tokens, int pieces);
+int mvl_decode_step_host_overlapped(const void* q_host, const void* k_host, const void* v_host,
+                                    const void* slot_mapping_host, const void* context_lens_host,
+                                    const int32_t* block_tables_host, void* out_host, void* q_dev,
+                                    void* k_dev, void* v_dev, void* slot_mapping_dev,
+                                    void* context_lens_dev, int32_t* block_tables_dev, void* out_dev,
+                                    void* k_cache, void* v_cache, int idx_is_i64, int64_t batch,
+                                    int64_t max_num_blocks, int num_heads, int num_kv_heads,
+                                    int head_dim, int block_size, int64_t num_blocks, float scale,
+                                    int elem_dtype, void* workspace, size_t workspace_bytes,
+                                    int chunk_tokens, unsigned flags, int pieces, void* stream);
 
 /*
  * mvl_paged_decode_static — mvl_paged_decode for callers that cannot allocate device memory.

@@ -5,6 +5,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "host.h"
 #include "prefill.h"
 #include "mvl_abi.h"
@@ -147,6 +149,20 @@ size_t plan_workspace(const Plan& pl, long long batch, int H, int D) {
   return kCounterBytes + share_meta_bytes(batch) + rows * D * sizeof(float) + rows * sizeof(float2);
 }
 
+// The persistent stream kernel (paged_decode_stream.cuh): resident CTAs and workspace.  It is a
+// candidate only when the caller left the split size to the library (chunk_tokens == 0).
+constexpr int kStreamCtasPerSm = 4;
+constexpr double kStreamGridWaves = 6.0;  // chunk grids with fewer waves of resident CTAs than this go to the stream kernel
+bool stream_eligible(long long batch, int KVH, int n_gt, long long max_ctx, int dtype, int chunk_req) {
+  if (chunk_req != 0 || elem_size(dtype) != 2 || batch < 1 || batch > mvl::kStreamBatchLimit) return false;
+  const long long units = batch * KVH * n_gt;
+  if (units * (long long)sizeof(int) > (long long)kCounterBytes) return false;
+  return units * ((max_ctx + 63) / 64) < (1ll << 31);  // stream positions fit comfortably
+}
+size_t stream_workspace(long long batch, int D, int num_sms) {
+  return kCounterBytes + share_meta_bytes(batch) + mvl::stream_workspace_partials(kStreamCtasPerSm * num_sms, D);
+}
+
 // ---- tensor maps for the TMA load path: [num_slots][KVH][D] with a [tile_rows][1][D] box
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
@@ -181,6 +197,43 @@ bool make_cache_map(CUtensorMap* map, const void* cache, int dtype, int D, int K
              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
+
+// Streams and events of mvl_decode_step_host_overlapped, created once per device (no device memory).
+constexpr int kMaxPieces = 8;
+struct HostPipe {
+  cudaStream_t st[kMaxPieces];
+  cudaEvent_t start, done[kMaxPieces];
+  bool ready;
+};
+std::mutex g_pipe_mutex;
+HostPipe g_pipes[64] = {};
+
+int pipe_for_current_device(HostPipe** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+  if (dev < 0 || dev >= 64) return MVL_ERR_LIMIT;
+  std::lock_guard<std::mutex> lock(g_pipe_mutex);
+  HostPipe& hp = g_pipes[dev];
+  if (!hp.ready) {
+    for (int i = 0; i < kMaxPieces; ++i) {
+      e = cudaStreamCreateWithFlags(&hp.st[i], cudaStreamNonBlocking);
+      if (e != cudaSuccess) return cuda_fail(e, "cudaStreamCreateWithFlags");
+      e = cudaEventCreateWithFlags(&hp.done[i], cudaEventDisableTiming);
+      if (e != cudaSuccess) return cuda_fail(e, "cudaEventCreateWithFlags");
+    }
+    e = cudaEventCreateWithFlags(&hp.start, cudaEventDisableTiming);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaEventCreateWithFlags");
+    hp.ready = true;
+  }
+  *out = &hp;
+  return MVL_OK;
+}
+
+struct PeerSync {  // completion signal of the peer-store gather (peer_sync.cu)
+  void* const* blocks;  // every rank's control block as mapped on this device
+  int my_rank;
+};
 
 struct StoreArgs {  // the step's new K/V rows for the fused store (mvl_decode_step)
   const void* key;
@@ -292,6 +345,10 @@ size_t mvl_paged_decode_workspace_bytes(int64_t batch, int num_heads, int num_kv
                 chunk_tokens, sms, &pl, true) == MVL_OK) {
     const size_t alt = plan_workspace(pl, batch, num_heads, head_dim);
     if (alt > need) need = alt;
+    if (stream_eligible(batch, num_kv_heads, pl.n_gt, pl.max_ctx, elem_dtype, chunk_tokens)) {
+      const size_t st = stream_workspace(batch, head_dim, sms);
+      if (st > need) need = st;
+    }
   }
   return need;
 }
@@ -303,7 +360,18 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
                      int64_t batch, int64_t max_num_blocks, int64_t block_table_stride,
                      int num_heads, int num_kv_heads, int head_dim, int block_size,
                      int64_t num_blocks, float scale, int elem_dtype, void* workspace,
-                     size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream) {
+                     size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream,
+                     const PeerSync* sync = nullptr);
+
+static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, int h_out, int head_off,
+                       const void* query,
+                       const void* k_cache, const void* v_cache,
+                     const int32_t* block_tables, const void* context_lens, int ctx_is_i64,
+                     int64_t batch, int64_t max_num_blocks, int64_t block_table_stride,
+                     int num_heads, int num_kv_heads, int head_dim, int block_size,
+                     int64_t num_blocks, float scale, int elem_dtype, void* workspace,
+                     size_t workspace_bytes, int chunk_tokens, unsigned flags, void* stream,
+                     const PeerSync* sync) {
   int sms = 0;
   int st = current_sm_count(&sms);
   if (st != MVL_OK) return st;
@@ -313,7 +381,22 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
   st = make_plan(batch, num_heads, num_kv_heads, head_dim, max_num_blocks, block_size, elem_dtype,
                  chunk_tokens, sms, &pl, mma);
   if (st != MVL_OK) return st;
-  if (batch == 0) return MVL_OK;
+  if (sync) {
+    if (!sync->blocks || sync->my_rank < 0 || sync->my_rank >= n_out) return MVL_ERR_SHAPE;
+    for (int r = 0; r < n_out && r < 8; ++r)
+      if (!sync->blocks[r]) return MVL_ERR_NULL_POINTER;
+    if (flags & (MVL_DECODE_SKIP_COMBINE | MVL_DECODE_ONLY_COMBINE)) return MVL_ERR_SHAPE;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  // with a completion signal even an empty step must announce itself
+  auto signal_after = [&]() -> int {
+    if (!sync) return MVL_OK;
+    unsigned* blocks[8] = {};
+    for (int r = 0; r < n_out; ++r) blocks[r] = static_cast<unsigned*>(sync->blocks[r]);
+    const int e = mvl::launch_peer_signal(blocks[sync->my_rank], blocks, n_out, sync->my_rank, s);
+    return e == 0 ? MVL_OK : cuda_fail((cudaError_t)e, "peer_signal launch");
+  };
+  if (batch == 0) return signal_after();
   if (num_blocks <= 0 || block_table_stride < max_num_blocks) return MVL_ERR_SHAPE;
   if (!outs || !query || !k_cache || !v_cache || !block_tables || !context_lens)
     return MVL_ERR_NULL_POINTER;
@@ -330,6 +413,18 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
   const size_t need = plan_workspace(pl, batch, num_heads, head_dim);
   if (need > 0 && (!workspace || workspace_bytes < need)) return MVL_ERR_WORKSPACE;
   if (need > 0 && !aligned16(workspace)) return MVL_ERR_ALIGNMENT;
+  // Persistent stream kernel instead of the chunk grid?  Only where its conditions hold and the
+  // workspace the caller sized with mvl_paged_decode_workspace_bytes() is there.
+  bool use_stream = false;
+  if (mma && (flags & MVL_DECODE_FUSED_COMBINE) &&
+      !(flags & (MVL_DECODE_SPLIT_GRID | MVL_DECODE_SHARE_PREFIX | MVL_DECODE_SKIP_COMBINE |
+                 MVL_DECODE_ONLY_COMBINE)) &&
+      stream_eligible(batch, num_kv_heads, pl.n_gt, pl.max_ctx, elem_dtype, chunk_tokens) && workspace &&
+      aligned16(workspace) && workspace_bytes >= stream_workspace(batch, head_dim, sms)) {
+    // The chunk grid balances itself once it has many waves of CTAs; below that the equal pieces win.
+    const double grid_ctas = (double)batch * num_kv_heads * pl.n_gt * (double)pl.max_splits;
+    use_stream = (flags & MVL_DECODE_STREAM) || grid_ctas < kStreamGridWaves * kStreamCtasPerSm * sms;
+  }
 
   mvl::DecodeParams p;
   memset(&p, 0, sizeof(p));
@@ -343,7 +438,14 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
   p.bt = block_tables;
   p.ctx = context_lens;
   const size_t rows = (size_t)batch * num_heads * pl.max_splits;
-  if (need) {
+  if (use_stream) {
+    char* base = reinterpret_cast<char*>(workspace);
+    const size_t head_bytes = kCounterBytes + share_meta_bytes(batch);
+    const size_t slots = (size_t)kStreamCtasPerSm * sms * 2;
+    p.part_o = reinterpret_cast<float*>(base + head_bytes);
+    p.part_ml = reinterpret_cast<float2*>(base + head_bytes + slots * 8 * head_dim * sizeof(float));
+    p.counters = reinterpret_cast<int*>(base);
+  } else if (need) {
     char* base = reinterpret_cast<char*>(workspace);
     const size_t head_bytes = kCounterBytes + share_meta_bytes(batch);
     p.part_o = reinterpret_cast<float*>(base + head_bytes);
@@ -383,8 +485,6 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
   p.gp_shift = 3;  // 8 columns = 8 heads of one sequence unless prefix sharing packs several
   p.mm_narrow = 1;
   p.wide = 0;
-
-  cudaStream_t s = (cudaStream_t)stream;
   // Prefix sharing: tensor-core kernel, fewer than 8 heads per KV head (spare columns), more than
   // one sequence, and a workspace to hold the grouping.  Two tiny launches find the groups.
   if ((flags & MVL_DECODE_SHARE_PREFIX) && mma && need && batch > 1 && p.G <= 4 &&
@@ -404,6 +504,23 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
     p.share_meta = meta;
   }
 
+  if (use_stream) {
+    // no more CTAs than 64-token rows the launch can possibly hold
+    long long ctas = (long long)kStreamCtasPerSm * sms;
+    const long long max_rows = batch * num_kv_heads * pl.n_gt * ((pl.max_ctx + 63) / 64);
+    if (ctas > max_rows) ctas = max_rows;
+    if (sync) {  // signalled from the kernel's own epilogue
+      for (int r = 0; r < n_out; ++r) p.sync_peers[r] = static_cast<unsigned*>(sync->blocks[r]);
+      p.sync_local = p.sync_peers[sync->my_rank];
+      p.my_rank = sync->my_rank;
+    }
+    const int e = elem_dtype == MVL_DTYPE_F16
+                      ? mvl::launch_decode_stream_mma<__half>(p, head_dim, (int)batch, (int)ctas, s)
+                      : mvl::launch_decode_stream_mma<__nv_bfloat16>(p, head_dim, (int)batch, (int)ctas, s);
+    if (e == -1000) return MVL_ERR_SHAPE;
+    if (e != 0) return cuda_fail((cudaError_t)e, "paged_decode_stream launch");
+    return MVL_OK;
+  }
   if (!(flags & MVL_DECODE_ONLY_COMBINE)) {
     dim3 grid((unsigned)(num_kv_heads * pl.n_gt), (unsigned)batch, (unsigned)pl.max_splits);
     CUtensorMap maps[2];
@@ -446,7 +563,7 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
     if (e == -1000) return MVL_ERR_SHAPE;
     if (e != 0) return cuda_fail((cudaError_t)e, "paged_decode_combine launch");
   }
-  return MVL_OK;
+  return signal_after();  // kernels other than the stream kernel: one-thread signal launch behind them
 }
 
 int mvl_paged_decode(void* out, const void* query, const void* k_cache, const void* v_cache,
@@ -506,6 +623,35 @@ int mvl_decode_step_peers(void* const* out_peers, int num_peers, int total_heads
                      scale, elem_dtype, workspace, workspace_bytes, chunk_tokens, flags, stream);
 }
 
+int mvl_decode_step_peers_sync(void* const* out_peers, void* const* sync_peers, int num_peers, int my_rank,
+                               int total_heads, int head_offset, const void* query, const void* key,
+                               const void* value, void* k_cache, void* v_cache, const void* slot_mapping,
+                               const int32_t* block_tables, const void* context_lens, int idx_is_i64,
+                               int64_t batch, int64_t max_num_blocks, int64_t block_table_stride,
+                               int64_t key_token_stride, int64_t value_token_stride, int num_heads,
+                               int num_kv_heads, int head_dim, int block_size, int64_t num_blocks,
+                               float scale, int elem_dtype, void* workspace, size_t workspace_bytes,
+                               int chunk_tokens, unsigned flags, void* stream) {
+  if (!sync_peers) return MVL_ERR_NULL_POINTER;
+  if (num_peers < 1 || num_peers > 8) return MVL_ERR_LIMIT;
+  PeerSync ps{sync_peers, my_rank};
+  StoreArgs st{key, value, slot_mapping, idx_is_i64, key_token_stride, value_token_stride};
+  const bool with_store = key != nullptr || value != nullptr || slot_mapping != nullptr;
+  return decode_impl(with_store ? &st : nullptr, out_peers, num_peers, total_heads, head_offset, query,
+                     k_cache, v_cache, block_tables, context_lens, idx_is_i64, batch, max_num_blocks,
+                     block_table_stride, num_heads, num_kv_heads, head_dim, block_size, num_blocks, scale,
+                     elem_dtype, workspace, workspace_bytes, chunk_tokens, flags, stream, &ps);
+}
+
+int mvl_peer_wait(void* sync_local, int num_peers, int64_t timeout_ms, void* stream) {
+  if (!sync_local) return MVL_ERR_NULL_POINTER;
+  if (num_peers < 1 || num_peers > 8) return MVL_ERR_LIMIT;
+  if (timeout_ms <= 0) timeout_ms = 10000;
+  const int e = mvl::launch_peer_wait(static_cast<unsigned*>(sync_local), num_peers,
+                                      (unsigned long long)timeout_ms * 1000000ull, (cudaStream_t)stream);
+  return e == 0 ? MVL_OK : cuda_fail((cudaError_t)e, "peer_wait launch");
+}
+
 int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_host,
                          const void* slot_mapping_host, const void* context_lens_host,
                          const int32_t* block_tables_host, void* out_host, void* q_dev,
@@ -561,6 +707,91 @@ int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_h
   if (st != MVL_OK) return st;
   e = cudaMemcpyAsync(out_host, out_dev, qb, cudaMemcpyDeviceToHost, s);
   if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync D2H out");
+  return MVL_OK;
+}
+
+size_t mvl_decode_step_host_workspace_bytes(int64_t batch, int num_heads, int num_kv_heads, int head_dim,
+                                            int64_t max_num_blocks, int block_size, int elem_dtype,
+                                            int chunk_tokens, int pieces) {
+  if (pieces < 1) pieces = 1;
+  if (pieces > kMaxPieces) pieces = kMaxPieces;
+  const int64_t per = (batch + pieces - 1) / pieces;
+  const size_t one = mvl_paged_decode_workspace_bytes(per, num_heads, num_kv_heads, head_dim, max_num_blocks,
+                                                      block_size, elem_dtype, chunk_tokens);
+  return ((one + 255) / 256 * 256) * (size_t)pieces;
+}
+
+int mvl_decode_step_host_overlapped(const void* q_host, const void* k_host, const void* v_host,
+                                    const void* slot_mapping_host, const void* context_lens_host,
+                                    const int32_t* block_tables_host, void* out_host, void* q_dev,
+                                    void* k_dev, void* v_dev, void* slot_mapping_dev,
+                                    void* context_lens_dev, int32_t* block_tables_dev, void* out_dev,
+                                    void* k_cache, void* v_cache, int idx_is_i64, int64_t batch,
+                                    int64_t max_num_blocks, int num_heads, int num_kv_heads,
+                                    int head_dim, int block_size, int64_t num_blocks, float scale,
+                                    int elem_dtype, void* workspace, size_t workspace_bytes,
+                                    int chunk_tokens, unsigned flags, int pieces, void* stream) {
+  const int es = elem_size(elem_dtype);
+  if (es == 0) return MVL_ERR_DTYPE;
+  if (batch < 0 || num_heads <= 0 || num_kv_heads <= 0 || head_dim <= 0 || max_num_blocks <= 0)
+    return MVL_ERR_SHAPE;
+  if (pieces < 1 || pieces > kMaxPieces) return MVL_ERR_LIMIT;
+  if (batch == 0) return MVL_OK;
+  if (!q_host || !k_host || !v_host || !slot_mapping_host || !context_lens_host ||
+      !block_tables_host || !out_host || !q_dev || !k_dev || !v_dev || !slot_mapping_dev ||
+      !context_lens_dev || !block_tables_dev || !out_dev)
+    return MVL_ERR_NULL_POINTER;
+  if (pieces > batch) pieces = (int)batch;
+  const size_t need = mvl_decode_step_host_workspace_bytes(batch, num_heads, num_kv_heads, head_dim,
+                                                           max_num_blocks, block_size, elem_dtype,
+                                                           chunk_tokens, pieces);
+  if (need > 0 && (!workspace || workspace_bytes < need)) return MVL_ERR_WORKSPACE;
+  const size_t region = need / (size_t)pieces;
+  HostPipe* hp = nullptr;
+  int st = pipe_for_current_device(&hp);
+  if (st != MVL_OK) return st;
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaError_t e = cudaEventRecord(hp->start, s);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaEventRecord");
+  const size_t qrow = (size_t)num_heads * head_dim * es, krow = (size_t)num_kv_heads * head_dim * es;
+  const size_t irow = idx_is_i64 ? 8 : 4, trow = (size_t)max_num_blocks * sizeof(int32_t);
+  const int64_t per = (batch + pieces - 1) / pieces;
+  auto at = [](const void* p, size_t off) { return static_cast<const char*>(p) + off; };
+  auto atw = [](void* p, size_t off) { return static_cast<char*>(p) + off; };
+#define MVL_H2D_PIECE(dst, src, row)                                                                \
+  e = cudaMemcpyAsync(atw(dst, b0 * (row)), at(src, b0 * (row)), nb * (row), cudaMemcpyHostToDevice, \
+                      ps);                                                                          \
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync H2D " #dst)
+  for (int i = 0; i < pieces; ++i) {
+    const size_t b0 = (size_t)i * per;
+    if ((int64_t)b0 >= batch) break;
+    const size_t nb = (size_t)((int64_t)(b0 + per) <= batch ? per : batch - (int64_t)b0);
+    cudaStream_t ps = hp->st[i];
+    e = cudaStreamWaitEvent(ps, hp->start, 0);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamWaitEvent");
+    MVL_H2D_PIECE(q_dev, q_host, qrow);
+    MVL_H2D_PIECE(k_dev, k_host, krow);
+    MVL_H2D_PIECE(v_dev, v_host, krow);
+    MVL_H2D_PIECE(slot_mapping_dev, slot_mapping_host, irow);
+    MVL_H2D_PIECE(context_lens_dev, context_lens_host, irow);
+    MVL_H2D_PIECE(block_tables_dev, block_tables_host, trow);
+    st = mvl_decode_step(atw(out_dev, b0 * qrow), at(q_dev, b0 * qrow), at(k_dev, b0 * krow),
+                         at(v_dev, b0 * krow), k_cache, v_cache, at(slot_mapping_dev, b0 * irow),
+                         reinterpret_cast<const int32_t*>(at(block_tables_dev, b0 * trow)),
+                         at(context_lens_dev, b0 * irow), idx_is_i64, (int64_t)nb, max_num_blocks,
+                         max_num_blocks, (int64_t)num_kv_heads * head_dim,
+                         (int64_t)num_kv_heads * head_dim, num_heads, num_kv_heads, head_dim, block_size,
+                         num_blocks, scale, elem_dtype, region ? atw(workspace, (size_t)i * region) : nullptr,
+                         region, chunk_tokens, MVL_DECODE_FUSED_COMBINE | flags, ps);
+    if (st != MVL_OK) return st;
+    e = cudaMemcpyAsync(atw(out_host, b0 * qrow), at(out_dev, b0 * qrow), nb * qrow, cudaMemcpyDeviceToHost, ps);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync D2H out");
+    e = cudaEventRecord(hp->done[i], ps);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaEventRecord");
+    e = cudaStreamWaitEvent(s, hp->done[i], 0);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamWaitEvent");
+  }
+#undef MVL_H2D_PIECE
   return MVL_OK;
 }
 

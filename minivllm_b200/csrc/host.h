@@ -16,6 +16,10 @@ int launch_prefix_share(const int32_t* bt, long long bt_stride, const void* ctx,
                         long long batch, long long max_ctx, int bs_shift, int chunk, int mm, int* meta,
                         cudaStream_t s);
 
+// peer_sync.cu: announce this rank's step to all ranks / wait until all ranks announced mine.
+int launch_peer_signal(unsigned* local, unsigned* const* peers, int n, int my_rank, cudaStream_t s);
+int launch_peer_wait(unsigned* local, int n, unsigned long long timeout_ns, cudaStream_t s);
+
 // Launchers, one translation unit per element type (keeps nvcc parallel and fast).
 // Return cudaSuccess (0) or the cudaError_t of the failed call; -1000 if (D, GT) is not built.
 // maps: {K cache, V cache} tensor maps for the TMA load path, or nullptr for the cp.async path.
@@ -25,6 +29,15 @@ int launch_decode_split(const DecodeParams& p, const CUtensorMap* maps, int head
 // Tensor-core variant (16-bit element types only): 8 heads per CTA, 16-token warp tiles.
 template <typename T>
 int launch_decode_split_mma(const DecodeParams& p, int head_dim, dim3 grid, cudaStream_t s);
+// Persistent, evenly balanced form of the tensor-core kernel (paged_decode_stream.cuh): `ctas`
+// resident CTAs share one stream of 64-token rows; partials at p.part_o / p.part_ml, two per CTA.
+template <typename T>
+int launch_decode_stream_mma(const DecodeParams& p, int head_dim, int batch, int ctas, cudaStream_t s);
+// Largest batch / partial bytes of that kernel (host-side planning).
+constexpr int kStreamBatchLimit = 1024;
+inline size_t stream_workspace_partials(int ctas, int head_dim) {
+  return (size_t)ctas * 2 * (8 * (size_t)head_dim * sizeof(float) + 8 * sizeof(float2));
+}
 // Prefix sharing, wide form (paged_decode_group.cuh): same grid as the split kernel, after it.
 template <typename T>
 int launch_decode_group_mma(const DecodeParams& p, int head_dim, dim3 grid, cudaStream_t s);

@@ -38,6 +38,14 @@ struct DecodeParams {
   // all-gathered by the stores themselves (NVLink P2P) instead of by a separate collective.
   void* outs[8];
   int n_out, H_out, head_off;
+  // Optional completion signal for the peer-store gather (peer_sync.cu): once the launch's last CTA
+  // has stored its rows, this rank's step count is bumped and written to slot [my_rank] of every
+  // rank's control block (system-scope release), where mvl_peer_wait polls it.  Control block =
+  // 16 x u32: [0..7] step counts announced by ranks 0..7, [8] this rank's own count, [9] CTA
+  // arrival counter, [10] wait time-out marker.
+  unsigned* sync_local;     // this rank's control block; nullptr = no signalling
+  unsigned* sync_peers[8];  // every rank's control block as mapped here (entry my_rank = sync_local)
+  int my_rank;
   // Optional fusion of the step's KV-cache write (store_kvcache of the sequence's newest token):
   // the CTA whose chunk holds token ctx-1 writes that row for its kv head before it streams it.
   const void* k_new;        // (batch, KVH, D), token strides in bytes; nullptr = no fused store

@@ -4,6 +4,7 @@
 #include "host.h"
 #include "paged_decode_mma.cuh"
 #include "paged_decode_group.cuh"
+#include "paged_decode_stream.cuh"
 
 namespace mvl {
 
@@ -93,6 +94,39 @@ int launch_decode_split_mma<MVL_T>(const DecodeParams& p, int head_dim, dim3 gri
       return uniform ? launch_mma_u<MVL_T, 64, true>(p, grid, s) : launch_mma_u<MVL_T, 64, false>(p, grid, s);
     case 128:
       return uniform ? launch_mma_u<MVL_T, 128, true>(p, grid, s) : launch_mma_u<MVL_T, 128, false>(p, grid, s);
+  }
+  return -1000;
+}
+#endif
+
+#ifdef MVL_T_IS_16BIT
+template <typename T, int D, bool UNIFORM>
+static int launch_stream_u(const DecodeParams& p, int batch, int ctas, cudaStream_t s) {
+  using S = StreamCfg<T, D>;
+  auto kern = paged_decode_stream_mma_kernel<T, D, UNIFORM>;
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev >= 64 || !configured[dev]) {
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::SMEM);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 64) configured[dev] = true;
+  }
+  kern<<<dim3((unsigned)ctas), 128, S::SMEM, s>>>(p, batch);
+  return (int)cudaGetLastError();
+}
+
+template <>
+int launch_decode_stream_mma<MVL_T>(const DecodeParams& p, int head_dim, int batch, int ctas, cudaStream_t s) {
+  const bool uniform = ((1 << p.bs_shift) % 16) == 0;
+  switch (head_dim) {
+    case 64:
+      return uniform ? launch_stream_u<MVL_T, 64, true>(p, batch, ctas, s)
+                     : launch_stream_u<MVL_T, 64, false>(p, batch, ctas, s);
+    case 128:
+      return uniform ? launch_stream_u<MVL_T, 128, true>(p, batch, ctas, s)
+                     : launch_stream_u<MVL_T, 128, false>(p, batch, ctas, s);
   }
   return -1000;
 }

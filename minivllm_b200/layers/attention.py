@@ -459,7 +459,10 @@ class HostDecodeStep:
 
     def __init__(self, k_cache: torch.Tensor, v_cache: torch.Tensor, batch: int, max_num_blocks: int,
                  num_heads: int, scale: float, index_dtype: torch.dtype = torch.int64,
-                 chunk_tokens: int = 0, flags: int = 0):
+                 chunk_tokens: int = 0, flags: int = 0, pieces: Optional[int] = None):
+        """``pieces``: how many runs of consecutive sequences the step is cut into so that the copies
+        of one run travel while another computes (``mvl_decode_step_host_overlapped``); 1 = the strictly
+        serial ``mvl_decode_step_host``.  Default: 4 for batches of at least 64 sequences, else 1."""
         dev = _need_cuda(k_cache=k_cache, v_cache=v_cache)
         if k_cache.dim() != 4 or k_cache.shape != v_cache.shape or not (
                 k_cache.is_contiguous() and v_cache.is_contiguous()):
@@ -497,10 +500,16 @@ class HostDecodeStep:
         self.q_d, self.k_d, self.v_d, self.slot_d, self.ctx_d, self.bt_d = views(self._d_arena)
         self.out_h = torch.empty((batch, num_heads, self.head_dim), dtype=dt, pin_memory=True)
         self.out_d = torch.empty((batch, num_heads, self.head_dim), dtype=dt, device=dev)
+        self.pieces = (4 if batch >= 64 else 1) if pieces is None else max(1, min(int(pieces), 8, batch))
         with torch.cuda.device(dev):
-            nbytes = _ext.lib().mvl_paged_decode_workspace_bytes(
-                batch, num_heads, self.num_kv_heads, self.head_dim, max_num_blocks, self.block_size,
-                self.code, chunk_tokens)
+            if self.pieces > 1:
+                nbytes = _ext.lib().mvl_decode_step_host_workspace_bytes(
+                    batch, num_heads, self.num_kv_heads, self.head_dim, max_num_blocks, self.block_size,
+                    self.code, chunk_tokens, self.pieces)
+            else:
+                nbytes = _ext.lib().mvl_paged_decode_workspace_bytes(
+                    batch, num_heads, self.num_kv_heads, self.head_dim, max_num_blocks, self.block_size,
+                    self.code, chunk_tokens)
         self.ws = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device=dev)  # counters start at zero
         self.ws_bytes = nbytes
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in
@@ -512,15 +521,18 @@ class HostDecodeStep:
         (valid once the stream is synchronised, which ``synchronize=True`` does)."""
         with torch.cuda.device(self.dev):
             stream = _stream_ptr(self.dev)
-            _ext.check(_ext.lib().mvl_decode_step_host(
-                self.q_h.data_ptr(), self.k_h.data_ptr(), self.v_h.data_ptr(), self.slot_h.data_ptr(),
-                self.ctx_h.data_ptr(), self.bt_h.data_ptr(), self.out_h.data_ptr(),
-                self.q_d.data_ptr(), self.k_d.data_ptr(), self.v_d.data_ptr(), self.slot_d.data_ptr(),
-                self.ctx_d.data_ptr(), self.bt_d.data_ptr(), self.out_d.data_ptr(),
-                self.k_cache.data_ptr(), self.v_cache.data_ptr(), self.idx_flag, self.batch,
-                self.max_num_blocks, self.num_heads, self.num_kv_heads, self.head_dim,
-                self.block_size, self.num_blocks, self.scale, self.code, self.ws.data_ptr(),
-                self.ws_bytes, self.chunk_tokens, self.flags, stream))
+            args = (self.q_h.data_ptr(), self.k_h.data_ptr(), self.v_h.data_ptr(), self.slot_h.data_ptr(),
+                    self.ctx_h.data_ptr(), self.bt_h.data_ptr(), self.out_h.data_ptr(),
+                    self.q_d.data_ptr(), self.k_d.data_ptr(), self.v_d.data_ptr(), self.slot_d.data_ptr(),
+                    self.ctx_d.data_ptr(), self.bt_d.data_ptr(), self.out_d.data_ptr(),
+                    self.k_cache.data_ptr(), self.v_cache.data_ptr(), self.idx_flag, self.batch,
+                    self.max_num_blocks, self.num_heads, self.num_kv_heads, self.head_dim,
+                    self.block_size, self.num_blocks, self.scale, self.code, self.ws.data_ptr(),
+                    self.ws_bytes, self.chunk_tokens, self.flags)
+            if self.pieces > 1:
+                _ext.check(_ext.lib().mvl_decode_step_host_overlapped(*args, self.pieces, stream))
+            else:
+                _ext.check(_ext.lib().mvl_decode_step_host(*args, stream))
             if synchronize:
                 torch.cuda.current_stream(self.dev).synchronize()
         return self.out_h

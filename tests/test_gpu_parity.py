@@ -294,6 +294,200 @@ def test_c3_full_size_properties(cuda_device):
     assert torch.equal(out_p, out)
 
 
+def _sample_parity(t, w, out, pick, dtype=torch.bfloat16):
+    s = workloads.oracle_sample(t, w, pick)
+    want = c_oracle.paged_decode(s["q"], s["k_cache"], s["v_cache"], s["block_tables"], s["context_lens"],
+                                 s["scale"], s["H"], s["KVH"], s["D"], s["BS"])
+    _assert_close(out[pick].float().cpu().numpy(), want.numpy(), dtype)
+
+
+def test_c2_full_size_properties(cuda_device):
+    """BASELINE config 2, one layer at full size (16Q/8KV/D128, batch 64, 2048-token contexts, 256-slot
+    pages): sample parity against the oracle, split-size invariance, ones-V, and the fused step."""
+    from minivllm_b200.layers.attention import decode_step
+    t = workloads.build_tables("c2")
+    w = workloads.materialize(t, cuda_device)
+    args = (w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"], w["H"],
+            w["KVH"], w["D"], w["BS"])
+    out = paged_attention_decode(w["q"], *args)
+    assert torch.isfinite(out.float()).all()
+    _sample_parity(t, w, out, [0, 21, 42, 63] + workloads.highest_page_sequences(t, 1))
+    for chunk in (256, 100000):
+        assert (out.float() - paged_attention_decode(w["q"], *args, chunk_tokens=chunk).float()).abs().max() <= 2e-2
+    o1 = paged_attention_decode(w["q"], w["k_cache"], torch.ones_like(w["v_cache"]), *args[2:])
+    assert (o1.float() - 1).abs().max() <= 1e-2
+    # the one-launch step (store fused in) on the same batch: caches bit-exact, output as above + new row
+    kc, vc = w["k_cache"].clone(), w["v_cache"].clone()
+    got = decode_step(w["q"], w["k"], w["v"], kc, vc, w["slot_mapping"], w["block_tables"], w["context_lens"],
+                      w["scale"], w["H"], w["KVH"], w["D"], w["BS"])
+    want_k, want_v = w["k_cache"].clone(), w["v_cache"].clone()
+    store_kvcache(w["k"], w["v"], want_k, want_v, w["slot_mapping"], w["BS"])
+    assert torch.equal(kc, want_k) and torch.equal(vc, want_v)
+    w2 = dict(w, k_cache=kc, v_cache=vc)
+    _sample_parity(t, w2, got, [0, 31, 63])
+
+
+def test_c4_full_size_properties(cuda_device):
+    """BASELINE config 4 at full size on one GPU (64Q/8KV/D128, batch 512, contexts 8k-16k): two 13 GB
+    caches whose byte offsets pass 2^32 (where the reference's Triton kernel faults).  The sample
+    deliberately holds the sequences that reach the highest pages of the pool."""
+    free, _ = torch.cuda.mem_get_info(cuda_device)
+    if free < 60e9:
+        pytest.skip("needs ~45 GB of free HBM")
+    t = workloads.build_tables("c4")
+    w = workloads.materialize(t, cuda_device)
+    assert w["k_cache"].numel() * w["k_cache"].element_size() > 2 ** 32
+    args = (w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"], w["H"],
+            w["KVH"], w["D"], w["BS"])
+    out = paged_attention_decode(w["q"], *args)
+    assert torch.isfinite(out.float()).all()
+    high = workloads.highest_page_sequences(t, 2)
+    assert int(t.tables[high[0]].max()) * w["BS"] * w["KVH"] * w["D"] * 2 > 2 ** 32
+    _sample_parity(t, w, out, [0, 255, 511] + high)
+    assert (out.float() - paged_attention_decode(w["q"], *args, chunk_tokens=1024).float()).abs().max() <= 2e-2
+    # CUDA-core kernel on the same batch (other arithmetic, same tolerance)
+    from minivllm_b200 import _ext
+    ffma = paged_attention_decode(w["q"], *args, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_CUDA_CORES)
+    _sample_parity(t, w, ffma, high)
+    w["v_cache"].fill_(1)
+    o1 = paged_attention_decode(w["q"], *args)
+    assert (o1.float() - 1).abs().max() <= 1e-2
+
+
+def test_c5_full_size_properties(cuda_device):
+    """BASELINE config 5 at full size (batch 32, contexts up to 131072, four groups aliasing 16k-96k-token
+    prefixes): unshared, prefix sharing narrow (bit-identical) and wide (group kernel), each against the
+    oracle on a sample holding the 131072-token sequence, one member of every group and the sequences on
+    the highest pages."""
+    from minivllm_b200 import _ext
+    t = workloads.build_tables("c5")
+    w = workloads.materialize(t, cuda_device)
+    assert int(t.ctx.max()) == 131072 and t.unique_tokens < int(t.ctx.sum())
+    args = (w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"], w["H"],
+            w["KVH"], w["D"], w["BS"])
+    pick = sorted(set([0, 9, 18, 31] + workloads.highest_page_sequences(t, 1)))
+    base = paged_attention_decode(w["q"], *args, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_SPLIT_GRID)
+    _sample_parity(t, w, base, pick)
+    stream = paged_attention_decode(w["q"], *args, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_STREAM)
+    assert (stream.float() - base.float()).abs().max() <= 2e-2
+    _sample_parity(t, w, stream, pick)
+    narrow = paged_attention_decode(w["q"], *args, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX |
+                                    _ext.DECODE_SHARE_NARROW)
+    assert torch.equal(narrow, base)
+    for _ in range(2):   # twice: counters and group lists must be left clean
+        wide = paged_attention_decode(w["q"], *args, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX)
+        assert torch.isfinite(wide.float()).all()
+        assert (wide.float() - base.float()).abs().max() <= 2e-2
+        _sample_parity(t, w, wide, pick)
+    o1 = paged_attention_decode(w["q"], w["k_cache"], torch.ones_like(w["v_cache"]), *args[2:],
+                                flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX)
+    assert (o1.float() - 1).abs().max() <= 1e-2
+
+
+# ------------------------------------------------------------------ persistent stream kernel
+def _stream_flags():
+    from minivllm_b200 import _ext
+    return _ext.DECODE_FUSED_COMBINE | _ext.DECODE_STREAM
+
+
+@pytest.mark.parametrize("name", sorted(n for n in CASES if CASES[n]["dtype"] != "f32"))
+def test_stream_kernel_matches_reference_and_oracle(cuda_device, name):
+    """The persistent, evenly cut form of the tensor-core kernel (MVL_DECODE_STREAM) on every 16-bit
+    golden case: same bars as the chunk-grid kernel, twice in a row (its arrival counters must come
+    back to zero), and deterministic."""
+    inp = make_inputs(name)
+    z = np.load(os.path.join(GOLD, name + ".npz"))
+    dev = _dev(inp, cuda_device)
+    outs = [_run(dev, flags=_stream_flags()) for _ in range(2)]
+    assert torch.equal(outs[0], outs[1])
+    got = outs[1].float().cpu().numpy()
+    assert np.abs(got - z["ref_out"]).max() <= 2e-2
+    _assert_close(got, z["ref_out_f32"], inp["q"].dtype)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("H,KVH", [(4, 4), (32, 8), (16, 2), (10, 2), (24, 2)])
+@pytest.mark.parametrize("D,BS", [(128, 16), (64, 16), (128, 256), (64, 8)])
+@pytest.mark.parametrize("B,max_ctx", [(5, 600), (37, 3000), (1, 20000)])
+def test_stream_kernel_random_ragged(cuda_device, dtype, H, KVH, D, BS, B, max_ctx):
+    """Pieces that start and end inside sequences, units spread over many pieces (one long sequence),
+    pieces holding many whole sequences (short ones), G > 8 (two head tiles), pages smaller than a tile."""
+    inp = _random_case(5000 + H * 7 + KVH + D + BS + B, dtype, H, KVH, D, BS, B=B, max_ctx=max_ctx,
+                       ctx_dtype=torch.int32 if BS == 16 else torch.int64)
+    want = _oracle(inp).numpy()
+    got = _run(_dev(inp, cuda_device), flags=_stream_flags()).float().cpu().numpy()
+    assert np.isfinite(got).all()
+    _assert_close(got, want, dtype)
+
+
+def test_stream_kernel_edges_and_fused_step(cuda_device):
+    """Zero-length rows give zeros, lengths around the 64-token row and the page size, the fused
+    KV-cache write (caches bit-exact against the store kernel), and a batch past the kernel's
+    1024-sequence limit falls back to the chunk grid with the same results."""
+    from minivllm_b200.layers.attention import decode_step
+    inp = _random_case(78, torch.bfloat16, 32, 8, 128, 16, B=14, max_ctx=10)
+    ctx = torch.tensor([1, 15, 16, 17, 63, 64, 65, 127, 128, 129, 1024, 1025, 0, 4000])
+    BS, B = 16, 14
+    nblk = (ctx + BS - 1) // BS
+    total = int(nblk.sum())
+    g = torch.Generator().manual_seed(5)
+    tables = torch.full((B, int(nblk.max())), -1, dtype=torch.int32)
+    perm = torch.randperm(total, generator=g).to(torch.int32)
+    at = 0
+    for b in range(B):
+        tables[b, :nblk[b]] = perm[at:at + nblk[b]]
+        at += int(nblk[b])
+    inp.update(k_cache=torch.randn(total, BS, 8, 128, generator=g).to(torch.bfloat16),
+               v_cache=torch.randn(total, BS, 8, 128, generator=g).to(torch.bfloat16),
+               block_tables=tables, context_lens=ctx)
+    dev = _dev(inp, cuda_device)
+    got = _run(dev, flags=_stream_flags()).float().cpu().numpy()
+    keep = ctx.numpy() > 0
+    _assert_close(got[keep], _oracle(inp).numpy()[keep], torch.bfloat16)
+    assert (got[~keep] == 0).all()
+    # fused step
+    k = torch.randn(B, 8, 128, generator=g).to(torch.bfloat16)
+    v = torch.randn(B, 8, 128, generator=g).to(torch.bfloat16)
+    last = (ctx - 1).clamp(min=0)
+    slots = tables[torch.arange(B), last // BS].long() * BS + last % BS
+    slots[12] = -1
+    kc, vc = dev["k_cache"].clone(), dev["v_cache"].clone()
+    out = decode_step(dev["q"], k.to(cuda_device), v.to(cuda_device), kc, vc, slots.to(cuda_device),
+                      dev["block_tables"], dev["context_lens"], inp["scale"], 32, 8, 128, BS, flags=_stream_flags())
+    want_k, want_v = inp["k_cache"].clone(), inp["v_cache"].clone()
+    po.store_kvcache_oracle(k, v, want_k, want_v, slots)
+    assert torch.equal(kc.cpu().view(torch.uint8), want_k.view(torch.uint8))
+    assert torch.equal(vc.cpu().view(torch.uint8), want_v.view(torch.uint8))
+    want = c_oracle.paged_decode(inp["q"], want_k, want_v, tables, ctx, inp["scale"], 32, 8, 128, BS).numpy()
+    _assert_close(out.float().cpu().numpy()[keep], want[keep], torch.bfloat16)
+    # 1100 short sequences: beyond the stream kernel's batch limit -> chunk grid, same answer
+    big = _random_case(79, torch.bfloat16, 8, 2, 128, 16, B=1100, max_ctx=90)
+    got = _run(_dev(big, cuda_device), flags=_stream_flags()).float().cpu().numpy()
+    _assert_close(got, _oracle(big).numpy(), torch.bfloat16)
+
+
+def test_stream_kernel_full_size_c3_shard(cuda_device):
+    """One kv head of C3 (an 8-way head shard, the shape the stream kernel is for) at full size: sample
+    parity, agreement with the chunk-grid kernel, block-permutation invariance (bit-identical)."""
+    from minivllm_b200 import _ext
+    t = workloads.build_tables("c3")
+    w = workloads.materialize(t, cuda_device, kv_heads=slice(0, 1))
+    args = (w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"], w["H"],
+            w["KVH"], w["D"], w["BS"])
+    out = paged_attention_decode(w["q"], *args, flags=_stream_flags())
+    _sample_parity(t, w, out, [0, 85, 170, 255] + workloads.highest_page_sequences(t, 1))
+    grid = paged_attention_decode(w["q"], *args, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_SPLIT_GRID)
+    assert (out.float() - grid.float()).abs().max() <= 2e-2
+    perm = torch.randperm(t.num_blocks, device=cuda_device)
+    inv = torch.empty_like(perm)
+    inv[perm] = torch.arange(t.num_blocks, device=cuda_device)
+    bt = w["block_tables"].long()
+    bt2 = torch.where(bt >= 0, inv[bt.clamp(min=0)], bt).to(torch.int32)
+    out_p = paged_attention_decode(w["q"], w["k_cache"][perm], w["v_cache"][perm], bt2, *args[3:],
+                                   flags=_stream_flags())
+    assert torch.equal(out_p, out)
+
+
 # ------------------------------------------------------------------ fused step (one launch)
 @pytest.mark.parametrize("name", ["ragged_bf16", "long_split", "bs256_bf16", "g8_ragged", "g5_d64"])
 def test_fused_step_equals_separate_launches(cuda_device, name):
@@ -446,16 +640,21 @@ def test_cuda_core_kernel_still_selectable_for_16bit(cuda_device, name):
 
 # ------------------------------------------------------------------ host-buffer step (e2e path)
 @pytest.mark.parametrize("idx", [torch.int64, torch.int32])
-def test_host_decode_step_matches_device_path(cuda_device, idx):
+@pytest.mark.parametrize("pieces", [1, 3, 8])
+def test_host_decode_step_matches_device_path(cuda_device, idx, pieces):
     """mvl_decode_step_host (pinned H2D of the step's inputs, fused store + decode, D2H) against the
-    device-resident fused step on the same inputs; two steps in a row reuse every buffer."""
+    device-resident fused step on the same inputs; two steps in a row reuse every buffer.  With
+    pieces > 1 (mvl_decode_step_host_overlapped) the batch is cut into runs that overlap their copies
+    with each other's kernels: same caches bit for bit, same rows to fp32 rounding (a piece is a
+    smaller launch, so the split points may differ)."""
     from minivllm_b200.layers.attention import HostDecodeStep, decode_step
     inp = make_inputs("ragged_bf16")
     B, H, KVH, D, BS = inp["q"].shape[0], inp["H"], inp["KVH"], inp["D"], inp["BS"]
     kc = inp["k_cache"].to(cuda_device)
     vc = inp["v_cache"].to(cuda_device)
     kc2, vc2 = kc.clone(), vc.clone()
-    hs = HostDecodeStep(kc, vc, B, inp["block_tables"].shape[1], H, inp["scale"], index_dtype=idx)
+    hs = HostDecodeStep(kc, vc, B, inp["block_tables"].shape[1], H, inp["scale"], index_dtype=idx, pieces=pieces)
+    assert hs.pieces == pieces
     g = torch.Generator().manual_seed(8)
     last = inp["context_lens"].long() - 1
     slots = inp["block_tables"][torch.arange(B), last // BS].long() * BS + last % BS
@@ -470,7 +669,13 @@ def test_host_decode_step_matches_device_path(cuda_device, idx):
         want = decode_step(q.to(cuda_device), k.to(cuda_device), v.to(cuda_device), kc2, vc2,
                            slots.to(cuda_device, idx), inp["block_tables"].to(cuda_device),
                            inp["context_lens"].to(cuda_device, idx), inp["scale"], H, KVH, D, BS)
-        assert torch.equal(got, want.cpu())
+        if pieces == 1:
+            assert torch.equal(got, want.cpu())
+        else:
+            assert (got.float() - want.float().cpu()).abs().max() <= 2e-2
+            exact = c_oracle.paged_decode(q, kc2.cpu(), vc2.cpu(), inp["block_tables"], inp["context_lens"],
+                                          inp["scale"], H, KVH, D, BS)
+            _assert_close(got.float().numpy(), exact.numpy(), torch.bfloat16)
         assert torch.equal(kc, kc2) and torch.equal(vc, vc2)
     assert hs.h2d_bytes == hs._h_arena.numel()
 
@@ -515,7 +720,7 @@ def test_prefix_sharing_is_bit_identical(cuda_device, H, KVH, D, chunk):
               (64, [200]), (512, [600, 520]), (320, [330, 321, 400, 900, 350, 322, 640, 333, 500, 321])]
     inp = _aliased_case(900 + H + D, torch.bfloat16, H, KVH, D, 16, groups)
     dev = _dev(inp, cuda_device)
-    base = _run(dev, chunk_tokens=chunk, flags=_ext.DECODE_FUSED_COMBINE)
+    base = _run(dev, chunk_tokens=chunk, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_SPLIT_GRID)
     want = _oracle(inp).numpy()
     narrow = _ext.DECODE_SHARE_PREFIX | _ext.DECODE_SHARE_NARROW
     for flags in (_ext.DECODE_FUSED_COMBINE | narrow, narrow,

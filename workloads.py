@@ -179,3 +179,30 @@ def materialize(t: Tables, device, kv_heads: Optional[slice] = None, seed_offset
     return dict(q=q, k=k, v=v, k_cache=k_cache, v_cache=v_cache, block_tables=tables,
                 context_lens=ctx, slot_mapping=slot_mapping, scale=1.0 / (sp.D ** 0.5),
                 H=h, KVH=kvh, D=sp.D, BS=sp.BS, B=B)
+
+
+def oracle_sample(t: Tables, w: dict, pick):
+    """CPU copies of sequences ``pick`` of a materialised batch ``w`` for the oracle: only the pages
+    those sequences reference are gathered (on the device) and the tables re-numbered, so a 26 GB
+    cache costs a few hundred MB of host memory.  Returns the oracle's argument dict."""
+    sp = t.spec
+    pick = np.asarray(pick, dtype=np.int64)
+    nblk = (t.ctx[pick] + sp.BS - 1) // sp.BS
+    used = np.unique(np.concatenate([t.tables[b, :n] for b, n in zip(pick, nblk)]))
+    remap = np.full(t.num_blocks, -1, dtype=np.int32)
+    remap[used] = np.arange(len(used), dtype=np.int32)
+    tables = np.full((len(pick), int(nblk.max())), -1, dtype=np.int32)
+    for i, (b, n) in enumerate(zip(pick, nblk)):
+        tables[i, :n] = remap[t.tables[b, :n]]
+    idx = torch.from_numpy(used.astype(np.int64)).to(w["k_cache"].device)
+    sel = torch.from_numpy(pick).to(w["q"].device)
+    return dict(q=w["q"][sel].cpu(), k_cache=w["k_cache"][idx].cpu(), v_cache=w["v_cache"][idx].cpu(),
+                block_tables=torch.from_numpy(tables), context_lens=torch.from_numpy(t.ctx[pick].copy()),
+                scale=w["scale"], H=w["H"], KVH=w["KVH"], D=w["D"], BS=w["BS"])
+
+
+def highest_page_sequences(t: Tables, k: int = 2):
+    """The ``k`` sequences whose block tables reach the highest physical pages of the pool (largest
+    byte offsets into the caches)."""
+    top = np.where(t.tables >= 0, t.tables, -1).max(axis=1)
+    return [int(i) for i in np.argsort(-top)[:k]]
