@@ -352,11 +352,14 @@ def run_ours(args, rank, world, local_rank):
     out = torch.empty_like(w["q"])
     staging = torch.empty((world, B, w["H"], w["D"]), dtype=out.dtype, device=dev) if world > 1 else None
     fused, gather_kind = None, "none"
+    if args.unfused and world > 1:
+        args.gather = "nccl"   # the peer-store gather signals once per step: one launch per step only
     if world > 1 and args.gather == "peer":
         try:
             from minivllm_b200.head_shard import PeerGatheredDecode
             fused = PeerGatheredDecode(sh, B, sp.H, sp.D, out.dtype, dev)
-            gather_kind = "peer stores from the decode kernels (mvl_paged_decode_peers) + barrier"
+            gather_kind = ("peer stores from the decode kernel, step announced from its epilogue, one-warp wait "
+                           "kernel (mvl_decode_step_peers_sync + mvl_peer_wait); two result buffers in turns")
         except Exception as exc:  # symmetric memory unavailable on this box: say so, use NCCL
             gather_kind = f"NCCL all-gather (peer-memory setup failed: {type(exc).__name__})"
         ok = torch.tensor([1 if fused is not None else 0], device=dev)

@@ -295,6 +295,21 @@ int mvl_decode_step_peers(void* const* out_peers, int num_peers, int total_heads
                           int chunk_tokens, unsigned flags, void* stream);
 
 /*
+ * mvl_allgather_heads — NCCL all-gather of head-sharded attention outputs into the unsharded layout.
+ * Rank r passes its (batch, heads_local, head_dim) result; every rank receives (batch,
+ * world_size * heads_local, head_dim) in out_full, rank r's heads at head offset r * heads_local —
+ * where the reference's tensor-parallel layout puts them (layers/linear.py:163-165; the reference
+ * itself never gathers, it all-reduces behind o_proj, linear.py:216-221).  `nccl_comm` is the
+ * caller's ncclComm_t passed as void*; `staging` is caller-owned scratch of world_size * batch *
+ * heads_local * head_dim elements.  One ncclAllGather plus one layout kernel on `stream`.
+ * The library does not link NCCL: it calls the ncclAllGather of the libnccl.so.2 already loaded in
+ * the process (the one that made the communicator).  world_size == 1 copies out_local to out_full.
+ */
+int mvl_allgather_heads(void* out_full, void* staging, const void* out_local, int64_t batch,
+                        int heads_local, int head_dim, int elem_dtype, int world_size, void* nccl_comm,
+                        void* stream);
+
+/*
  * mvl_decode_step_peers_sync / mvl_peer_wait — the peer-store gather with its own completion
  * protocol, for use between steps WITHOUT a barrier collective.  No reference counterpart (the
  * reference gathers nothing: it all-reduces after a row-parallel o_proj, layers/linear.py:216-221).

@@ -50,6 +50,7 @@ PROTOTYPES = {
                                    _i, _i, _i, _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
     "mvl_decode_step_peers_sync": (_i, [_vp, _vp, _i, _i, _i, _i] + [_vp] * 8 + [_i, _i64, _i64, _i64, _i64, _i64,
                                         _i, _i, _i, _i, _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
+    "mvl_allgather_heads": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _vp, _vp]),
     "mvl_peer_wait": (_i, [_vp, _i, _i64, _vp]),
     "mvl_decode_step_host": (_i, [_vp] * 16 + [_i, _i64, _i64, _i, _i, _i, _i, _i64, _f, _i, _vp,
                                                _sz, _i, _u, _vp]),

@@ -16,6 +16,10 @@ int launch_prefix_share(const int32_t* bt, long long bt_stride, const void* ctx,
                         long long batch, long long max_ctx, int bs_shift, int chunk, int mm, int* meta,
                         cudaStream_t s);
 
+// abi.cu: record an error text for mvl_last_cuda_error() and return MVL_ERR_CUDA.
+int fail_text(const char* where, int code);
+int fail_cuda(int cuda_error, const char* where);
+
 // peer_sync.cu: announce this rank's step to all ranks / wait until all ranks announced mine.
 int launch_peer_signal(unsigned* local, unsigned* const* peers, int n, int my_rank, cudaStream_t s);
 int launch_peer_wait(unsigned* local, int n, unsigned long long timeout_ns, cudaStream_t s);

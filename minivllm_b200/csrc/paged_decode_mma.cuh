@@ -104,7 +104,12 @@ struct MmaCfg {
   static constexpr int RING = 3;
   static constexpr int MRG_BYTES = NC * D * 4 + NC * 8;  // merged [column][D] fp32 + (m,l)[column]
   static constexpr int WARP_SMEM = (RING * TILEB > MRG_BYTES ? RING * TILEB : ((MRG_BYTES + 255) / 256) * 256);
-  static constexpr int SMEM = NW * WARP_SMEM;
+  // q of the CTA's columns, staged once through shared memory (rows padded by 16 B so that the 8
+  // fragment rows a load touches fall into different banks): one coalesced 16-byte read per chunk
+  // instead of every warp gathering its fragments from global memory in 4-byte pieces.
+  static constexpr int QROWB = ROWB + 16;
+  static constexpr int Q_BYTES = ((NC * QROWB + 255) / 256) * 256;
+  static constexpr int SMEM = NW * WARP_SMEM + Q_BYTES;
   static_assert(sizeof(T) == 2, "tensor-core path is for 16-bit caches");
   static_assert(CPRW >= 8 && CPRW <= 16, "head_dim 64 or 128");
 };
@@ -178,20 +183,27 @@ __global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_k
   const uint32_t ring = smem_u32(smem) + warp * C::WARP_SMEM;
 
   // ---- q as B fragments of the score product: n = column nt*8+g = (member, head), k = d.
+  // Staged through shared memory: thread i copies 16-byte chunk i of the CTA's q rows (coalesced; also
+  // the only q traffic when q lives in host memory), then every lane picks its fragments from there.
+  const uint32_t qs = smem_u32(smem) + NW * C::WARP_SMEM;
+  for (int i = threadIdx.x; i < NC * CPRW; i += NW * 32) {
+    const int col = i / CPRW, c16 = i % CPRW;
+    const int cm = col >> p.gp_shift, chd = col & gp_mask;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (cm < nmem && chd < g_valid)
+      v = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(p.q) +
+                                          ((long long)(b + cm) * p.H + head0 + chd) * ROWB + c16 * 16);
+    sts128(qs + col * C::QROWB + c16 * 16, v);
+  }
+  __syncthreads();
   uint32_t qb[NT][KS][2];
 #pragma unroll
   for (int nt = 0; nt < NT; ++nt) {
-    const int col = nt * 8 + g, cm = col >> p.gp_shift, chd = col & gp_mask;  // member and head
-    const bool col_ok = cm < nmem && chd < g_valid;
+    const uint32_t qrow = qs + (nt * 8 + g) * C::QROWB + 4 * t;
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks) {
-      qb[nt][ks][0] = qb[nt][ks][1] = 0u;
-      if (col_ok) {
-        const T* qrow = reinterpret_cast<const T*>(p.q) + ((long long)(b + cm) * p.H + head0 + chd) * D +
-                        ks * 16 + 2 * t;
-        qb[nt][ks][0] = *reinterpret_cast<const uint32_t*>(qrow);
-        qb[nt][ks][1] = *reinterpret_cast<const uint32_t*>(qrow + 8);
-      }
+      qb[nt][ks][0] = lds32(qrow + ks * 32);
+      qb[nt][ks][1] = lds32(qrow + ks * 32 + 16);
     }
   }
 

@@ -51,6 +51,7 @@ __global__ void __launch_bounds__(128, 4) paged_decode_stream_mma_kernel(const D
   constexpr int GT = C::GT, NW = C::NW, TR = C::TR, ROWB = C::ROWB, CPRW = C::CPRW, RPP = C::RPP,
                 R = C::R, TILEB = C::TILEB, KS = C::KS, RING = C::RING;
   extern __shared__ __align__(1024) unsigned char smem[];
+  // (C::SMEM = the four warps' rings + the q staging area of paged_decode_mma.cuh)
   int* cum = reinterpret_cast<int*>(smem + C::SMEM);                 // cum[b] = rows of sequences < b
   int* misc = reinterpret_cast<int*>(smem + C::SMEM + S::CUM_BYTES);  // [0..3] warp totals, [8] flag
 
@@ -173,15 +174,25 @@ __global__ void __launch_bounds__(128, 4) paged_decode_stream_mma_kernel(const D
       __syncthreads();
     }
 
-    // ---- q as B fragments: n = head g, k = d
+    // ---- q as B fragments (n = head g, k = d), staged through shared memory as in the split kernel.
+    // The previous segment's fragment reads of the staging area are behind that segment's barriers.
+    const uint32_t qs = sbase + NW * C::WARP_SMEM;
+    for (int i = threadIdx.x; i < 8 * CPRW; i += NW * 32) {
+      const int col = i / CPRW, c16 = i % CPRW;
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      if (col < g_valid)
+        v = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(p.q) +
+                                            ((long long)b * p.H + head0 + col) * ROWB + c16 * 16);
+      sts128(qs + col * C::QROWB + c16 * 16, v);
+    }
+    __syncthreads();
     uint32_t qb[KS][2];
+    {
+      const uint32_t qrow = qs + g * C::QROWB + 4 * t;
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) {
-      qb[ks][0] = qb[ks][1] = 0u;
-      if (g < g_valid) {
-        const T* qrow = reinterpret_cast<const T*>(p.q) + ((long long)b * p.H + head0 + g) * D + ks * 16 + 2 * t;
-        qb[ks][0] = *reinterpret_cast<const uint32_t*>(qrow);
-        qb[ks][1] = *reinterpret_cast<const uint32_t*>(qrow + 8);
+      for (int ks = 0; ks < KS; ++ks) {
+        qb[ks][0] = lds32(qrow + ks * 32);
+        qb[ks][1] = lds32(qrow + ks * 32 + 16);
       }
     }
 

@@ -70,14 +70,23 @@ def gather_heads(o_local: torch.Tensor, group: Optional[dist.ProcessGroup] = Non
 
 
 class PeerGatheredDecode:
-    """Head-sharded decode whose result stores ARE the all-gather (``mvl_paged_decode_peers``).
+    """Head-sharded decode whose result stores ARE the all-gather (``mvl_decode_step_peers_sync``).
 
-    Every rank owns a (batch, total_heads, head_dim) result buffer in symmetric (peer-mapped)
-    memory.  A rank's decode kernels write its heads straight into all ranks' buffers over NVLink
-    P2P; one barrier on the symmetric-memory signal pads then makes every buffer complete.  Compared
-    with ``gather_heads`` this removes the NCCL all-gather launch and the (N,B,h,D)->(B,H,D)
-    permute copy from the step.  ``torch.distributed._symmetric_memory`` is used for the plumbing
-    only (allocation, handle exchange, barrier); the data path is our kernels' stores.
+    Every rank owns TWO (batch, total_heads, head_dim) result buffers and a 64-byte control block in
+    symmetric (peer-mapped) memory.  A rank's decode kernels write its heads straight into all ranks'
+    buffers over NVLink P2P and then announce the step in every rank's control block; ``wait()``
+    enqueues a one-warp kernel that returns once all ranks have announced this rank's current step.
+    Compared with ``gather_heads`` this removes the NCCL all-gather launch, the (N,B,h,D)->(B,H,D)
+    permute copy and any barrier collective from the step.
+
+    The two buffers are used in turns, so a fast rank's step t+1 stores never land in the buffer a
+    slow rank is still reading for step t; a rank reaches step t+2 (the next writer of step t's
+    buffer) only behind its own wait of step t+1, which every rank signals after its step-t consumer
+    in stream order.  Contract for the caller: every rank makes the same sequence of calls, and the
+    tensor returned for step t is valid from that step's wait until this rank's call of step t+2.
+
+    ``torch.distributed._symmetric_memory`` is used for the plumbing only (allocation, handle
+    exchange); the data path and the signalling are this library's kernels.
     """
 
     def __init__(self, shard: HeadShard, batch: int, total_heads: int, head_dim: int,
@@ -88,20 +97,36 @@ class PeerGatheredDecode:
 
         self.shard, self.batch, self.total_heads, self.head_dim = shard, batch, total_heads, head_dim
         self.group = group if group is not None else dist.group.WORLD
-        self.out = symm_mem.empty((batch, total_heads, head_dim), dtype=dtype, device=device)
-        self.handle = symm_mem.rendezvous(self.out, self.group)
+        self.bufs = symm_mem.empty((2, batch, total_heads, head_dim), dtype=dtype, device=device)
+        self.handle = symm_mem.rendezvous(self.bufs, self.group)
+        self.ctrl = symm_mem.empty((16,), dtype=torch.int32, device=device)
+        self.ctrl.zero_()
+        self.ctrl_handle = symm_mem.rendezvous(self.ctrl, self.group)
         ptrs = list(self.handle.buffer_ptrs)
-        if len(ptrs) != shard.world_size:
+        cptrs = list(self.ctrl_handle.buffer_ptrs)
+        if len(ptrs) != shard.world_size or len(cptrs) != shard.world_size:
             raise RuntimeError("symmetric-memory rendezvous returned the wrong number of peers")
-        self._ptr_array = (ctypes.c_void_p * len(ptrs))(*ptrs)
+        half = batch * total_heads * head_dim * self.bufs.element_size()
+        self._ptr_arrays = [(ctypes.c_void_p * len(ptrs))(*[p + par * half for p in ptrs]) for par in (0, 1)]
+        self._ctrl_array = (ctypes.c_void_p * len(cptrs))(*cptrs)
         self.device = device
+        self.step = 0
+        # every control block is zero before any rank can write a step count into it
+        torch.cuda.synchronize(device)
+        dist.barrier(self.group)
+
+    @property
+    def out(self) -> torch.Tensor:
+        """The buffer of the most recent step (of step 0 before any call)."""
+        return self.bufs[(self.step - 1) & 1 if self.step else 0]
 
     def __call__(self, query, k_cache, v_cache, block_tables, context_lens, scale, block_size,
                  chunk_tokens: int = 0, flags: Optional[int] = None, barrier: bool = True,
                  store=None) -> torch.Tensor:
-        """Decode this rank's heads into every rank's buffer; returns this rank's full
-        (batch, total_heads, head_dim) buffer (complete after the barrier).  ``store=(key, value,
-        slot_mapping)`` fuses the step's KV-cache write into the same launch (mvl_decode_step_peers)."""
+        """Decode this rank's heads into every rank's buffer of this step; returns this rank's full
+        (batch, total_heads, head_dim) buffer (complete after ``wait()``, which ``barrier=True``
+        enqueues).  ``store=(key, value, slot_mapping)`` fuses the step's KV-cache write into the
+        same launch."""
         import ctypes
 
         from . import _ext
@@ -113,34 +138,42 @@ class PeerGatheredDecode:
         batch, max_blocks = query.shape[0], block_tables.shape[1]
         code = att._dtype_code(query)
         lib = _ext.lib()
+        par = self.step & 1
         with att._on_device(self.device):
             nbytes = lib.mvl_paged_decode_workspace_bytes(batch, sh.num_heads, sh.num_kv_heads,
                                                           self.head_dim, max_blocks, block_size, code,
                                                           chunk_tokens)
             ws = att.workspace_for(self.device, nbytes)
-            peers = ctypes.cast(self._ptr_array, ctypes.c_void_p)
+            peers = ctypes.cast(self._ptr_arrays[par], ctypes.c_void_p)
+            ctrls = ctypes.cast(self._ctrl_array, ctypes.c_void_p)
             wsp, wsn = (ws.data_ptr(), ws.numel()) if ws is not None else (None, 0)
             idx = att._index_flag("context_lens", context_lens)
-            if store is None:
-                _ext.check(lib.mvl_paged_decode_peers(
-                    peers, sh.world_size, self.total_heads, sh.q_heads.start, query.data_ptr(),
-                    k_cache.data_ptr(), v_cache.data_ptr(), block_tables.data_ptr(),
-                    context_lens.data_ptr(), idx, batch, max_blocks, block_tables.stride(0),
-                    sh.num_heads, sh.num_kv_heads, self.head_dim, block_size, k_cache.shape[0],
-                    float(scale), code, wsp, wsn, chunk_tokens, flags, att._stream_ptr(self.device)))
-            else:
-                key, value, slots = store
-                _ext.check(lib.mvl_decode_step_peers(
-                    peers, sh.world_size, self.total_heads, sh.q_heads.start, query.data_ptr(),
-                    key.data_ptr(), value.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
-                    slots.data_ptr(), block_tables.data_ptr(), context_lens.data_ptr(), idx, batch,
-                    max_blocks, block_tables.stride(0), key.stride(0), value.stride(0), sh.num_heads,
-                    sh.num_kv_heads, self.head_dim, block_size, k_cache.shape[0], float(scale), code,
-                    wsp, wsn, chunk_tokens, flags, att._stream_ptr(self.device)))
+            key, value, slots = store if store is not None else (None, None, None)
+            _ext.check(lib.mvl_decode_step_peers_sync(
+                peers, ctrls, sh.world_size, sh.rank, self.total_heads, sh.q_heads.start, query.data_ptr(),
+                key.data_ptr() if key is not None else None, value.data_ptr() if value is not None else None,
+                k_cache.data_ptr(), v_cache.data_ptr(), slots.data_ptr() if slots is not None else None,
+                block_tables.data_ptr(), context_lens.data_ptr(), idx, batch, max_blocks,
+                block_tables.stride(0), key.stride(0) if key is not None else 0,
+                value.stride(0) if value is not None else 0, sh.num_heads, sh.num_kv_heads, self.head_dim,
+                block_size, k_cache.shape[0], float(scale), code, wsp, wsn, chunk_tokens, flags,
+                att._stream_ptr(self.device)))
+            self.step += 1
             if barrier:
-                self.barrier()
-        return self.out
+                self.wait()
+        return self.bufs[par]
 
-    def barrier(self) -> None:
-        """All ranks' stores issued before this point are visible in every buffer after it."""
-        self.handle.barrier(channel=0)
+    def wait(self, timeout_ms: int = 0) -> None:
+        """Enqueue the wait for the current step on this device's current stream: work enqueued after
+        it sees every rank's rows of the step in this rank's buffer."""
+        from . import _ext
+        from .layers import attention as att
+        with att._on_device(self.device):
+            _ext.check(_ext.lib().mvl_peer_wait(self.ctrl.data_ptr(), self.shard.world_size, timeout_ms,
+                                                att._stream_ptr(self.device)))
+
+    barrier = wait  # earlier name
+
+    def timed_out(self) -> int:
+        """0, or 1 + the rank a wait gave up on (reads the control block: synchronises)."""
+        return int(self.ctrl[10].item())

@@ -395,6 +395,18 @@ class Attention(nn.Module):
         block_size = self._effective_block_size()
 
         has_cache = k_cache.numel() > 0 and v_cache.numel() > 0 and context.slot_mapping is not None
+        # The reference's own caller can hand over mixed dtypes: with a 16-bit model its rotary
+        # embedding multiplies by an fp32 table, so q and k arrive in fp32 next to a 16-bit v and
+        # 16-bit caches (rotary_embedding.py:15-23; qwen3.py:108-110).  Its Triton kernels cast on
+        # store / load; here the operands are brought to the cache's dtype once and the result goes
+        # back to the caller's q dtype (the reference returns empty_like(query), attention.py:450).
+        want_dtype = q.dtype
+        if k_cache.numel() > 0 and (q.dtype != k_cache.dtype or k.dtype != k_cache.dtype or v.dtype != k_cache.dtype):
+            q, k, v = q.to(k_cache.dtype), k.to(k_cache.dtype), v.to(k_cache.dtype)
+            if out is not None and out.dtype != k_cache.dtype:
+                raise ValueError("out= must have the cache's dtype when the operands are cast to it")
+            o = self.forward(q, k, v, out=out)
+            return o.to(want_dtype)
         if has_cache and k.dim() == 4:  # (B, N, KVH, D) -> (B*N, KVH, D)
             k = k.reshape(-1, k.shape[-2], k.shape[-1])
             v = v.reshape(-1, v.shape[-2], v.shape[-1])
@@ -459,10 +471,13 @@ class HostDecodeStep:
 
     def __init__(self, k_cache: torch.Tensor, v_cache: torch.Tensor, batch: int, max_num_blocks: int,
                  num_heads: int, scale: float, index_dtype: torch.dtype = torch.int64,
-                 chunk_tokens: int = 0, flags: int = 0, pieces: Optional[int] = None):
-        """``pieces``: how many runs of consecutive sequences the step is cut into so that the copies
+                 chunk_tokens: int = 0, flags: int = 0, pieces: Optional[int] = None,
+                 direct_out: bool = False, direct_q: bool = False):
+        """``direct_out`` / ``direct_q`` (serial form only): the kernels write the result rows straight
+        into the pinned host buffer / read q straight from it over PCIe, instead of a separate copy.
+        ``pieces``: how many runs of consecutive sequences the step is cut into so that the copies
         of one run travel while another computes (``mvl_decode_step_host_overlapped``); 1 = the strictly
-        serial ``mvl_decode_step_host``.  Default: 4 for batches of at least 64 sequences, else 1."""
+        serial ``mvl_decode_step_host`` (the default: measured on B200 the smaller launches lose what the overlap gains)."""
         dev = _need_cuda(k_cache=k_cache, v_cache=v_cache)
         if k_cache.dim() != 4 or k_cache.shape != v_cache.shape or not (
                 k_cache.is_contiguous() and v_cache.is_contiguous()):
@@ -500,7 +515,8 @@ class HostDecodeStep:
         self.q_d, self.k_d, self.v_d, self.slot_d, self.ctx_d, self.bt_d = views(self._d_arena)
         self.out_h = torch.empty((batch, num_heads, self.head_dim), dtype=dt, pin_memory=True)
         self.out_d = torch.empty((batch, num_heads, self.head_dim), dtype=dt, device=dev)
-        self.pieces = (4 if batch >= 64 else 1) if pieces is None else max(1, min(int(pieces), 8, batch))
+        self.direct_out, self.direct_q = bool(direct_out), bool(direct_q)
+        self.pieces = 1 if pieces is None else max(1, min(int(pieces), 8, batch))
         with torch.cuda.device(dev):
             if self.pieces > 1:
                 nbytes = _ext.lib().mvl_decode_step_host_workspace_bytes(
@@ -521,10 +537,13 @@ class HostDecodeStep:
         (valid once the stream is synchronised, which ``synchronize=True`` does)."""
         with torch.cuda.device(self.dev):
             stream = _stream_ptr(self.dev)
+            direct = self.pieces == 1
+            q_d = self.q_h.data_ptr() if (direct and self.direct_q) else self.q_d.data_ptr()
+            out_d = self.out_h.data_ptr() if (direct and self.direct_out) else self.out_d.data_ptr()
             args = (self.q_h.data_ptr(), self.k_h.data_ptr(), self.v_h.data_ptr(), self.slot_h.data_ptr(),
                     self.ctx_h.data_ptr(), self.bt_h.data_ptr(), self.out_h.data_ptr(),
-                    self.q_d.data_ptr(), self.k_d.data_ptr(), self.v_d.data_ptr(), self.slot_d.data_ptr(),
-                    self.ctx_d.data_ptr(), self.bt_d.data_ptr(), self.out_d.data_ptr(),
+                    q_d, self.k_d.data_ptr(), self.v_d.data_ptr(), self.slot_d.data_ptr(),
+                    self.ctx_d.data_ptr(), self.bt_d.data_ptr(), out_d,
                     self.k_cache.data_ptr(), self.v_cache.data_ptr(), self.idx_flag, self.batch,
                     self.max_num_blocks, self.num_heads, self.num_kv_heads, self.head_dim,
                     self.block_size, self.num_blocks, self.scale, self.code, self.ws.data_ptr(),

@@ -55,4 +55,15 @@ for pieces in (1, 2, 4, 8):
             hs(synchronize=False)
         res[f"host_issue_us_pieces{pieces}"] = (time.perf_counter() - t0) / 50 * 1e6
         torch.cuda.synchronize()
+for name_, kw in (("direct_out", dict(direct_out=True)), ("direct_q", dict(direct_q=True)),
+                  ("direct_out_q", dict(direct_out=True, direct_q=True))):
+    hs = HostDecodeStep(w["k_cache"], w["v_cache"], B, t.tables.shape[1], w["H"], w["scale"], pieces=1, **kw)
+    hs.q_h.copy_(w["q"].cpu()), hs.k_h.copy_(w["k"].cpu()), hs.v_h.copy_(w["v"].cpu())
+    hs.slot_h.copy_(w["slot_mapping"].cpu()), hs.ctx_h.copy_(w["context_lens"].cpu())
+    hs.bt_h.copy_(w["block_tables"].cpu())
+    res[f"host_step_{name_}_ms"] = timed(lambda: hs())
+    ref = HostDecodeStep(w["k_cache"], w["v_cache"], B, t.tables.shape[1], w["H"], w["scale"], pieces=1)
+    for a in ("q_h", "k_h", "v_h", "slot_h", "ctx_h", "bt_h"):
+        getattr(ref, a).copy_(getattr(hs, a))
+    res[f"{name_}_bitwise_equal"] = bool(torch.equal(ref().clone(), hs().clone()))
 print(json.dumps(res))

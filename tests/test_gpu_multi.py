@@ -99,6 +99,107 @@ def test_peer_stores_gather_on_one_gpu(cuda_device, name, world):
         assert torch.equal(buf, full)
 
 
+@pytest.mark.parametrize("chunk", [0, CHUNK])
+def test_peer_sync_protocol_on_one_gpu(cuda_device, chunk):
+    """mvl_decode_step_peers_sync / mvl_peer_wait with two emulated ranks on this GPU, one launch after
+    the other (never a wait before the rank it waits for has been launched): after both ranks' steps
+    each control block holds both step counts, the waits pass, the step's buffer of each rank equals
+    the unsharded result and the other buffer is untouched; then a wait for a rank that never
+    arrives gives up after its time-out and names the rank."""
+    import ctypes
+
+    from minivllm_b200 import _ext
+    from minivllm_b200.layers import attention as att
+    inp = make_inputs("ragged_bf16")
+    world = 2
+    full = _local_decode(inp, shard_plan(inp["H"], inp["KVH"], 1, 0), cuda_device)
+    B, H, D = inp["q"].shape
+    bufs = torch.full((world, 2, B, H, D), float("nan"), dtype=inp["q"].dtype, device=cuda_device)
+    ctrl = torch.zeros(world, 16, dtype=torch.int32, device=cuda_device)
+    cptr = (ctypes.c_void_p * world)(*[ctrl[r].data_ptr() for r in range(world)])
+    bt, cl = inp["block_tables"].to(cuda_device), inp["context_lens"].to(cuda_device)
+    lib = _ext.lib()
+    stream = torch.cuda.current_stream().cuda_stream
+    shards = []
+    for r in range(world):
+        sh = shard_plan(H, inp["KVH"], world, r)
+        shards.append((sh, inp["q"][:, sh.q_heads].contiguous().to(cuda_device),
+                       inp["k_cache"][:, :, sh.kv_heads].contiguous().to(cuda_device),
+                       inp["v_cache"][:, :, sh.kv_heads].contiguous().to(cuda_device)))
+    nbytes = lib.mvl_paged_decode_workspace_bytes(B, H // world, inp["KVH"] // world, D, bt.shape[1], inp["BS"],
+                                                  att._dtype_code(inp["q"]), chunk)
+    ws = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device=cuda_device)
+
+    def launch(r, par):
+        sh, q, kc, vc = shards[r]
+        optr = (ctypes.c_void_p * world)(*[bufs[d, par].data_ptr() for d in range(world)])
+        _ext.check(lib.mvl_decode_step_peers_sync(
+            ctypes.cast(optr, ctypes.c_void_p), ctypes.cast(cptr, ctypes.c_void_p), world, r, H, sh.q_heads.start,
+            q.data_ptr(), None, None, kc.data_ptr(), vc.data_ptr(), None, bt.data_ptr(), cl.data_ptr(),
+            int(cl.dtype == torch.int64), B, bt.shape[1], bt.stride(0), 0, 0, sh.num_heads, sh.num_kv_heads, D,
+            inp["BS"], kc.shape[0], float(inp["scale"]), att._dtype_code(q), ws.data_ptr(), ws.numel(), chunk,
+            _ext.DECODE_FUSED_COMBINE, stream))
+
+    for step in range(3):
+        par = step & 1
+        for r in range(world):
+            launch(r, par)
+        for r in range(world):
+            _ext.check(lib.mvl_peer_wait(ctrl[r].data_ptr(), world, 2000, stream))
+        torch.cuda.synchronize()
+        c = ctrl.cpu()
+        assert c[:, :world].eq(step + 1).all() and c[:, 8].eq(step + 1).all()
+        assert c[:, 9].eq(0).all() and c[:, 10].eq(0).all()
+        for r in range(world):
+            if chunk:
+                assert torch.equal(bufs[r, par], full)
+            else:
+                assert (bufs[r, par].float() - full.float()).abs().max() <= 2e-2
+            if step == 0:
+                assert torch.isnan(bufs[r, 1].float()).all()
+    # rank 1 never launches step 4: rank 0's wait must give up and say so (bounded, 50 ms)
+    launch(0, 1)
+    _ext.check(lib.mvl_peer_wait(ctrl[0].data_ptr(), world, 50, stream))
+    torch.cuda.synchronize()
+    assert int(ctrl[0, 10]) == 2 and int(ctrl[0, 8]) == 4 and int(ctrl[0, 1]) == 3
+
+
+def _c_abi_nccl_gather(rank, world, dev, local, full):
+    """mvl_allgather_heads with a communicator made the way a non-Python host would make it: raw NCCL
+    calls (here through ctypes on the process's libnccl.so.2), the ncclComm_t handed over as void*."""
+    import ctypes
+
+    import torch.distributed as dist
+    from minivllm_b200 import _ext
+    from minivllm_b200.layers import attention as att
+    nccl = ctypes.CDLL("libnccl.so.2")
+
+    class UniqueId(ctypes.Structure):
+        _fields_ = [("internal", ctypes.c_char * 128)]
+
+    uid = UniqueId()
+    if rank == 0:
+        assert nccl.ncclGetUniqueId(ctypes.byref(uid)) == 0
+    buf = torch.frombuffer(bytearray(bytes(uid)), dtype=torch.uint8).to(dev)
+    dist.broadcast(buf, 0)
+    ctypes.memmove(ctypes.byref(uid), bytes(buf.cpu().numpy().tobytes()), 128)
+    comm = ctypes.c_void_p()
+    nccl.ncclCommInitRank.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int, UniqueId, ctypes.c_int]
+    assert nccl.ncclCommInitRank(ctypes.byref(comm), world, uid, rank) == 0
+    try:
+        B, h, D = local.shape
+        staging = torch.empty(world, B, h, D, dtype=local.dtype, device=dev)
+        out = torch.full((B, world * h, D), float("nan"), dtype=local.dtype, device=dev)
+        _ext.check(_ext.lib().mvl_allgather_heads(out.data_ptr(), staging.data_ptr(), local.contiguous().data_ptr(), B,
+                                                  h, D, att._dtype_code(local), world, comm,
+                                                  torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        return bool(torch.equal(out, full))
+    finally:
+        nccl.ncclCommDestroy.argtypes = [ctypes.c_void_p]
+        nccl.ncclCommDestroy(comm)
+
+
 def _nccl_worker(rank, world, port, ret):
     import torch.distributed as dist
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
@@ -122,13 +223,21 @@ def _nccl_worker(rank, world, port, ret):
         kc = inp["k_cache"][:, :, sh.kv_heads].contiguous().to(dev)
         vc = inp["v_cache"][:, :, sh.kv_heads].contiguous().to(dev)
         bt, cl = inp["block_tables"].to(dev), inp["context_lens"].to(dev)
-        for _ in range(3):  # repeated steps reuse the buffers
-            fused.out.fill_(float("nan"))
-            fused.barrier()
-            res = fused(q, kc, vc, bt, cl, inp["scale"], inp["BS"], chunk_tokens=CHUNK)
+        for it in range(8):
+            # even steps: the library's own split (persistent kernel, step announced from its epilogue);
+            # odd steps: pinned chunk size (chunk grid + one-thread signal launch), bit-identical to `full`
+            res = fused(q, kc, vc, bt, cl, inp["scale"], inp["BS"], chunk_tokens=(CHUNK if it % 2 else 0))
+            if rank == it % world:
+                torch.cuda._sleep(30_000_000)   # a slow consumer on one rank: the others run ahead
+            snap = res.clone()                  # the consumer's read, behind the wait in stream order
+            res.fill_(float("nan"))             # poison what was read; its next writer is step it + 2
             torch.cuda.synchronize()
-            ok = ok and bool(torch.equal(res, full))
-            fused.barrier()
+            if it % 2:
+                ok = ok and bool(torch.equal(snap, full))
+            else:
+                ok = ok and bool((snap.float() - full.float()).abs().max() <= 2e-2)
+        ok = ok and fused.timed_out() == 0
+        ok = ok and _c_abi_nccl_gather(rank, world, dev, local, full)
         ret[rank] = ok
     finally:
         dist.destroy_process_group()

@@ -249,3 +249,32 @@ def test_scheduler_prefill_first_decode_preempt_finish():
     assert sch.is_finished() and sch.num_preemptions >= 1
     assert b.num_completion_tokens == 8 and d.num_completion_tokens == 20
     assert len(sch.block_manager.free_block_ids) == 9
+
+
+def test_dropin_registers_the_reference_import_paths():
+    """Without the reference package on the path, ``dropin.install()`` registers stand-in modules so the
+    reference's import lines resolve to the mirror; ``uninstall()`` removes them again."""
+    import importlib
+    import sys
+
+    from minivllm_b200 import dropin
+    from minivllm_b200.layers import attention as att
+    from minivllm_b200.utils import context as ctx
+    if importlib.util.find_spec("myvllm") is not None:
+        pytest.skip("a real myvllm is importable here; the patching path is covered by tests/test_gpu_dropin.py")
+    try:
+        names = dropin.install()
+        assert "myvllm.layers.attention.Attention" in names and "myvllm.utils.set_context" in names
+        from myvllm.layers.attention import Attention, paged_attention_decode, store_kvcache
+        from myvllm.utils import get_context, reset_context, set_context
+        from myvllm.utils.context import Context
+        import myvllm.layers
+        assert Attention is att.Attention and store_kvcache is att.store_kvcache
+        assert paged_attention_decode is att.paged_attention_decode and myvllm.layers.Attention is att.Attention
+        assert (get_context, set_context, reset_context, Context) == (ctx.get_context, ctx.set_context,
+                                                                      ctx.reset_context, ctx.Context)
+        assert dropin.paged_attention_decode_triton is att.paged_attention_decode
+        assert dropin.install() == []          # idempotent
+    finally:
+        dropin.uninstall()
+    assert "myvllm" not in sys.modules and "myvllm.layers.attention" not in sys.modules
