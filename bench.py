@@ -69,6 +69,9 @@ def parse_args():
     ap.add_argument("--kernel", default="auto", choices=["auto", "grid", "stream"],
                     help="tensor-core decode kernel: one CTA per chunk (grid), the persistent evenly cut "
                          "stream (stream), or the library's own choice (auto)")
+    ap.add_argument("--no-overlap", action="store_true",
+                    help="plain stream order between steps (default: MVL_DECODE_OVERLAP_PREV, a step's kernel "
+                         "starts up while the previous step's finishes, as between the layers of a decode step)")
     ap.add_argument("--sustain-s", type=float, default=2.0,
                     help="seconds of back-to-back steps for the 'sustained' sub-record (0 = skip)")
     ap.add_argument("--parity-seqs", type=int, default=4, help="sequences checked against the oracle after timing")
@@ -375,7 +378,8 @@ def run_ours(args, rank, world, local_rank):
     tma = ((_ext.DECODE_LOAD_TMA if args.tma else 0) | (_ext.DECODE_CUDA_CORES if args.cuda_cores else 0) |
            (_ext.DECODE_SHARE_PREFIX if share else 0) |
            (_ext.DECODE_SHARE_NARROW if args.share_prefix == "narrow" else 0) |
-           {"auto": 0, "grid": _ext.DECODE_SPLIT_GRID, "stream": _ext.DECODE_STREAM}[args.kernel])
+           {"auto": 0, "grid": _ext.DECODE_SPLIT_GRID, "stream": _ext.DECODE_STREAM}[args.kernel] |
+           (0 if args.no_overlap else _ext.DECODE_OVERLAP_PREV))
     if tma:
         from minivllm_b200.layers import attention as att_mod
         att_mod.DEFAULT_DECODE_FLAGS |= tma
@@ -532,7 +536,9 @@ def run_ours(args, rank, world, local_rank):
             e2e_ms = float(red[0])
         e2e = {"value": B / (e2e_ms * 1e-3), "unit": "tokens/s", "ms_per_step": e2e_ms, "steps": ke,
                "h2d_bytes_per_step": hs.h2d_bytes, "d2h_bytes_per_step": hs.d2h_bytes,
-               "api": "HostDecodeStep -> mvl_decode_step_host (per rank: its head shard)"}
+               "api": "HostDecodeStep -> mvl_decode_step_host (per rank: its head shard); k, v, slots, lengths and "
+                      "tables in one pinned H2D copy, q read and result rows written by the kernel across PCIe "
+                      "(device-mapped pinned memory), stream-synchronised every step"}
 
     if rank != 0:
         if world > 1:
@@ -578,6 +584,8 @@ def run_ours(args, rank, world, local_rank):
         "config": workload_config(args, t, world),
         "implementation": {"chunk_tokens": int(chunk), "gather": gather_kind, "prefix_sharing": bool(share),
                            "kv_load": "tensor-map TMA" if args.tma else "cp.async", "kernel": args.kernel,
+                           "launch": "plain stream order" if args.no_overlap else
+                           "programmatic dependent launch between steps (MVL_DECODE_OVERLAP_PREV)",
                            "math": "FFMA2 (CUDA cores)" if (args.cuda_cores or args.tma or sp.dtype == "f32")
                            else "mma.sync m16n8k16 (tensor cores)"},
         "hbm_gbs_step": alg_unique / (ms_step * 1e-3) / 1e9,

@@ -86,6 +86,17 @@ typedef enum mvl_dtype {
                                        kernel (measurement switch) */
 #define MVL_DECODE_SPLIT_GRID 128u /* 16-bit caches, chunk_tokens == 0: never use the persistent
                                        stream kernel (below), always one CTA per chunk */
+#define MVL_DECODE_OVERLAP_PREV 512u /* 16-bit caches: launch the decode kernel with a programmatic
+                                       dependency (PDL) on the kernel in front of it on the stream, so
+                                       that its start-up — context lengths, block tables, the first K/V
+                                       tiles — overlaps that kernel's tail; q, the new token's K/V and
+                                       every write wait for that kernel to complete.  A PROMISE by the
+                                       caller: the kernel in front writes no K/V-cache row this call
+                                       reads other than each sequence's newest token (context_lens - 1).
+                                       True between the layers of a decode step and between decode
+                                       steps (reference qwen3.py:104-111: norm, RoPE and the store of the
+                                       new token sit in front of attention); NOT true right behind a
+                                       store_kvcache of older rows, e.g. a prefill's. */
 #define MVL_DECODE_STREAM 256u     /* 16-bit caches, chunk_tokens == 0: always use the persistent
                                        stream kernel when its conditions hold.  Without either flag
                                        the library picks: with chunk_tokens == 0, FUSED_COMBINE set and
@@ -345,6 +356,11 @@ int mvl_decode_step_peers_sync(void* const* out_peers, void* const* sync_peers, 
                                float scale, int elem_dtype, void* workspace, size_t workspace_bytes,
                                int chunk_tokens, unsigned flags, void* stream);
 int mvl_peer_wait(void* sync_local, int num_peers, int64_t timeout_ms, void* stream);
+
+/* Diagnostics only (scripts/diag_stream_times.py): device buffer of 5 x uint64 per CTA into which the
+ * persistent stream kernel writes %globaltimer at entry / piece known / first tile landed / exit, and its %smid;
+ * NULL (the default) switches it off.  Process-wide, not thread-safe.  No reference counterpart. */
+void mvl_debug_set_times(void* buf);
 
 /*
  * mvl_decode_step_host — one decode-attention step of a layer driven from HOST buffers:

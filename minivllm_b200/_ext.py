@@ -20,7 +20,7 @@ F32, F16, BF16 = 0, 1, 2
 DECODE_SKIP_COMBINE, DECODE_ONLY_COMBINE, DECODE_FUSED_COMBINE, DECODE_LOAD_TMA, DECODE_CUDA_CORES = 1, 2, 4, 8, 16
 DECODE_SHARE_PREFIX = 32
 DECODE_SHARE_NARROW = 64
-DECODE_SPLIT_GRID, DECODE_STREAM = 128, 256
+DECODE_SPLIT_GRID, DECODE_STREAM, DECODE_OVERLAP_PREV = 128, 256, 512
 # flags of mvl_flash_prefill
 PREFILL_MMA_SYNC, PREFILL_ONE_TILE, PREFILL_PAIR = 1, 2, 4
 
@@ -51,6 +51,7 @@ PROTOTYPES = {
     "mvl_decode_step_peers_sync": (_i, [_vp, _vp, _i, _i, _i, _i] + [_vp] * 8 + [_i, _i64, _i64, _i64, _i64, _i64,
                                         _i, _i, _i, _i, _i64, _f, _i, _vp, _sz, _i, _u, _vp]),
     "mvl_allgather_heads": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _vp, _vp]),
+    "mvl_debug_set_times": (None, [_vp]),
     "mvl_peer_wait": (_i, [_vp, _i, _i64, _vp]),
     "mvl_decode_step_host": (_i, [_vp] * 16 + [_i, _i64, _i64, _i, _i, _i, _i, _i64, _f, _i, _vp,
                                                _sz, _i, _u, _vp]),

@@ -3,6 +3,7 @@
 // synchronisation, no host reads of device memory.
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -229,6 +230,8 @@ int pipe_for_current_device(HostPipe** out) {
   *out = &hp;
   return MVL_OK;
 }
+
+unsigned long long* g_dbg_times = nullptr;  // mvl_debug_set_times
 
 struct PeerSync {  // completion signal of the peer-store gather (peer_sync.cu)
   void* const* blocks;  // every rank's control block as mapped on this device
@@ -485,6 +488,8 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
   p.gp_shift = 3;  // 8 columns = 8 heads of one sequence unless prefix sharing packs several
   p.mm_narrow = 1;
   p.wide = 0;
+  p.overlap_prev = (flags & MVL_DECODE_OVERLAP_PREV) ? 1 : 0;
+  p.dbg_times = g_dbg_times;
   // Prefix sharing: tensor-core kernel, fewer than 8 heads per KV head (spare columns), more than
   // one sequence, and a workspace to hold the grouping.  Two tiny launches find the groups.
   if ((flags & MVL_DECODE_SHARE_PREFIX) && mma && need && batch > 1 && p.G <= 4 &&
@@ -642,6 +647,8 @@ int mvl_decode_step_peers_sync(void* const* out_peers, void* const* sync_peers, 
                      block_table_stride, num_heads, num_kv_heads, head_dim, block_size, num_blocks, scale,
                      elem_dtype, workspace, workspace_bytes, chunk_tokens, flags, stream, &ps);
 }
+
+void mvl_debug_set_times(void* buf) { g_dbg_times = static_cast<unsigned long long*>(buf); }
 
 int mvl_peer_wait(void* sync_local, int num_peers, int64_t timeout_ms, void* stream) {
   if (!sync_local) return MVL_ERR_NULL_POINTER;

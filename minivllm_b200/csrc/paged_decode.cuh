@@ -43,6 +43,13 @@ struct DecodeParams {
   // rank's control block (system-scope release), where mvl_peer_wait polls it.  Control block =
   // 16 x u32: [0..7] step counts announced by ranks 0..7, [8] this rank's own count, [9] CTA
   // arrival counter, [10] wait time-out marker.
+  // 1: the launch carries a programmatic dependency on the kernel in front of it (MVL_DECODE_OVERLAP_PREV):
+  // context lengths, block tables and K/V rows older than each sequence's newest token may be read
+  // before griddepcontrol.wait.  0: ordinary stream order.
+  int overlap_prev;
+  // Diagnostics (mvl_debug_set_times): per CTA of the stream kernel four %globaltimer stamps —
+  // kernel entry, piece known, first tile landed, exit — and the SM it ran on.  nullptr in normal use.
+  unsigned long long* dbg_times;
   unsigned* sync_local;     // this rank's control block; nullptr = no signalling
   unsigned* sync_peers[8];  // every rank's control block as mapped here (entry my_rank = sync_local)
   int my_rank;

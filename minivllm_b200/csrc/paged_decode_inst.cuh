@@ -8,6 +8,27 @@
 
 namespace mvl {
 
+// Launch with programmatic stream serialisation allowed: the kernel may start while its predecessor
+// on the stream finishes, and orders itself with griddepcontrol.wait.  Only for kernels that do.
+template <typename Kern, typename... Args>
+static int launch_pdl(bool pdl, Kern kern, dim3 grid, int block, size_t smem, cudaStream_t s, Args... args) {
+  if (!pdl) {
+    kern<<<grid, block, smem, s>>>(args...);
+    return (int)cudaGetLastError();
+  }
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return (int)cudaLaunchKernelEx(&cfg, kern, args...);
+}
+
 template <typename T, int D, int GT, bool UNIFORM, bool TMA>
 static int launch_split_u(const DecodeParams& p, const CUtensorMap* maps, dim3 grid, cudaStream_t s) {
   using C = DecodeCfg<T, D, GT>;
@@ -74,8 +95,7 @@ static int launch_mma_nt(const DecodeParams& p, dim3 grid, cudaStream_t s) {
     if (e != cudaSuccess) return (int)e;
     if (dev < 64) configured[dev] = true;
   }
-  kern<<<grid, C::NW * 32, C::SMEM, s>>>(p);
-  return (int)cudaGetLastError();
+  return launch_pdl(p.overlap_prev != 0, kern, grid, C::NW * 32, C::SMEM, s, p);
 }
 
 // One column tile (8 columns).  The kernel is written for NT column tiles; NT = 2 (16 columns, up
@@ -113,8 +133,7 @@ static int launch_stream_u(const DecodeParams& p, int batch, int ctas, cudaStrea
     if (e != cudaSuccess) return (int)e;
     if (dev < 64) configured[dev] = true;
   }
-  kern<<<dim3((unsigned)ctas), 128, S::SMEM, s>>>(p, batch);
-  return (int)cudaGetLastError();
+  return launch_pdl(p.overlap_prev != 0, kern, dim3((unsigned)ctas), 128, S::SMEM, s, p, batch);
 }
 
 template <>

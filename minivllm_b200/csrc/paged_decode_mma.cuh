@@ -139,9 +139,11 @@ __global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_k
   if (ctx_ll > p.max_ctx) ctx_ll = p.max_ctx;
   const int ctx = (int)ctx_ll;
   if (ctx <= 0) {
-    if (split == 0)
+    if (split == 0) {
+      griddep_wait();
       for (int i = threadIdx.x; i < g_valid * (D / 4); i += NW * 32)
         store_out4<T, D>(p, b, head0 + i / (D / 4), (i % (D / 4)) * 4, 0.f, 0.f, 0.f, 0.f);
+    }
     return;
   }
   const int start = split * p.chunk;
@@ -149,7 +151,16 @@ __global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_k
   const int end = min(ctx, start + p.chunk);
   const int n_act = (ctx + p.chunk - 1) / p.chunk;
 
-  if (p.k_new != nullptr && ctx - 1 >= start && ctx - 1 < end) {  // fused store (see paged_decode.cuh)
+  // Programmatic dependent launch: this grid may have been started while the kernel in front of it
+  // on the stream is still finishing.  What that kernel cannot have touched — context lengths, block
+  // tables and the K/V rows of tokens older than the step's new one — is fetched before
+  // griddep_wait(); everything it may have produced (q, the new token's K/V row, the prefix-sharing
+  // groups) and every global write comes after.
+  const bool holds_last = ctx - 1 >= start && ctx - 1 < end;
+  const bool prefetch_early = p.overlap_prev && p.share_meta == nullptr && !holds_last;
+  if (!prefetch_early) griddep_wait();
+
+  if (p.k_new != nullptr && holds_last) {  // fused store (see paged_decode.cuh)
     const long long slot = p.slot_is_i64 ? reinterpret_cast<const long long*>(p.slot_map)[b]
                                          : (long long)reinterpret_cast<const int*>(p.slot_map)[b];
     if (slot >= 0 && slot < p.num_slots) {
@@ -181,31 +192,6 @@ __global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_k
   const int gp_mask = (1 << p.gp_shift) - 1;
 
   const uint32_t ring = smem_u32(smem) + warp * C::WARP_SMEM;
-
-  // ---- q as B fragments of the score product: n = column nt*8+g = (member, head), k = d.
-  // Staged through shared memory: thread i copies 16-byte chunk i of the CTA's q rows (coalesced; also
-  // the only q traffic when q lives in host memory), then every lane picks its fragments from there.
-  const uint32_t qs = smem_u32(smem) + NW * C::WARP_SMEM;
-  for (int i = threadIdx.x; i < NC * CPRW; i += NW * 32) {
-    const int col = i / CPRW, c16 = i % CPRW;
-    const int cm = col >> p.gp_shift, chd = col & gp_mask;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (cm < nmem && chd < g_valid)
-      v = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(p.q) +
-                                          ((long long)(b + cm) * p.H + head0 + chd) * ROWB + c16 * 16);
-    sts128(qs + col * C::QROWB + c16 * 16, v);
-  }
-  __syncthreads();
-  uint32_t qb[NT][KS][2];
-#pragma unroll
-  for (int nt = 0; nt < NT; ++nt) {
-    const uint32_t qrow = qs + (nt * 8 + g) * C::QROWB + 4 * t;
-#pragma unroll
-    for (int ks = 0; ks < KS; ++ks) {
-      qb[nt][ks][0] = lds32(qrow + ks * 32);
-      qb[nt][ks][1] = lds32(qrow + ks * 32 + 16);
-    }
-  }
 
   // ---- this warp's tiles and the cp.async ring (same scheme as the FFMA2 kernel)
   const int ntiles = (end - start + TR - 1) / TR;
@@ -253,6 +239,32 @@ __global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_k
   };
 #pragma unroll 1
   for (int n = 0; n < RING - 1; ++n) issue(n, n);
+  if (prefetch_early) griddep_wait();
+
+  // ---- q as B fragments of the score product: n = column nt*8+g = (member, head), k = d.
+  // Staged through shared memory: thread i copies 16-byte chunk i of the CTA's q rows (coalesced; also
+  // the only q traffic when q lives in host memory), then every lane picks its fragments from there.
+  const uint32_t qs = smem_u32(smem) + NW * C::WARP_SMEM;
+  for (int i = threadIdx.x; i < NC * CPRW; i += NW * 32) {
+    const int col = i / CPRW, c16 = i % CPRW;
+    const int cm = col >> p.gp_shift, chd = col & gp_mask;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (cm < nmem && chd < g_valid)
+      v = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(p.q) +
+                                          ((long long)(b + cm) * p.H + head0 + chd) * ROWB + c16 * 16);
+    sts128(qs + col * C::QROWB + c16 * 16, v);
+  }
+  __syncthreads();
+  uint32_t qb[NT][KS][2];
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt) {
+    const uint32_t qrow = qs + (nt * 8 + g) * C::QROWB + 4 * t;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      qb[nt][ks][0] = lds32(qrow + ks * 32);
+      qb[nt][ks][1] = lds32(qrow + ks * 32 + 16);
+    }
+  }
 
   // ---- state per column tile: O^T accumulators (d x 8 columns), running max / sum of this thread's
   // two columns (2t, 2t+1), P^T B fragments

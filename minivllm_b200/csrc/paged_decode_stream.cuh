@@ -17,6 +17,14 @@
 // under way when its piece began and the one still under way when it ends) and the last to arrive
 // merges them in piece order — deterministic whatever the arrival order.
 //
+// What equal pieces cannot fix (measured, scripts/diag_stream_times.py): SMs do not stream at equal
+// speed.  On C3's 8-way shard the mean CTA time per SM ranges from 72 to 90 us, the same SMs fast and
+// slow in every run (a property of where an SM sits), so the median CTA is done at 87 us and the last
+// at ~100.  Handing the last quarter of the stream out dynamically (items claimed with an atomic
+// counter, halving in size) was built and measured: the fine items it needs near the end turn every
+// long sequence into dozens of partials whose merge sits on the critical path (0.11 -> 0.20 ms on that
+// shard), so the cut stays static.
+//
 // The piece boundaries come from the context lengths, which live on the device: every CTA scans them
 // itself at start (batch <= 1024 values from L2, ~1 us), so there is no pre-pass launch, no host
 // read-back, and the grid depends only on host-known sizes (graph-capturable like the split kernel).
@@ -55,6 +63,23 @@ __global__ void __launch_bounds__(128, 4) paged_decode_stream_mma_kernel(const D
   int* cum = reinterpret_cast<int*>(smem + C::SMEM);                 // cum[b] = rows of sequences < b
   int* misc = reinterpret_cast<int*>(smem + C::SMEM + S::CUM_BYTES);  // [0..3] warp totals, [8] flag
 
+  // Programmatic dependent launch (see paged_decode_mma.cuh): the scan of the context lengths and the
+  // search for this CTA's piece run while the kernel in front is still finishing.
+  griddep_launch_dependents();
+  auto stamp = [&](int which) {
+    if (p.dbg_times != nullptr && threadIdx.x == 0) {
+      unsigned long long tnow;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tnow));
+      p.dbg_times[(size_t)blockIdx.x * 5 + which] = tnow;
+      if (which == 0) {
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        p.dbg_times[(size_t)blockIdx.x * 5 + 4] = smid;
+      }
+    }
+  };
+  stamp(0);
+  bool first_tile_stamped = false;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t = lane & 3;
   const int X = p.KVH * p.n_gt;  // units per sequence
@@ -96,12 +121,6 @@ __global__ void __launch_bounds__(128, 4) paged_decode_stream_mma_kernel(const D
     if (threadIdx.x == NW * 32 - 1) cum[batch] = run;
     __syncthreads();
   }
-  // rows with no context: zeros (the split kernel's convention), spread over the CTAs
-  for (int b = blockIdx.x; b < batch; b += gridDim.x) {
-    if (cum[b + 1] == cum[b])
-      for (int i = threadIdx.x; i < p.H * (D / 4); i += NW * 32)
-        store_out4<T, D>(p, b, i / (D / 4), (i % (D / 4)) * 4, 0.f, 0.f, 0.f, 0.f);
-  }
 
   const long long total = (long long)cum[batch] * X;
   long long Tll = (total + gridDim.x - 1) / gridDim.x;
@@ -131,6 +150,15 @@ __global__ void __launch_bounds__(128, 4) paged_decode_stream_mma_kernel(const D
   const int k_tok = (mi & 1) * 8 + mr, k_chk = mi >> 1;
   const int v_tok = (mi >> 1) * 8 + mr, v_chk = mi & 1;
   const uint32_t k_off = k_tok * ROWB, v_off = v_tok * ROWB;
+
+  griddep_wait();
+  stamp(1);
+  // rows with no context: zeros (the split kernel's convention), spread over the CTAs
+  for (int bz = blockIdx.x; bz < batch; bz += gridDim.x) {
+    if (cum[bz + 1] == cum[bz])
+      for (int i = threadIdx.x; i < p.H * (D / 4); i += NW * 32)
+        store_out4<T, D>(p, bz, i / (D / 4), (i % (D / 4)) * 4, 0.f, 0.f, 0.f, 0.f);
+  }
 
   long long pos = piece0;
 #pragma unroll 1
@@ -250,6 +278,10 @@ __global__ void __launch_bounds__(128, 4) paged_decode_stream_mma_kernel(const D
     for (int n = 0; n < 2 * my_nt; ++n) {
       cp_async_wait<RING - 2>();
       __syncwarp();
+      if (!first_tile_stamped) {
+        stamp(2);
+        first_tile_stamped = true;
+      }
       issue(n + RING - 1, slot_c == 0 ? RING - 1 : slot_c - 1);
       const uint32_t tile = ring + slot_c * TILEB;
       slot_c = (slot_c + 1 == RING) ? 0 : slot_c + 1;
@@ -415,6 +447,7 @@ __global__ void __launch_bounds__(128, 4) paged_decode_stream_mma_kernel(const D
     }
   }
 
+  stamp(3);
   // ---- head sharding with peer stores: the launch's last CTA announces the step to every rank
   if (p.sync_local != nullptr) {
     __syncthreads();

@@ -28,6 +28,9 @@ __global__ void peer_signal_kernel(unsigned* local, unsigned* p0, unsigned* p1, 
 }
 
 __global__ void peer_wait_kernel(unsigned* local, int n, unsigned long long timeout_ns) {
+  // a decode kernel launched behind this wait with MVL_DECODE_OVERLAP_PREV may begin its start-up now;
+  // it orders itself behind this kernel's completion with griddepcontrol.wait
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int r = threadIdx.x;
   if (r < n) {
     const unsigned target = local[8];

@@ -23,6 +23,7 @@ from typing import Dict, List, NamedTuple, Optional, Sequence
 import numpy as np
 import torch
 
+from .. import _ext
 from ..layers.attention import Attention
 from ..utils.context import reset_context, set_context
 
@@ -130,6 +131,12 @@ class DecodeRunner:
                                     dtype=dtype, device=self.device)
         self.layers = torch.nn.ModuleList(
             Attention(num_heads, head_dim, 1.0, num_kv_heads, block_size) for _ in range(num_layers))
+        # A layer's decode kernel may start while the previous layer's is finishing: that kernel writes
+        # only ITS layer's cache and output (MVL_DECODE_OVERLAP_PREV).  Layer 0 keeps plain stream order,
+        # whatever ran in front of the step.
+        from ..layers import attention as _att
+        for layer in list(self.layers)[1:]:
+            layer.decode_flags = _att.DEFAULT_DECODE_FLAGS | _ext.DECODE_OVERLAP_PREV
         for i, layer in enumerate(self.layers):
             layer.k_cache, layer.v_cache = self.kv_cache[0, i], self.kv_cache[1, i]
         # Pinned host staging for the step's metadata: a small ring of sets, each guarded by an event

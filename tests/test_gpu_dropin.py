@@ -83,7 +83,7 @@ def test_reference_callers_run_on_the_mirror(cuda_device, reference, dtype):
     from minivllm_b200.layers.pre_attention import Qwen3AttentionCore
     from oracle import c_oracle
     ref, dev = reference, cuda_device
-    hidden, H, KVH, D, BS, NB = 512, 16, 8, 128, 16, 64      # the reference's Attention is built with BS 16
+    hidden, H, KVH, D, BS, NB = 2048, 16, 8, 128, 16, 64     # hidden = H * D (qwen3.py:38); the reference builds Attention with BS 16
     lens = [5, 17, 31, 33, 250, 129, 2, 63]                   # never a multiple of BS (SURVEY A-4)
     B = len(lens)
     old_disable = torch._dynamo.config.disable
