@@ -84,8 +84,15 @@ typedef enum mvl_dtype {
                                        there results agree with the unshared run to rounding. */
 #define MVL_DECODE_SHARE_NARROW 64u /* with SHARE_PREFIX: sub-groups of 8/G sequences only, no second
                                        kernel (measurement switch) */
-#define MVL_DECODE_SPLIT_GRID 128u /* 16-bit caches, chunk_tokens == 0: never use the persistent
-                                       stream kernel (below), always one CTA per chunk */
+#define MVL_DECODE_SPLIT_GRID 128u /* reserved (the chunk grid is the default); accepted and ignored */
+#define MVL_DECODE_STREAM 256u     /* 16-bit caches, chunk_tokens == 0, FUSED_COMBINE set, batch <= 1024:
+                                       run the persistent stream kernel — the launch's whole token stream
+                                       cut into equal pieces, one per resident CTA (4 x SMs) — instead of
+                                       one CTA per (sequence, kv head, chunk).  Same arithmetic; the split
+                                       points differ, so results agree to fp32 rounding.  Measured on B200
+                                       it wins only on one-kv-head shards of large batches (by 1-2 %), so
+                                       it is never chosen automatically.  Ignored where its conditions do
+                                       not hold. */
 #define MVL_DECODE_OVERLAP_PREV 512u /* 16-bit caches: launch the decode kernel with a programmatic
                                        dependency (PDL) on the kernel in front of it on the stream, so
                                        that its start-up — context lengths, block tables, the first K/V
@@ -97,14 +104,6 @@ typedef enum mvl_dtype {
                                        steps (reference qwen3.py:104-111: norm, RoPE and the store of the
                                        new token sit in front of attention); NOT true right behind a
                                        store_kvcache of older rows, e.g. a prefill's. */
-#define MVL_DECODE_STREAM 256u     /* 16-bit caches, chunk_tokens == 0: always use the persistent
-                                       stream kernel when its conditions hold.  Without either flag
-                                       the library picks: with chunk_tokens == 0, FUSED_COMBINE set and
-                                       batch <= 1024 it cuts the launch's whole token stream into equal
-                                       pieces, one per resident CTA (4 x SMs), when the chunk grid
-                                       would be too few waves to balance; otherwise one CTA per
-                                       (sequence, kv head, chunk).  Same arithmetic either way; the
-                                       split points differ, so results agree to fp32 rounding. */
 
 /* Library / ABI identification.  No reference counterpart (the reference has no native layer). */
 int mvl_abi_version(void);

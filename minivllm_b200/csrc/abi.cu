@@ -153,7 +153,6 @@ size_t plan_workspace(const Plan& pl, long long batch, int H, int D) {
 // The persistent stream kernel (paged_decode_stream.cuh): resident CTAs and workspace.  It is a
 // candidate only when the caller left the split size to the library (chunk_tokens == 0).
 constexpr int kStreamCtasPerSm = 4;
-constexpr double kStreamGridWaves = 6.0;  // chunk grids with fewer waves of resident CTAs than this go to the stream kernel
 bool stream_eligible(long long batch, int KVH, int n_gt, long long max_ctx, int dtype, int chunk_req) {
   if (chunk_req != 0 || elem_size(dtype) != 2 || batch < 1 || batch > mvl::kStreamBatchLimit) return false;
   const long long units = batch * KVH * n_gt;
@@ -424,9 +423,11 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
                  MVL_DECODE_ONLY_COMBINE)) &&
       stream_eligible(batch, num_kv_heads, pl.n_gt, pl.max_ctx, elem_dtype, chunk_tokens) && workspace &&
       aligned16(workspace) && workspace_bytes >= stream_workspace(batch, head_dim, sms)) {
-    // The chunk grid balances itself once it has many waves of CTAs; below that the equal pieces win.
-    const double grid_ctas = (double)batch * num_kv_heads * pl.n_gt * (double)pl.max_splits;
-    use_stream = (flags & MVL_DECODE_STREAM) || grid_ctas < kStreamGridWaves * kStreamCtasPerSm * sms;
+    // Measured on B200 (profiles/r02_sweep_stream_vs_grid.jsonl, r02_sweep_small.jsonl): the chunk grid is
+    // as fast or faster on every shape but the one-kv-head shard of a large batch (1-2 % there), because
+    // SMs stream at unequal, position-dependent speeds and the hardware's CTA scheduler evens that out
+    // where equal fixed pieces cannot.  So the stream kernel runs only when asked for.
+    use_stream = (flags & MVL_DECODE_STREAM) != 0;
   }
 
   mvl::DecodeParams p;
@@ -509,16 +510,18 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
     p.share_meta = meta;
   }
 
+  bool signalled_in_kernel = false;
+  auto set_sync = [&]() {
+    for (int r = 0; r < n_out; ++r) p.sync_peers[r] = static_cast<unsigned*>(sync->blocks[r]);
+    p.sync_local = p.sync_peers[sync->my_rank];
+    p.my_rank = sync->my_rank;
+  };
   if (use_stream) {
     // no more CTAs than 64-token rows the launch can possibly hold
     long long ctas = (long long)kStreamCtasPerSm * sms;
     const long long max_rows = batch * num_kv_heads * pl.n_gt * ((pl.max_ctx + 63) / 64);
     if (ctas > max_rows) ctas = max_rows;
-    if (sync) {  // signalled from the kernel's own epilogue
-      for (int r = 0; r < n_out; ++r) p.sync_peers[r] = static_cast<unsigned*>(sync->blocks[r]);
-      p.sync_local = p.sync_peers[sync->my_rank];
-      p.my_rank = sync->my_rank;
-    }
+    if (sync) set_sync();  // signalled from the kernel's own epilogue
     const int e = elem_dtype == MVL_DTYPE_F16
                       ? mvl::launch_decode_stream_mma<__half>(p, head_dim, (int)batch, (int)ctas, s)
                       : mvl::launch_decode_stream_mma<__nv_bfloat16>(p, head_dim, (int)batch, (int)ctas, s);
@@ -537,6 +540,10 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
         use_maps = maps;
     }
     int e = -1000;
+    // the tensor-core split kernel announces the step itself when no later kernel writes result rows
+    signalled_in_kernel = sync && mma && p.share_meta == nullptr && !(flags & MVL_DECODE_SKIP_COMBINE) &&
+                          (pl.max_splits <= 1 || p.counters != nullptr);
+    if (signalled_in_kernel) set_sync();
     if (mma) {
       e = elem_dtype == MVL_DTYPE_F16 ? mvl::launch_decode_split_mma<__half>(p, head_dim, grid, s)
                                       : mvl::launch_decode_split_mma<__nv_bfloat16>(p, head_dim, grid, s);
@@ -568,7 +575,7 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
     if (e == -1000) return MVL_ERR_SHAPE;
     if (e != 0) return cuda_fail((cudaError_t)e, "paged_decode_combine launch");
   }
-  return signal_after();  // kernels other than the stream kernel: one-thread signal launch behind them
+  return signalled_in_kernel ? MVL_OK : signal_after();  // else: one-warp signal launch behind the kernels
 }
 
 int mvl_paged_decode(void* out, const void* query, const void* k_cache, const void* v_cache,

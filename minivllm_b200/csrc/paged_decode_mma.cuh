@@ -115,7 +115,7 @@ struct MmaCfg {
 };
 
 template <typename T, int D, bool UNIFORM, int NT>
-__global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_kernel(const DecodeParams p) {
+__device__ __forceinline__ void paged_decode_split_mma_body(const DecodeParams& p) {
   using C = MmaCfg<T, D, NT>;
   constexpr int NC = C::NC;
   using M = MmaType<T>;
@@ -490,6 +490,27 @@ __global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_k
     }
     const float inv = 1.f / Lsum;
     store_out4<T, D>(p, b + cm, head0 + hd, dq * 4, a0 * inv, a1 * inv, a2 * inv, a3 * inv);
+  }
+}
+
+template <typename T, int D, bool UNIFORM, int NT>
+__global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_kernel(const DecodeParams p) {
+  paged_decode_split_mma_body<T, D, UNIFORM, NT>(p);  // every exit from it is CTA-uniform
+  // ---- head sharding with peer stores (peer_sync.cu): the last CTA of the whole grid to get here —
+  // CTAs whose chunk lies past their sequence's end included — announces the step to every rank
+  if (p.sync_local != nullptr) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();  // this CTA's rows (peer stores included) before its arrival
+      if (atomicAdd(p.sync_local + 9, 1u) == gridDim.x * gridDim.y * gridDim.z - 1u) {
+        p.sync_local[9] = 0u;
+        const unsigned step = p.sync_local[8] + 1u;
+        p.sync_local[8] = step;
+        __threadfence_system();
+        for (int r = 0; r < p.n_out; ++r)
+          asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p.sync_peers[r] + p.my_rank), "r"(step) : "memory");
+      }
+    }
   }
 }
 

@@ -457,9 +457,9 @@ __global__ void __launch_bounds__(128, 4) paged_decode_stream_mma_kernel(const D
         p.sync_local[9] = 0u;
         const unsigned step = p.sync_local[8] + 1u;
         p.sync_local[8] = step;
-        __threadfence_system();
+        __threadfence_system();  // one fence, then the announcements as relaxed stores (no round trip each)
         for (int r = 0; r < p.n_out; ++r)
-          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.sync_peers[r] + p.my_rank), "r"(step) : "memory");
+          asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p.sync_peers[r] + p.my_rank), "r"(step) : "memory");
       }
     }
   }

@@ -14,7 +14,11 @@ from minivllm_b200.layers.attention import decode_step  # noqa: E402
 
 dev = torch.device("cuda", 0)
 H, KVH, D, BS = 32, 8, 128, 16
-chunks = [int(c) for c in sys.argv[1:]] or [0]
+# arguments: split sizes (0 = the library's choice), or "grid" / "stream" / "pdl" to force the chunk grid, the
+# persistent stream kernel, or to add MVL_DECODE_OVERLAP_PREV, with the library's split size
+chunks = [c if c in ("grid", "stream", "pdl") else int(c) for c in sys.argv[1:]] or [0]
+FL = {"grid": _ext.DECODE_FUSED_COMBINE | _ext.DECODE_SPLIT_GRID, "stream": _ext.DECODE_FUSED_COMBINE | _ext.DECODE_STREAM,
+      "pdl": _ext.DECODE_FUSED_COMBINE | _ext.DECODE_OVERLAP_PREV}
 for B in (1, 4, 16, 64):
     for ctx in (512, 4096, 16384, 65536):
         if B * ctx > 2 ** 21:
@@ -32,8 +36,9 @@ for B in (1, 4, 16, 64):
         nbytes = B * ctx * KVH * D * 2 * 2 + 2 * B * H * D * 2
         row = {"B": B, "ctx": ctx, "MB": round(nbytes / 1e6, 1)}
         for chunk in chunks:
-            call = lambda: decode_step(q, k, v, kc, vc, slots, tables, cl, D ** -0.5, H, KVH, D, BS,
-                                       out=out, chunk_tokens=chunk)
+            named = isinstance(chunk, str)
+            call = lambda: decode_step(q, k, v, kc, vc, slots, tables, cl, D ** -0.5, H, KVH, D, BS, out=out,
+                                       chunk_tokens=0 if named else chunk, flags=FL[chunk] if named else None)
             for _ in range(3):
                 call()
             torch.cuda.synchronize()
@@ -50,6 +55,6 @@ for B in (1, 4, 16, 64):
             e1.record()
             torch.cuda.synchronize()
             us = e0.elapsed_time(e1) * 1000 / 200
-            used = chunk or _ext.lib().mvl_paged_decode_default_chunk(B, H, KVH, D, nblk, BS, 2)
-            row[f"chunk{used}"] = f"{us:.1f}us {nbytes / us / 1e3:.0f}GB/s"
+            used = chunk if named else (chunk or "auto")
+            row[f"{used}"] = f"{us:.1f}us {nbytes / us / 1e3:.0f}GB/s"
         print(json.dumps(row))
