@@ -47,7 +47,7 @@ def parse_args():
                     help="c1..c5: one attention call per step; c2e: 28-layer engine-shaped decode "
                          "loop of config 2 under CUDA-graph replay")
     ap.add_argument("--eager", action="store_true", help="c2e: no CUDA graphs")
-    ap.add_argument("--share-prefix", choices=["auto", "on", "off", "narrow"], default="auto",
+    ap.add_argument("--share-prefix", choices=["auto", "on", "off", "narrow", "mma"], default="auto",
                     help="score sequences with aliased block-table prefixes together "
                          "(MVL_DECODE_SHARE_PREFIX); auto = on for the shared-prefix workload c5")
     ap.add_argument("--cuda-cores", action="store_true",
@@ -376,11 +376,12 @@ def run_ours(args, rank, world, local_rank):
     lib = _ext.lib()
     # auto: on for the shared-prefix workload on one GPU with all its kv heads; on a one-kv-head shard the
     # grouped kernels measured slower than scoring each sequence alone (N = 8: 0.233 vs 0.127 ms)
-    share = args.share_prefix in ("on", "narrow") or (args.share_prefix == "auto" and args.workload == "c5"
+    share = args.share_prefix in ("on", "narrow", "mma") or (args.share_prefix == "auto" and args.workload == "c5"
                                                       and world == 1 and args.shard_of == 1)
     tma = ((_ext.DECODE_LOAD_TMA if args.tma else 0) | (_ext.DECODE_CUDA_CORES if args.cuda_cores else 0) |
            (_ext.DECODE_SHARE_PREFIX if share else 0) |
            (_ext.DECODE_SHARE_NARROW if args.share_prefix == "narrow" else 0) |
+           (_ext.DECODE_GROUP_MMA if args.share_prefix == "mma" else 0) |
            {"auto": 0, "grid": _ext.DECODE_SPLIT_GRID, "stream": _ext.DECODE_STREAM}[args.kernel] |
            (0 if args.no_overlap else _ext.DECODE_OVERLAP_PREV))
     if tma:

@@ -84,6 +84,9 @@ typedef enum mvl_dtype {
                                        there results agree with the unshared run to rounding. */
 #define MVL_DECODE_SHARE_NARROW 64u /* with SHARE_PREFIX: sub-groups of 8/G sequences only, no second
                                        kernel (measurement switch) */
+#define MVL_DECODE_GROUP_MMA 1024u /* with SHARE_PREFIX (wide form): keep the shared chunks of large
+                                       sub-groups on the mma.sync group kernel instead of the tcgen05 one
+                                       (measurement switch) */
 #define MVL_DECODE_SPLIT_GRID 128u /* reserved (the chunk grid is the default); accepted and ignored */
 #define MVL_DECODE_STREAM 256u     /* 16-bit caches, chunk_tokens == 0, FUSED_COMBINE set, batch <= 1024:
                                        run the persistent stream kernel — the launch's whole token stream

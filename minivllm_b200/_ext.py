@@ -20,7 +20,7 @@ F32, F16, BF16 = 0, 1, 2
 DECODE_SKIP_COMBINE, DECODE_ONLY_COMBINE, DECODE_FUSED_COMBINE, DECODE_LOAD_TMA, DECODE_CUDA_CORES = 1, 2, 4, 8, 16
 DECODE_SHARE_PREFIX = 32
 DECODE_SHARE_NARROW = 64
-DECODE_SPLIT_GRID, DECODE_STREAM, DECODE_OVERLAP_PREV = 128, 256, 512
+DECODE_SPLIT_GRID, DECODE_STREAM, DECODE_OVERLAP_PREV, DECODE_GROUP_MMA = 128, 256, 512, 1024
 # flags of mvl_flash_prefill
 PREFILL_MMA_SYNC, PREFILL_ONE_TILE, PREFILL_PAIR = 1, 2, 4
 

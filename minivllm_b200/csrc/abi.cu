@@ -142,7 +142,8 @@ int make_plan(long long batch, int H, int KVH, int D, long long max_num_blocks, 
 // partials, whatever the shapes: it only ever holds counters, which every call leaves at zero.
 constexpr size_t kCounterBytes = 256u << 10;  // 65536 counters
 
-size_t share_meta_bytes(long long batch) { return (((size_t)batch * 16 + 255) / 256) * 256; }
+// leader | gsize | gshare | lcpt | work-list leaders | work-list chunk offsets (batch ints each) + 2 counts
+size_t share_meta_bytes(long long batch) { return (((size_t)batch * 24 + 8 + 255) / 256) * 256; }
 
 size_t plan_workspace(const Plan& pl, long long batch, int H, int D) {
   if (pl.max_splits <= 1) return 0;
@@ -260,6 +261,22 @@ int make_packed_map(CUtensorMap* map, const void* base, int dtype, int D, int he
   const cuuint32_t box[3] = {64u, 1u, (cuuint32_t)box_rows};
   const cuuint32_t estr[3] = {1u, 1u, 1u};
   return (int)enc(map, dt, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+}
+// Tensor map over q (batch, heads, D) whose box is one sub-group's rows for one kv head: 64 elements x
+// `box_heads` consecutive heads x `box_seqs` consecutive sequences (row = sequence-major, head-minor).
+int make_group_q_map(CUtensorMap* map, const void* q, int dtype, int D, int heads, long long batch, int box_heads,
+                     int box_seqs) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc) return -1;
+  const CUtensorMapDataType dt =
+      dtype == MVL_DTYPE_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  const cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)heads, (cuuint64_t)batch};
+  const cuuint64_t strides[2] = {(cuuint64_t)D * 2, (cuuint64_t)heads * D * 2};
+  const cuuint32_t box[3] = {64u, (cuuint32_t)box_heads, (cuuint32_t)box_seqs};
+  const cuuint32_t estr[3] = {1u, 1u, 1u};
+  return (int)enc(map, dt, 3, const_cast<void*>(q), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 }
@@ -505,7 +522,7 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
     int* meta = reinterpret_cast<int*>(reinterpret_cast<char*>(workspace) + kCounterBytes);
     const int e = mvl::launch_prefix_share(block_tables, block_table_stride, context_lens, p.ctx_is_i64,
                                            batch, pl.max_ctx, pl.bs_shift, pl.chunk,
-                                           p.wide ? 4 * p.mm_narrow : p.mm_narrow, meta, s);
+                                           p.wide ? 4 * p.mm_narrow : p.mm_narrow, p.mm_narrow, meta, s);
     if (e != 0) return cuda_fail((cudaError_t)e, "prefix_share launch");
     p.share_meta = meta;
   }
@@ -540,6 +557,21 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
         use_maps = maps;
     }
     int e = -1000;
+    // Prefix sharing, wide form: the shared chunks of large sub-groups go to the tcgen05 group kernel (one
+    // CTA per SM, persistent) where its tiling holds — 128-token tiles inside chunks, whole 16-token pieces
+    // inside pages — else to the mma.sync one.  The tcgen05 kernel is launched FIRST and the split kernel
+    // as its programmatic dependent: its big uniform CTAs start on every SM at once, and the split kernel's
+    // many small ones fill each SM as a group CTA leaves it (launched behind the split kernel it started
+    // SM by SM over 80 us and ended a third round nearly alone: 0.396 ms on C5 instead of what is measured now).
+    const bool group_wide = mma && p.share_meta != nullptr && p.wide;
+    const bool group_tc5 = group_wide && !(flags & MVL_DECODE_GROUP_MMA) && pl.chunk % 128 == 0 &&
+                           block_size % 16 == 0 && num_blocks * (long long)block_size < (1ll << 31) && n_out == 1;
+    if (group_tc5) {
+      e = mvl::launch_decode_group_tc5(p, head_dim, batch, block_size, num_blocks, sms, elem_dtype, s);
+      if (e == -1000) return MVL_ERR_SHAPE;
+      if (e != 0) return e;  // text recorded by the launcher
+      p.beside_group = 1;
+    }
     // the tensor-core split kernel announces the step itself when no later kernel writes result rows
     signalled_in_kernel = sync && mma && p.share_meta == nullptr && !(flags & MVL_DECODE_SKIP_COMBINE) &&
                           (pl.max_splits <= 1 || p.counters != nullptr);
@@ -557,7 +589,7 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
     }
     if (e == -1000) return MVL_ERR_SHAPE;
     if (e != 0) return cuda_fail((cudaError_t)e, "paged_decode_split launch");
-    if (mma && p.share_meta != nullptr && p.wide) {
+    if (group_wide && !group_tc5) {
       e = elem_dtype == MVL_DTYPE_F16 ? mvl::launch_decode_group_mma<__half>(p, head_dim, grid, s)
                                       : mvl::launch_decode_group_mma<__nv_bfloat16>(p, head_dim, grid, s);
       if (e == -1000) return MVL_ERR_SHAPE;

@@ -12,9 +12,16 @@ int launch_store_kvcache(const void* key, const void* value, void* k_cache, void
                          long long num_slots, int num_sms, cudaStream_t stream);
 
 // Prefix-sharing pre-pass (prefix_share.cu): fills meta[4*batch] = leader | gsize | gshare | lcpt.
+// meta[6 * batch + 2] = leader | gsize | gshare | lcpt | wl_b | wl_cum | (wl_n, wl_total): the last three
+// list the sub-groups of more than `mm_narrow` members with their shared whole chunks (work list of the
+// tcgen05 group kernel).
 int launch_prefix_share(const int32_t* bt, long long bt_stride, const void* ctx, int ctx_is_i64,
-                        long long batch, long long max_ctx, int bs_shift, int chunk, int mm, int* meta,
-                        cudaStream_t s);
+                        long long batch, long long max_ctx, int bs_shift, int chunk, int mm, int mm_narrow,
+                        int* meta, cudaStream_t s);
+// Prefix sharing, wide form on tcgen05 (paged_decode_group_tc5.cu): persistent, one CTA per SM, launched
+// behind the split kernel as its programmatic dependent.  Returns 0, -1000, or an mvl_status (text recorded).
+int launch_decode_group_tc5(const DecodeParams& p, int head_dim, long long batch, int block_size,
+                            long long num_blocks, int num_sms, int dtype, cudaStream_t s);
 
 // abi.cu: record an error text for mvl_last_cuda_error() and return MVL_ERR_CUDA.
 int fail_text(const char* where, int code);

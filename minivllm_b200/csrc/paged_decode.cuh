@@ -47,6 +47,11 @@ struct DecodeParams {
   // context lengths, block tables and K/V rows older than each sequence's newest token may be read
   // before griddepcontrol.wait.  0: ordinary stream order.
   int overlap_prev;
+  // 1: the tcgen05 group kernel (prefix sharing, wide form) was launched in FRONT of this split kernel and
+  // this launch is its programmatic dependent: the two touch disjoint chunks, so the split kernel's CTAs
+  // start wherever a group CTA has left an SM, do not wait at entry, and wait for that grid's completion
+  // only before they exit (so that this kernel's completion implies that one's).
+  int beside_group;
   // Diagnostics (mvl_debug_set_times): per CTA of the stream kernel four %globaltimer stamps —
   // kernel entry, piece known, first tile landed, exit — and the SM it ran on.  nullptr in normal use.
   unsigned long long* dbg_times;

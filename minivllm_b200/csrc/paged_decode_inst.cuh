@@ -95,7 +95,7 @@ static int launch_mma_nt(const DecodeParams& p, dim3 grid, cudaStream_t s) {
     if (e != cudaSuccess) return (int)e;
     if (dev < 64) configured[dev] = true;
   }
-  return launch_pdl(p.overlap_prev != 0, kern, grid, C::NW * 32, C::SMEM, s, p);
+  return launch_pdl(p.overlap_prev != 0 || p.beside_group != 0, kern, grid, C::NW * 32, C::SMEM, s, p);
 }
 
 // One column tile (8 columns).  The kernel is written for NT column tiles; NT = 2 (16 columns, up

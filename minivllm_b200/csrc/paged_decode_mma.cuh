@@ -140,7 +140,7 @@ __device__ __forceinline__ void paged_decode_split_mma_body(const DecodeParams& 
   const int ctx = (int)ctx_ll;
   if (ctx <= 0) {
     if (split == 0) {
-      griddep_wait();
+      if (!p.beside_group) griddep_wait();
       for (int i = threadIdx.x; i < g_valid * (D / 4); i += NW * 32)
         store_out4<T, D>(p, b, head0 + i / (D / 4), (i % (D / 4)) * 4, 0.f, 0.f, 0.f, 0.f);
     }
@@ -158,7 +158,7 @@ __device__ __forceinline__ void paged_decode_split_mma_body(const DecodeParams& 
   // groups) and every global write comes after.
   const bool holds_last = ctx - 1 >= start && ctx - 1 < end;
   const bool prefetch_early = p.overlap_prev && p.share_meta == nullptr && !holds_last;
-  if (!prefetch_early) griddep_wait();
+  if (!prefetch_early && !p.beside_group) griddep_wait();
 
   if (p.k_new != nullptr && holds_last) {  // fused store (see paged_decode.cuh)
     const long long slot = p.slot_is_i64 ? reinterpret_cast<const long long*>(p.slot_map)[b]
@@ -509,6 +509,11 @@ __device__ __forceinline__ void paged_decode_split_mma_body(const DecodeParams& 
 template <typename T, int D, bool UNIFORM, int NT>
 __global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_kernel(const DecodeParams p) {
   paged_decode_split_mma_body<T, D, UNIFORM, NT>(p);  // every exit from it is CTA-uniform
+  // Beside the group kernel: this grid's completion must imply that grid's, and ONE CTA waiting for it is
+  // enough for that (the last in launch order).  If every CTA waited, the thousands that have nothing to do
+  // would sit in all the slots the group CTAs free and keep the working ones out until that grid is done.
+  if (p.beside_group && blockIdx.x == gridDim.x - 1 && blockIdx.y == gridDim.y - 1 && blockIdx.z == gridDim.z - 1)
+    griddep_wait();
   // ---- head sharding with peer stores (peer_sync.cu): the last CTA of the whole grid to get here —
   // CTAs whose chunk lies past their sequence's end included — announces the step to every rank
   if (p.sync_local != nullptr) {

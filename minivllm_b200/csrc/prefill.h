@@ -32,6 +32,10 @@ struct PrefillParams {
 int make_packed_map(CUtensorMap* map, const void* base, int dtype, int D, int heads, long long tokens,
                      long long token_stride, int box_rows);
 
+// Tensor map over q (batch, heads, D): box = 64 elements x box_heads heads x box_seqs sequences.
+int make_group_q_map(CUtensorMap* map, const void* q, int dtype, int D, int heads, long long batch, int box_heads,
+                     int box_seqs);
+
 // Record a failure for mvl_last_cuda_error() and return MVL_ERR_CUDA (abi.cu).
 int fail_text(const char* where, int code);
 int fail_cuda(int cuda_error, const char* where);
