@@ -374,10 +374,9 @@ def run_ours(args, rank, world, local_rank):
     dec_args = (w["k_cache"], w["v_cache"], w["block_tables"], w["context_lens"], w["scale"], w["H"],
                 w["KVH"], w["D"], w["BS"])
     lib = _ext.lib()
-    # auto: on for the shared-prefix workload on one GPU with all its kv heads; on a one-kv-head shard the
-    # grouped kernels measured slower than scoring each sequence alone (N = 8: 0.233 vs 0.127 ms)
-    share = args.share_prefix in ("on", "narrow", "mma") or (args.share_prefix == "auto" and args.workload == "c5"
-                                                      and world == 1 and args.shard_of == 1)
+    # auto: on for the shared-prefix workload (also on head shards: with the tcgen05 group kernel a one-kv-head
+    # shard of C5 runs 0.104 ms shared against 0.127 ms unshared; the mma.sync group kernel lost there, 0.181)
+    share = args.share_prefix in ("on", "narrow", "mma") or (args.share_prefix == "auto" and args.workload == "c5")
     tma = ((_ext.DECODE_LOAD_TMA if args.tma else 0) | (_ext.DECODE_CUDA_CORES if args.cuda_cores else 0) |
            (_ext.DECODE_SHARE_PREFIX if share else 0) |
            (_ext.DECODE_SHARE_NARROW if args.share_prefix == "narrow" else 0) |

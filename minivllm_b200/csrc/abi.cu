@@ -565,7 +565,7 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
     // SM by SM over 80 us and ended a third round nearly alone: 0.396 ms on C5 instead of what is measured now).
     const bool group_wide = mma && p.share_meta != nullptr && p.wide;
     const bool group_tc5 = group_wide && !(flags & MVL_DECODE_GROUP_MMA) && pl.chunk % 128 == 0 &&
-                           block_size % 16 == 0 && num_blocks * (long long)block_size < (1ll << 31) && n_out == 1;
+                           block_size % 16 == 0 && num_blocks * (long long)block_size < (1ll << 31);
     if (group_tc5) {
       e = mvl::launch_decode_group_tc5(p, head_dim, batch, block_size, num_blocks, sms, elem_dtype, s);
       if (e == -1000) return MVL_ERR_SHAPE;
