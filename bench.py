@@ -548,6 +548,13 @@ def run_ours(args, rank, world, local_rank):
                       "tables in one pinned H2D copy, q read and result rows written by the kernel across PCIe "
                       "(device-mapped pinned memory), stream-synchronised every step"}
 
+    # a peer wait that gave up (a lost announcement) would show as a multi-second step: say so explicitly
+    wait_timeouts = None
+    if fused is not None:
+        red = torch.tensor([float(fused.timed_out())], device=dev, dtype=torch.float64)
+        dist.all_reduce(red, op=dist.ReduceOp.MAX)
+        wait_timeouts = int(red[0])
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -593,6 +600,7 @@ def run_ours(args, rank, world, local_rank):
         "config": workload_config(args, t, world),
         "implementation": {"chunk_tokens": int(chunk), "gather": gather_kind, "prefix_sharing": bool(share),
                            "kv_load": "tensor-map TMA" if args.tma else "cp.async", "kernel": args.kernel,
+                           "peer_wait_gave_up_on_rank_plus_1": wait_timeouts,
                            "launch": "plain stream order" if args.no_overlap else
                            "programmatic dependent launch between steps (MVL_DECODE_OVERLAP_PREV)",
                            "math": "FFMA2 (CUDA cores)" if (args.cuda_cores or args.tma or sp.dtype == "f32")

@@ -517,6 +517,11 @@ __global__ void __launch_bounds__(128, NT == 1 ? 4 : 2) paged_decode_split_mma_k
   // ---- head sharding with peer stores (peer_sync.cu): the last CTA of the whole grid to get here —
   // CTAs whose chunk lies past their sequence's end included — announces the step to every rank
   if (p.sync_local != nullptr) {
+    // A CTA that had nothing to do never reached the body's griddepcontrol.wait; with a programmatic
+    // dependency it may be running while the PREVIOUS launch of this kernel is still counting arrivals on
+    // the same counter (seen at N = 8: a step announced early, the next one never, every rank in its
+    // time-out).  No arrival before the kernel in front has completed.
+    griddep_wait();
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence_system();  // this CTA's rows (peer stores included) before its arrival
