@@ -723,18 +723,20 @@ int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_h
   const size_t tb = (size_t)batch * max_num_blocks * sizeof(int32_t);
   cudaError_t e;
   // Zero-copy options: a device-side pointer equal to its host-side pointer means "this array stays in
-  // (pinned, device-mapped) host memory": the kernels read q from it / write the result rows into it
-  // across PCIe themselves, as they go, and no separate copy is enqueued for it.
+  // (pinned, device-mapped) host memory": the kernels read q and the new token's k / v rows from it and
+  // write the result rows into it across PCIe themselves, as they go, and no separate copy is enqueued
+  // for it.  Slots, lengths and block tables are always copied (the kernels read them many times).
   const bool q_direct = q_dev == q_host, out_direct = out_dev == out_host;
-  // When the caller laid the six input arrays out back to back (same order, host and device), the
-  // step's inputs travel in ONE copy instead of six.
+  const bool kv_direct = k_dev == k_host && v_dev == v_host;  // the new token's rows: read once by the fused store
+  // When the caller laid the input arrays out back to back (same order, host and device), what has to
+  // travel goes in ONE copy instead of up to six.
   auto after = [](const void* p, size_t n) { return static_cast<const char*>(p) + n; };
-  const bool tail_packed =
-      after(k_host, kb) == v_host && after(v_host, kb) == slot_mapping_host &&
+  const bool meta_packed =
       after(slot_mapping_host, ib) == context_lens_host && after(context_lens_host, ib) == (const void*)block_tables_host &&
-      after(k_dev, kb) == v_dev && after(v_dev, kb) == slot_mapping_dev &&
       after(slot_mapping_dev, ib) == context_lens_dev && after(context_lens_dev, ib) == (const void*)block_tables_dev;
-  const bool packed = !q_direct && tail_packed && after(q_host, qb) == k_host && after(q_dev, qb) == k_dev;
+  const bool kv_packed = !kv_direct && meta_packed && after(k_host, kb) == v_host && after(v_host, kb) == slot_mapping_host &&
+                         after(k_dev, kb) == v_dev && after(v_dev, kb) == slot_mapping_dev;
+  const bool packed = !q_direct && kv_packed && after(q_host, qb) == k_host && after(q_dev, qb) == k_dev;
 #define MVL_H2D(dst, src, n)                                          \
   e = cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, s);        \
   if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync H2D " #dst)
@@ -742,14 +744,20 @@ int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_h
     MVL_H2D(q_dev, q_host, qb + 2 * kb + 2 * ib + tb);
   } else {
     if (!q_direct) { MVL_H2D(q_dev, q_host, qb); }
-    if (tail_packed) {
+    if (kv_packed) {
       MVL_H2D(k_dev, k_host, 2 * kb + 2 * ib + tb);
     } else {
-      MVL_H2D(k_dev, k_host, kb);
-      MVL_H2D(v_dev, v_host, kb);
-      MVL_H2D(slot_mapping_dev, slot_mapping_host, ib);
-      MVL_H2D(context_lens_dev, context_lens_host, ib);
-      MVL_H2D(block_tables_dev, block_tables_host, tb);
+      if (!kv_direct) {
+        MVL_H2D(k_dev, k_host, kb);
+        MVL_H2D(v_dev, v_host, kb);
+      }
+      if (meta_packed) {
+        MVL_H2D(slot_mapping_dev, slot_mapping_host, 2 * ib + tb);
+      } else {
+        MVL_H2D(slot_mapping_dev, slot_mapping_host, ib);
+        MVL_H2D(context_lens_dev, context_lens_host, ib);
+        MVL_H2D(block_tables_dev, block_tables_host, tb);
+      }
     }
   }
 #undef MVL_H2D

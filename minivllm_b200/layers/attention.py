@@ -475,10 +475,11 @@ class HostDecodeStep:
     def __init__(self, k_cache: torch.Tensor, v_cache: torch.Tensor, batch: int, max_num_blocks: int,
                  num_heads: int, scale: float, index_dtype: torch.dtype = torch.int64,
                  chunk_tokens: int = 0, flags: int = 0, pieces: Optional[int] = None,
-                 direct_out: bool = True, direct_q: bool = True):
+                 direct_out: bool = True, direct_q: bool = True, direct_kv: bool = True):
         """``direct_out`` / ``direct_q`` (serial form only; default on): the kernels write the result rows
         straight into the pinned host buffer / read q straight from it over PCIe as they go, instead of
         a separate copy before and after (C3 on B200: 0.856 -> 0.766 ms per step; same bits).
+        ``direct_kv``: the new token's k / v rows likewise (read once, by the fused store).
         ``pieces``: how many runs of consecutive sequences the step is cut into so that the copies
         of one run travel while another computes (``mvl_decode_step_host_overlapped``); 1 = the strictly
         serial ``mvl_decode_step_host`` (the default: measured on B200 the smaller launches lose what the overlap gains)."""
@@ -519,7 +520,7 @@ class HostDecodeStep:
         self.q_d, self.k_d, self.v_d, self.slot_d, self.ctx_d, self.bt_d = views(self._d_arena)
         self.out_h = torch.empty((batch, num_heads, self.head_dim), dtype=dt, pin_memory=True)
         self.out_d = torch.empty((batch, num_heads, self.head_dim), dtype=dt, device=dev)
-        self.direct_out, self.direct_q = bool(direct_out), bool(direct_q)
+        self.direct_out, self.direct_q, self.direct_kv = bool(direct_out), bool(direct_q), bool(direct_kv)
         self.pieces = 1 if pieces is None else max(1, min(int(pieces), 8, batch))
         with torch.cuda.device(dev):
             if self.pieces > 1:
@@ -544,9 +545,12 @@ class HostDecodeStep:
             direct = self.pieces == 1
             q_d = self.q_h.data_ptr() if (direct and self.direct_q) else self.q_d.data_ptr()
             out_d = self.out_h.data_ptr() if (direct and self.direct_out) else self.out_d.data_ptr()
+            kv = direct and self.direct_kv
+            k_d = self.k_h.data_ptr() if kv else self.k_d.data_ptr()
+            v_d = self.v_h.data_ptr() if kv else self.v_d.data_ptr()
             args = (self.q_h.data_ptr(), self.k_h.data_ptr(), self.v_h.data_ptr(), self.slot_h.data_ptr(),
                     self.ctx_h.data_ptr(), self.bt_h.data_ptr(), self.out_h.data_ptr(),
-                    q_d, self.k_d.data_ptr(), self.v_d.data_ptr(), self.slot_d.data_ptr(),
+                    q_d, k_d, v_d, self.slot_d.data_ptr(),
                     self.ctx_d.data_ptr(), self.bt_d.data_ptr(), out_d,
                     self.k_cache.data_ptr(), self.v_cache.data_ptr(), self.idx_flag, self.batch,
                     self.max_num_blocks, self.num_heads, self.num_kv_heads, self.head_dim,
