@@ -6,7 +6,7 @@ from minivllm_b200.layers.attention import flash_attention_prefill
 dev = torch.device("cuda", 0)
 FLAGS = 1 if "--mma-sync" in sys.argv else 2 if "--single" in sys.argv else 4 if "--pair" in sys.argv else 0
 H, KVH, D = 32, 8, 128
-for nseq, n in ((64, 128), (32, 256), (16, 512), (8, 1024), (32, 1024), (16, 2048)):
+for nseq, n in ((64, 128), (32, 256), (16, 512), (8, 1024), (32, 1024), (16, 2048), (4, 4096), (2, 16384)):
     T = nseq * n
     q = torch.randn(T, H, D, device=dev).to(torch.bfloat16)
     k = torch.randn(T, KVH, D, device=dev).to(torch.bfloat16)
