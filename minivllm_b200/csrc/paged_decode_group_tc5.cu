@@ -134,6 +134,9 @@ __device__ __forceinline__ uint32_t lds_word(uint32_t addr) {
   return v;
 }
 
+// (4 stages and a 184-register cap leave room on every SM for one CTA of the split kernel beside this one;
+// measured on C5: items 52 -> 59 us, step 0.351 -> 0.359 ms — sharing the SM costs this kernel more than the
+// split kernel's single CTA gains.  One CTA per SM, all of it.)
 template <typename T, int D, bool PAGE16>
 __global__ void __launch_bounds__(256, 1)
 paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const DecodeParams p, const int batch) {
@@ -159,23 +162,6 @@ paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const Deco
   static_assert(8 + 8 * (3 * STAGES + 6) + 8 <= 256, "barrier block");
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-
-  // ---- work list of the pre-pass: wl_b[e] = leader of wide sub-group e, wl_cum[e] = shared chunks of
-  // the sub-groups before it; meta = leader | gsize | gshare | lcpt | wl_b | wl_cum | (n, total)
-  const int* meta = p.share_meta;
-  const int* gsize = meta + batch;
-  const int* wl_b = meta + 4 * batch;
-  const int* wl_cum = meta + 5 * batch;
-  const int wl_n = meta[6 * batch], wl_total = meta[6 * batch + 1];
-  const int X = p.KVH;                       // kv heads (sharing needs G <= 4: one head tile each)
-  const long long n_items = (long long)wl_total * X;
-  if (n_items == 0) return;
-  // as many CTAs as make every one of them do the same number of items (416 items on 148 SMs: 139 CTAs x 3
-  // rather than 120 x 3 + 28 x 2); the SMs left over go to the split kernel from the start
-  const long long rounds = (n_items + gridDim.x - 1) / gridDim.x;
-  const int use_ctas = (int)((n_items + rounds - 1) / rounds);
-  if ((int)blockIdx.x >= use_ctas) return;
 
   if (tid == 64) tc5::prefetch_tensormap(&mq);
   if (warp == 2) {
@@ -197,6 +183,30 @@ paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const Deco
   __syncthreads();
   tc5::fence_after_sync();
   const uint32_t tmem = lds_word(tmem_slot);
+
+  // Everything above ran while the pre-pass in front (programmatic dependency) was still finishing.  Its
+  // work list is read only behind this wait — and only then may the split kernel, OUR dependent, start:
+  // it reads the same pre-pass output and does not wait at its entry.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  // ---- work list of the pre-pass: wl_b[e] = leader of wide sub-group e, wl_cum[e] = shared chunks of
+  // the sub-groups before it; meta = leader | gsize | gshare | lcpt | wl_b | wl_cum | (n, total)
+  const int* meta = p.share_meta;
+  const int* gsize = meta + batch;
+  const int* wl_b = meta + 4 * batch;
+  const int* wl_cum = meta + 5 * batch;
+  const int wl_n = meta[6 * batch], wl_total = meta[6 * batch + 1];
+  const int X = p.KVH;                       // kv heads (sharing needs G <= 4: one head tile each)
+  const long long n_items = (long long)wl_total * X;
+  // as many CTAs as make every one of them do the same number of items (416 items on 148 SMs: 139 CTAs x 3
+  // rather than 120 x 3 + 28 x 2); the SMs left over go to the split kernel from the start
+  const long long rounds = n_items > 0 ? (n_items + gridDim.x - 1) / gridDim.x : 1;
+  const int use_ctas = (int)((n_items + rounds - 1) / rounds);
+  if ((int)blockIdx.x >= use_ctas) {  // nothing for this CTA (use_ctas = 0 when no sub-group is wide)
+    __syncthreads();
+    if (warp == 2) tc5::tmem_dealloc(tmem, C::TMEM_COLS);
+    return;
+  }
 
   // diagnostics (mvl_debug_set_times): CTA 0's first item, 6 stamps per tile
   auto stamp = [&](int j, int which) {
@@ -565,9 +575,19 @@ int launch_group_tc5_d(const DecodeParams& p, const CUtensorMap& mq, long long b
       return fail_cuda((int)e, "cudaFuncSetAttribute (group tcgen05)");
     if (dev < 64) configured[dev][di] = true;
   }
-  // ordinary stream order behind the pre-pass; the split kernel follows as ITS programmatic dependent
-  kern<<<dim3((unsigned)num_sms), 256, C::SMEM, s>>>(mq, p, (int)batch);
-  e = cudaGetLastError();
+  // programmatic dependent of the pre-pass (its set-up overlaps that; it waits before reading the work list);
+  // the split kernel follows as ITS programmatic dependent
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)num_sms);
+  cfg.blockDim = dim3(256);
+  cfg.dynamicSmemBytes = C::SMEM;
+  cfg.stream = s;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  e = cudaLaunchKernelEx(&cfg, kern, mq, p, (int)batch);
   if (e != cudaSuccess) return fail_cuda((int)e, "paged_decode_group_tc5 launch");
   return 0;
 }

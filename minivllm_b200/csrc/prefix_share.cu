@@ -20,11 +20,12 @@ __device__ __forceinline__ long long load_ctx(const void* ctx, int is_i64, long 
   return v > cap ? cap : v;
 }
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(512)
 lcp_kernel(const int32_t* __restrict__ bt, long long bt_stride, const void* ctx, int ctx_is_i64,
            long long max_ctx, int bs_shift, int* __restrict__ lcpt) {
   const int b = blockIdx.x;
-  __shared__ int s_min[4];
+  __shared__ int s_min[16];
+  griddep_launch_dependents();  // group_kernel may be set up meanwhile; it waits for this grid before reading
   if (b == 0) {
     if (threadIdx.x == 0) lcpt[0] = 0;
     return;
@@ -58,7 +59,7 @@ lcp_kernel(const int32_t* __restrict__ bt, long long bt_stride, const void* ctx,
   if ((threadIdx.x & 31) == 0) s_min[threadIdx.x >> 5] = first;
   __syncthreads();
   if (threadIdx.x == 0) {
-    first = min(min(s_min[0], s_min[1]), min(s_min[2], s_min[3]));
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) first = min(first, s_min[w]);
     const long long tok = (long long)first << bs_shift;
     lcpt[b] = (int)(tok < lim ? tok : lim);
   }
@@ -73,6 +74,8 @@ __global__ void __launch_bounds__(256) group_kernel(int* __restrict__ meta, int 
   const int* lcpt = meta + 3 * batch;
   __shared__ int s_warp[8];
   __shared__ int s_carry;
+  griddep_launch_dependents();  // the decode kernels behind wait for this grid before they read `meta`
+  griddep_wait();               // lcpt of every sequence is written
   if (threadIdx.x == 0) s_carry = 0;
   __syncthreads();
   // run start of b = last j <= b that does not share a whole chunk with its predecessor
@@ -128,10 +131,21 @@ __global__ void __launch_bounds__(256) group_kernel(int* __restrict__ meta, int 
 int launch_prefix_share(const int32_t* bt, long long bt_stride, const void* ctx, int ctx_is_i64,
                         long long batch, long long max_ctx, int bs_shift, int chunk, int mm, int mm_narrow,
                         int* meta, cudaStream_t s) {
-  lcp_kernel<<<(unsigned)batch, 128, 0, s>>>(bt, bt_stride, ctx, ctx_is_i64, max_ctx, bs_shift,
+  lcp_kernel<<<(unsigned)batch, 512, 0, s>>>(bt, bt_stride, ctx, ctx_is_i64, max_ctx, bs_shift,
                                              meta + 3 * batch);
-  group_kernel<<<1, 256, 0, s>>>(meta, (int)batch, chunk, mm, mm_narrow);
-  return (int)cudaGetLastError();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return (int)e;
+  // programmatic dependent of lcp_kernel: its launch overlaps that kernel, it waits for it before reading
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(1);
+  cfg.blockDim = dim3(256);
+  cfg.stream = s;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return (int)cudaLaunchKernelEx(&cfg, group_kernel, meta, (int)batch, chunk, mm, mm_narrow);
 }
 
 }  // namespace mvl
