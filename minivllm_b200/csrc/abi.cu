@@ -441,9 +441,9 @@ static int decode_impl(const StoreArgs* st_args, void* const* outs, int n_out, i
       stream_eligible(batch, num_kv_heads, pl.n_gt, pl.max_ctx, elem_dtype, chunk_tokens) && workspace &&
       aligned16(workspace) && workspace_bytes >= stream_workspace(batch, head_dim, sms)) {
     // Measured on B200 (profiles/r02_sweep_stream_vs_grid.jsonl, r02_sweep_small.jsonl): the chunk grid is
-    // as fast or faster on every shape but the one-kv-head shard of a large batch (1-2 % there), because
-    // SMs stream at unequal, position-dependent speeds and the hardware's CTA scheduler evens that out
-    // where equal fixed pieces cannot.  So the stream kernel runs only when asked for.
+    // as fast or faster on every shape but the one-kv-head shard of a large batch (1-2 % there): CTAs with
+    // equal work finish +-10 % apart, and the hardware's CTA scheduler, handing out many small CTAs as slots
+    // free up, evens that out where fixed pieces cannot.  So the stream kernel runs only when asked for.
     use_stream = (flags & MVL_DECODE_STREAM) != 0;
   }
 

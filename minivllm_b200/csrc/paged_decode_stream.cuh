@@ -17,10 +17,11 @@
 // under way when its piece began and the one still under way when it ends) and the last to arrive
 // merges them in piece order — deterministic whatever the arrival order.
 //
-// What equal pieces cannot fix (measured, scripts/diag_stream_times.py): SMs do not stream at equal
-// speed.  On C3's 8-way shard the mean CTA time per SM ranges from 72 to 90 us, the same SMs fast and
-// slow in every run (a property of where an SM sits), so the median CTA is done at 87 us and the last
-// at ~100.  Handing the last quarter of the stream out dynamically (items claimed with an atomic
+// What equal pieces do not buy (measured, scripts/diag_stream_times.py): CTAs with equal work do not finish
+// together.  On C3's 8-way shard the median CTA is done at 87 us and the last at ~100, the same blocks early
+// and late in every launch; sizing the pieces by a probe's per-SM speed or by each block's own speed in the
+// previous launch leaves that spread where it is.  Handing the last quarter of the
+// stream out dynamically (items claimed with an atomic
 // counter, halving in size) was built and measured: the fine items it needs near the end turn every
 // long sequence into dozens of partials whose merge sits on the critical path (0.11 -> 0.20 ms on that
 // shard), so the cut stays static.
