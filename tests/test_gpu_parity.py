@@ -738,6 +738,31 @@ def test_prefix_sharing_is_bit_identical(cuda_device, H, KVH, D, chunk):
     _assert_close(base.float().cpu().numpy(), want, torch.bfloat16)
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("H,KVH,D", [(8, 2, 128), (4, 4, 64), (6, 2, 128)])
+def test_prefix_sharing_wide_form_on_tcgen05(cuda_device, dtype, H, KVH, D):
+    """The shared chunks of large sub-groups on the tcgen05 group kernel (chunks of whole 128-token multiples,
+    16-slot pages): fp16 and bf16, D 64 and 128, G = 4 / 1 / 3 (a spare head row per member), sub-groups of 3
+    to 10 sequences with shared lengths of several chunks, against the oracle, the unshared run and the
+    mma.sync group kernel; twice (counters and work list left clean)."""
+    from minivllm_b200 import _ext
+    groups = [(1024, [1100, 1025, 1900, 1030, 1500]), (0, [130]), (512, [513, 700, 600]), (256, [300, 290]),
+              (768, [800, 769, 900, 1000, 770, 1200, 1700, 771, 905, 800])]
+    inp = _aliased_case(1200 + H + D, dtype, H, KVH, D, 16, groups)
+    dev = _dev(inp, cuda_device)
+    want = _oracle(inp).numpy()
+    base = _run(dev, chunk_tokens=128, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_SPLIT_GRID)
+    _assert_close(base.float().cpu().numpy(), want, dtype)
+    for chunk in (128, 256):
+        for flags in (_ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX,
+                      _ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX | _ext.DECODE_GROUP_MMA,
+                      _ext.DECODE_SHARE_PREFIX):
+            for _ in range(2):
+                got = _run(dev, chunk_tokens=chunk, flags=flags)
+                assert (got.float() - base.float()).abs().max() <= 2e-2
+                _assert_close(got.float().cpu().numpy(), want, dtype)
+
+
 def test_prefix_sharing_golden_and_fused_step(cuda_device):
     from minivllm_b200 import _ext
     from minivllm_b200.layers.attention import decode_step
