@@ -24,8 +24,8 @@
 //           copies, rows located through the leader's block-table row (the members' rows agree on these
 //           pages), written in the 128-byte-swizzled layout the MMA descriptors read; "full" barriers
 //           by cp.async.mbarrier.arrive, "empty" barriers armed by tcgen05.commit.  (Q comes by TMA.)
-//   warp 2  lane 0 issues every MMA, in the order QK(j+1), PV(j): the next tile's scores are computed
-//           while this tile's softmax runs (S is double-buffered in TMEM)
+//   warp 2  lane 0 issues every MMA, in the order QK(j+2), PV(j): the scores of the next two tiles are
+//           computed while this tile's softmax runs (three S buffers in TMEM)
 // With 192 KB of K/V in flight per SM the loads are never exposed (the first tcgen05 attempt of round 1
 // had one K and one V buffer per CTA and lost to the mma.sync kernel for that reason).
 //
@@ -56,10 +56,15 @@ struct Gt5Cfg {
   static constexpr int TILE_BYTES = PANELS * PANEL_BYTES;
   static constexpr int OFF_KV = Q_TILE_BYTES;       // stage s: K at OFF_KV + 2 s TILE_BYTES, V one tile further
   static constexpr int OFF_BAR = OFF_KV + 2 * STAGES * TILE_BYTES;
-  static constexpr int SMEM = OFF_BAR + 256 + 1024;  // + barriers / TMEM slot / flags + alignment slack
-  // S0 [0, TPC)  S1 [TPC, 2 TPC)  O of the even tiles [2 TPC, 2 TPC + D)  O of the odd tiles behind it
-  static constexpr int O_COL = 2 * TPC;
-  static constexpr int TMEM_COLS = (2 * TPC + 2 * D) <= 256 ? 256 : 512;
+  static constexpr int OFF_XML = OFF_BAR + 256;      // (m, l) of the odd softmax stream, two items deep
+  static constexpr int SMEM = OFF_XML + 512 + 1024;  // + alignment slack
+  // Three score buffers S0 S1 S2 of TPC columns, then O of the even tiles (D columns) and O of the odd tiles.
+  // Three, so that Q.K of tile j+2 can be issued while tile j's softmax still runs: with two, a softmax warp
+  // sat idle between its tiles for a P.V issue + Q.K round trip (0.5 us of every 1.5 us, measured) and the
+  // K/V ring drained at one tile per 0.77 us, below the SM's share of HBM.
+  static constexpr int SBUF = 3;
+  static constexpr int O_COL = SBUF * TPC;
+  static constexpr int TMEM_COLS = (SBUF * TPC + 2 * D) <= 256 ? 256 : 512;
 };
 
 __device__ __forceinline__ float fmax3f(float a, float b, float c) {
@@ -151,15 +156,19 @@ paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const Deco
   auto sK = [&](int st) -> uint32_t { return base + C::OFF_KV + (uint32_t)st * 2 * C::TILE_BYTES; };
   auto sV = [&](int st) -> uint32_t { return sK(st) + C::TILE_BYTES; };
   const uint32_t bar0 = base + C::OFF_BAR;
-  const uint32_t bar_q = bar0;
-  auto bar_kf = [&](int st) { return bar0 + 8 + 8 * st; };                      // K tile of a stage landed
-  auto bar_vf = [&](int st) { return bar0 + 8 + 8 * (STAGES + st); };           // V tile landed
-  auto bar_emp = [&](int st) { return bar0 + 8 + 8 * (2 * STAGES + st); };      // both consumed
-  auto bar_sf = [&](int sb) { return bar0 + 8 + 8 * (3 * STAGES + sb); };       // S buffer holds a tile's scores
-  auto bar_pr = [&](int sb) { return bar0 + 8 + 8 * (3 * STAGES + 2 + sb); };   // ... its P
-  auto bar_o = [&](int sb) { return bar0 + 8 + 8 * (3 * STAGES + 4 + sb); };    // P.V into O[sb] retired
-  const uint32_t tmem_slot = bar0 + 8 + 8 * (3 * STAGES + 6), flag = tmem_slot + 4;
-  static_assert(8 + 8 * (3 * STAGES + 6) + 8 <= 256, "barrier block");
+  auto bar_q = [&](int slot) { return bar0 + 8 * slot; };                        // Q rows of an item landed (two slots)
+  auto bar_kf = [&](int st) { return bar0 + 16 + 8 * st; };                     // K tile of a stage landed
+  auto bar_vf = [&](int st) { return bar0 + 16 + 8 * (STAGES + st); };          // V tile landed
+  auto bar_emp = [&](int st) { return bar0 + 16 + 8 * (2 * STAGES + st); };     // both consumed
+  auto bar_sf = [&](int sb) { return bar0 + 16 + 8 * (3 * STAGES + sb); };      // S buffer holds a tile's scores
+  auto bar_pr = [&](int sb) { return bar0 + 16 + 8 * (3 * STAGES + 3 + sb); };  // ... its P
+  auto bar_o = [&](int sb) { return bar0 + 16 + 8 * (3 * STAGES + 6 + sb); };   // P.V into O[sb] retired
+  const uint32_t bar_drain = bar0 + 16 + 8 * (3 * STAGES + 8);  // both O accumulators of an item read out
+  const uint32_t bar_done = bar_drain + 8;                      // the item's partials are in global memory
+  const uint32_t bar_fin = bar_drain + 16;                      // the finishers are through with the item
+  const uint32_t tmem_slot = bar_drain + 24, flag = tmem_slot + 4;
+  static_assert(16 + 8 * (3 * STAGES + 11) + 8 <= 256, "barrier block");
+  const uint32_t s_xml = base + C::OFF_XML;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
@@ -169,13 +178,14 @@ paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const Deco
     tc5::tmem_relinquish();
   }
   if (tid == 32) {
-    mbar_init(bar_q, 1);
+    mbar_init(bar_q(0), 1), mbar_init(bar_q(1), 1);
+    mbar_init(bar_drain, 1), mbar_init(bar_done, 1), mbar_init(bar_fin, 1);
     for (int st = 0; st < STAGES; ++st) mbar_init(bar_kf(st), 64), mbar_init(bar_vf(st), 64), mbar_init(bar_emp(st), 1);
-    for (int sb = 0; sb < 2; ++sb) mbar_init(bar_sf(sb), 1), mbar_init(bar_pr(sb), 1);
+    for (int sb = 0; sb < C::SBUF; ++sb) mbar_init(bar_sf(sb), 1), mbar_init(bar_pr(sb), 1);
     mbar_init(bar_o(0), 1), mbar_init(bar_o(1), 1);
     mbar_fence_init();
   }
-  // rows of the Q tile the loads never write (rows past the sub-group's 32) must hold finite garbage at most
+  // rows of the Q tile the loads never write: zeros (they only feed accumulator rows nobody reads)
   for (uint32_t i = tid * 16; i < (uint32_t)C::Q_TILE_BYTES; i += 256 * 16)
     asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(sQ + i), "r"(0u) : "memory");
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -216,59 +226,176 @@ paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const Deco
       p.dbg_times[j * 6 + which] = tnow;
     }
   };
+  // ... and per CTA and item: start / partials written / counted / merged (called by one thread)
+  auto stamp_item = [&](uint32_t n, int which) {
+    if (p.dbg_times != nullptr && n < 4) {
+      unsigned long long tnow;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tnow));
+      p.dbg_times[192 + (blockIdx.x * 4 + n) * 5 + which] = tnow;
+    }
+  };
   const int gp = 1 << p.gp_shift, gp_mask = gp - 1;
   const int rows_box = 32;                          // (32 / gp) members x gp heads
-  const int tiles = p.chunk / TPC;                  // a shared chunk is a whole chunk (multiple of 128)
+  const int tiles = p.chunk / TPC;                  // a shared chunk is a whole chunk (multiple of 128): even, >= 2
   const uint32_t q_bytes = (uint32_t)C::PANELS * rows_box * 128;
   constexpr uint32_t HI = tc5::smem_desc_hi_sw128(1024);
-  const uint32_t q_lo = tc5::smem_desc_lo(sQ, 16);
+  // An item's 32 Q rows take the first 4 KB of each panel of the Q tile; the next item's go behind them
+  // (rows 32..63), so that they can be fetched while this item's Q.K still read theirs.  The 128-row
+  // operand of an odd item starts at row 32 and runs into whatever follows the tile: rows nobody reads.
+  constexpr uint32_t Q_SLOT_BYTES = 32 * 128;
+  const int g_valid = p.G;
 
-  uint32_t gt = 0;      // tiles this CTA has streamed so far (all roles count alike): stage / phase bookkeeping
-  uint32_t items_done = 0;
-  for (long long item = blockIdx.x; item < n_items; item += use_ctas, ++items_done) {
-    // ---- which (sub-group, kv head, chunk)
-    const int x = (int)(item % X);
+  // ---- which (sub-group, kv head, shared chunk) a work item is
+  struct Item {
+    int b, split, nmem, start, head0, x;
+  };
+  auto item_of = [&](long long item) -> Item {
+    Item it;
+    it.x = (int)(item % X);
     const int ci = (int)(item / X);
     int lo = 0, hi = wl_n;  // wl_cum[lo] <= ci < wl_cum[hi]
     while (hi - lo > 1) {
       const int mid = (lo + hi) >> 1;
       if (wl_cum[mid] <= ci) lo = mid; else hi = mid;
     }
-    const int b = wl_b[lo], split = ci - wl_cum[lo];
-    const int nmem = gsize[b];
-    const int start = split * p.chunk;
-    const int head0 = x * p.G;
-    const int g_valid = p.G;
-    const uint32_t q_phase = items_done & 1u;
-    auto stamp_item = [&](int which) {   // diagnostics: per CTA and item, start / streamed / counted / merged
-      if (p.dbg_times != nullptr && tid == 0 && items_done < 4) {
-        unsigned long long tnow;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tnow));
-        p.dbg_times[192 + (blockIdx.x * 4 + items_done) * 5 + which] = tnow;
-      }
-    };
-    stamp_item(0);
+    it.b = wl_b[lo];
+    it.split = ci - wl_cum[lo];
+    it.nmem = gsize[it.b];
+    it.start = it.split * p.chunk;
+    it.head0 = it.x * p.G;
+    return it;
+  };
 
-    if (warp == 1 || warp == 3) {
-      // ================================================================ K/V producer (64 threads)
-      // 16-byte cp.async copies straight into the 128-byte-swizzled tile layout the MMA descriptors
-      // expect (row = token, 128 bytes per row and panel, chunk index XOR row % 8).  Measured first with
-      // TMA boxes: with 16-slot pages a tile is 32 boxes of 2 KB, and the TMA unit's box rate capped the
-      // kernel at 2.2 TB/s.  A thread owns chunk column `cc` of rows rg, rg + 4, ...; it arrives on the
-      // stage's barriers with cp.async.mbarrier.arrive.noinc, i.e. when its copies have landed.
-      const int pt = (warp == 1 ? 0 : 32) + lane;        // 0..63
-      const int cc = pt % (C::PANELS * 8), rg = pt / (C::PANELS * 8);
-      constexpr int RSTEP = 64 / (C::PANELS * 8);         // rows covered per pass of the 64 threads
-      if (pt == 0) {
-        mbar_expect_tx(bar_q, q_bytes);
-#pragma unroll
-        for (int pn = 0; pn < C::PANELS; ++pn) tma_load_3d(sQ + pn * C::Q_PANEL_BYTES, &mq, pn * 64, head0, b, bar_q);
+  // ---- finishing an item: per member, the last of its chunk CTAs to arrive merges its partials (the split
+  // kernel's protocol).  Run by a group of `nt` threads (thread `ft` of it) that meets on named barrier `bar_id`:
+  // the three finisher warps while the item behind is streaming, the whole CTA for its last item.
+  auto finish = [&](const Item& it, uint32_t n, int ft, int nt, int bar_id) {
+    const int b = it.b, x = it.x, nmem = it.nmem, head0 = it.head0;
+    auto group_sync = [&] { asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(nt) : "memory"); };
+    if (p.counters != nullptr) {
+      auto member_chunks = [&](int mm) -> int {
+        long long c = p.ctx_is_i64 ? reinterpret_cast<const long long*>(p.ctx)[b + mm]
+                                   : (long long)reinterpret_cast<const int*>(p.ctx)[b + mm];
+        if (c > p.max_ctx) c = p.max_ctx;
+        return (int)((c + p.chunk - 1) / p.chunk);
+      };
+      // lane m of the group's first warp counts member m's arrival (the members' atomics in parallel, not
+      // one thread after the other: that loop cost 5 us per item)
+      if (ft < 32) {
+        __threadfence();
+        bool last = false;
+        if (lane < nmem) {
+          const int na = member_chunks(lane);
+          int* cnt = p.counters + (long long)(b + lane) * X + x;
+          if (atomicAdd(cnt, 1) == na - 1) {
+            *cnt = 0;
+            last = true;
+          }
+        }
+        const uint32_t lm = __ballot_sync(0xffffffffu, last);
+        if (lm) __threadfence();
+        if (lane == 0) asm volatile("st.shared.u32 [%0], %1;" ::"r"(flag), "r"(lm) : "memory");
       }
-      const int32_t* table = p.bt + (long long)b * p.bt_stride;
+      group_sync();
+      const uint32_t last_mask = lds_word(flag);
+      if (ft == 0) stamp_item(n, 2);
+      if (last_mask != 0) {
+        // Merge of the members this CTA completed: 32 rows x D/4 columns of float4, IT (row, column) items
+        // per thread and pass.  All of a thread's items advance together, two partials at a time, so 16
+        // loads are in flight per thread instead of one item's four (the merge of a whole sub-group took
+        // up to 86 us as eight dependent passes per thread); every item still folds in chunk order.
+        constexpr int IT = 4, NI = 32 * (D / 4);
+        for (int base_i = 0; base_i < NI; base_i += nt * IT) {
+          float Mx[IT], Ls[IT], a0[IT], a1[IT], a2[IT], a3[IT];
+          long long pi0[IT];
+          int na_i[IT];
+          int na_max = 0;
+#pragma unroll
+          for (int u = 0; u < IT; ++u) {
+            const int itx = base_i + ft + u * nt;
+            const int r = itx / (D / 4);
+            const int mm = r >> p.gp_shift, hd = r & gp_mask;
+            const bool ok = itx < NI && mm < nmem && hd < g_valid && ((last_mask >> mm) & 1u);
+            na_i[u] = ok ? member_chunks(mm) : 0;
+            pi0[u] = ((long long)(b + (ok ? mm : 0)) * p.H + head0 + (ok ? hd : 0)) * p.max_splits;
+            Mx[u] = -INFINITY;
+            Ls[u] = a0[u] = a1[u] = a2[u] = a3[u] = 0.f;
+            na_max = max(na_max, na_i[u]);
+          }
+          for (int s0 = 0; s0 < na_max; s0 += 2) {
+            float2 ml[IT][2];
+            float4 v[IT][2];
+#pragma unroll
+            for (int u = 0; u < IT; ++u) {
+              const int dq = (base_i + ft + u * nt) % (D / 4);
+#pragma unroll
+              for (int k = 0; k < 2; ++k) {
+                const int sidx = min(s0 + k, max(na_i[u] - 1, 0));
+                ml[u][k] = __ldcg(p.part_ml + pi0[u] + sidx);
+                v[u][k] = __ldcg(reinterpret_cast<const float4*>(p.part_o + (pi0[u] + sidx) * D + dq * 4));
+              }
+            }
+#pragma unroll
+            for (int u = 0; u < IT; ++u) {
+#pragma unroll
+              for (int k = 0; k < 2; ++k) {
+                if (s0 + k < na_i[u]) {
+                  const float Mn = fmaxf(Mx[u], ml[u][k].x);
+                  const float so = fast_exp2(Mx[u] - Mn), sn = fast_exp2(ml[u][k].x - Mn);
+                  Ls[u] = Ls[u] * so + ml[u][k].y * sn;
+                  a0[u] = a0[u] * so + v[u][k].x * sn;
+                  a1[u] = a1[u] * so + v[u][k].y * sn;
+                  a2[u] = a2[u] * so + v[u][k].z * sn;
+                  a3[u] = a3[u] * so + v[u][k].w * sn;
+                  Mx[u] = Mn;
+                }
+              }
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < IT; ++u) {
+            if (na_i[u] == 0) continue;
+            const int itx = base_i + ft + u * nt;
+            const int r = itx / (D / 4), dq = itx % (D / 4);
+            const int mm = r >> p.gp_shift, hd = r & gp_mask;
+            const float inv = 1.f / Ls[u];
+            store_out4<T, D>(p, b + mm, head0 + hd, dq * 4, a0[u] * inv, a1[u] * inv, a2[u] * inv, a3[u] * inv);
+          }
+        }
+      }
+      group_sync();  // the flag word is rewritten by the next item
+      if (ft == 0) {
+        stamp_item(n, 3);
+        if (p.dbg_times != nullptr && n < 4) p.dbg_times[192 + (blockIdx.x * 4 + n) * 5 + 4] = last_mask;
+      }
+    }
+  };
+  const uint32_t my_items = (uint32_t)((n_items - blockIdx.x + use_ctas - 1) / use_ctas);
+
+  // Every role walks this CTA's items on its own, meeting the others only through mbarriers: the producers
+  // are copying the next item's tiles while the last scores of this one are still being exponentiated, its
+  // Q rows are already there, and counting / merging is the business of three otherwise idle warps.  (With
+  // a __syncthreads() at the end of every item the ring ran dry, the partials were written, counted and
+  // merged, and the ring filled again: 7.7 us of every 57.)  `gt` = tiles streamed before the item; all
+  // roles count alike: ring stage g % STAGES, score buffer g % 3, and the phases that follow from them.
+  if (warp == 1 || warp == 3) {
+    // ================================================================ K/V producers (64 threads)
+    // 16-byte cp.async copies straight into the 128-byte-swizzled tile layout the MMA descriptors
+    // expect (row = token, 128 bytes per row and panel, chunk index XOR row % 8).  Measured first with
+    // TMA boxes: with 16-slot pages a tile is 32 boxes of 2 KB, and the TMA unit's box rate capped the
+    // kernel at 2.2 TB/s.  A thread owns chunk column `cc` of rows rg, rg + 4, ...; it arrives on the
+    // stage's barriers with cp.async.mbarrier.arrive.noinc, i.e. when its copies have landed.
+    const int pt = (warp == 1 ? 0 : 32) + lane;        // 0..63
+    const int cc = pt % (C::PANELS * 8), rg = pt / (C::PANELS * 8);
+    constexpr int RSTEP = 64 / (C::PANELS * 8);         // rows covered per pass of the 64 threads
+    uint32_t gt = 0, n = 0;
+    for (long long item = blockIdx.x; item < n_items; item += use_ctas, ++n) {
+      const Item it = item_of(item);
+      const int32_t* table = p.bt + (long long)it.b * p.bt_stride;
       const int bs_mask = (1 << p.bs_shift) - 1;
       const uint32_t row_pitch = (uint32_t)p.KVH * (D * 2);
-      const char* kbase = reinterpret_cast<const char*>(p.kc) + (long long)x * (D * 2) + cc * 16;
-      const char* vbase = reinterpret_cast<const char*>(p.vc) + (long long)x * (D * 2) + cc * 16;
+      const char* kbase = reinterpret_cast<const char*>(p.kc) + (long long)it.x * (D * 2) + cc * 16;
+      const char* vbase = reinterpret_cast<const char*>(p.vc) + (long long)it.x * (D * 2) + cc * 16;
       const uint32_t col_off = (uint32_t)(cc >> 3) * C::PANEL_BYTES;
       // row r = rg + kk (kk a multiple of RSTEP): swizzled offset inside its 8-row atom, and byte offset of
       // its slot inside a 16-slot page, for the few values (kk & 7) and (kk & 15) can take
@@ -281,18 +408,34 @@ paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const Deco
       }
 #pragma unroll
       for (int u = 0; u < 16 / RSTEP; ++u) within[u] = (long long)(rg + u * RSTEP) * row_pitch;
+      // The item's table entries travel in windows of 32, one window ahead of the copies: lane l holds
+      // entry pgs + 32 w + l of the current window and of the next one, a row fetches its page with a
+      // shuffle.  (One load per tile, issued when the tile came up, was measured as the ring's longest
+      // link: every other tile missed L1 for its 32-byte table sector and the stage sat empty for ~1 us
+      // before its first copy left.)  A tile's pages never straddle a window: TPC / block_size of them,
+      // aligned to that count from the item's first page.
+      const int pgs = it.start >> p.bs_shift;
+      const int pg_last = (it.start + p.chunk - 1) >> p.bs_shift;
+      auto load_window = [&](int w) -> uint32_t {
+        const int e = pgs + w * 32 + lane;
+        return e <= pg_last ? (uint32_t)__ldg(table + e) : 0u;
+      };
+      uint32_t e_cur = load_window(0), e_nxt = load_window(1);
+      int win = 0;
       for (int j = 0; j < tiles; ++j) {
         const uint32_t g = gt + j;
         const int st = g % STAGES;
+        const int tok0 = it.start + j * TPC;
+        const int rel = (tok0 >> p.bs_shift) - pgs;
+        if ((rel >> 5) != win) {  // at most one window further: a tile advances by TPC / block_size <= 4 pages
+          e_cur = e_nxt;
+          ++win;
+          e_nxt = load_window(win + 1);
+        }
+        const int wi = rel & 31;
         if (g >= (uint32_t)STAGES) tc5::mbar_wait_bounded(bar_emp(st), ((g / STAGES) - 1) & 1u);
-        if (pt == 0 && items_done == 0) stamp(j, 0);
+        if (pt == 0 && n == 0) stamp(j, 0);
         const uint32_t kdst = sK(st) + col_off, vdst = sV(st) + col_off;
-        const int tok0 = start + j * TPC;
-        // the tile's table entries (at most 8 pages of >= 16 slots): lane l holds entry l, rows fetch
-        // theirs with a shuffle — one table load per tile and lane instead of a dependent load per row
-        const int pg0 = tok0 >> p.bs_shift;
-        const int npg = ((tok0 + TPC - 1) >> p.bs_shift) - pg0 + 1;
-        const uint32_t my_e = lane < npg ? (uint32_t)__ldg(table + pg0 + lane) : 0u;
         if (PAGE16) {
           // 16-slot pages (the reference's default, attention.py:483): page and slot-in-page of every row
           // this thread copies are compile-time functions of the unrolled row counter, so a copy costs an
@@ -301,7 +444,7 @@ paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const Deco
           const char* kpage[TPC / 16];
 #pragma unroll
           for (int pg = 0; pg < TPC / 16; ++pg)
-            kpage[pg] = kbase + (unsigned long long)(__shfl_sync(0xffffffffu, my_e, pg) << 4) * row_pitch;
+            kpage[pg] = kbase + (unsigned long long)(__shfl_sync(0xffffffffu, e_cur, wi + pg) << 4) * row_pitch;
           const long long v_minus_k = vbase - kbase;
 #pragma unroll
           for (int i = 0; i < TPC / RSTEP; ++i) {
@@ -320,7 +463,7 @@ paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const Deco
 #pragma unroll 8
           for (int r = rg; r < TPC; r += RSTEP) {
             const int tok = tok0 + r;
-            const uint32_t e = __shfl_sync(0xffffffffu, my_e, (tok >> p.bs_shift) - pg0);
+            const uint32_t e = __shfl_sync(0xffffffffu, e_cur, ((tok >> p.bs_shift) - pgs) & 31);
             const uint32_t slot = (e << p.bs_shift) + (uint32_t)(tok & bs_mask);
             const uint32_t off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u + (uint32_t)(((cc & 7) ^ (r & 7)) << 4);
             cp_async16(kdst + off, row_ptr(kbase, slot, row_pitch), 16u);
@@ -329,233 +472,195 @@ paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const Deco
 #pragma unroll 8
           for (int r = rg; r < TPC; r += RSTEP) {
             const int tok = tok0 + r;
-            const uint32_t e = __shfl_sync(0xffffffffu, my_e, (tok >> p.bs_shift) - pg0);
+            const uint32_t e = __shfl_sync(0xffffffffu, e_cur, ((tok >> p.bs_shift) - pgs) & 31);
             const uint32_t slot = (e << p.bs_shift) + (uint32_t)(tok & bs_mask);
             const uint32_t off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u + (uint32_t)(((cc & 7) ^ (r & 7)) << 4);
             cp_async16(vdst + off, row_ptr(vbase, slot, row_pitch), 16u);
           }
         }
         asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar_vf(st)) : "memory");
-        if (pt == 0 && items_done == 0) stamp(j, 1);
+        if (pt == 0 && n == 0) stamp(j, 1);
       }
-    } else if (warp == 2) {
-      // ================================================================ MMA issuer
-      if (lane == 0) {
+      gt += tiles;
+    }
+  } else if (warp == 2) {
+    // ================================================================ MMA issuer (and Q loader)
+    if (lane == 0) {
+      auto load_q = [&](const Item& it, uint32_t n) {
+        const uint32_t slot = n & 1u;
+        mbar_expect_tx(bar_q(slot), q_bytes);
+#pragma unroll
+        for (int pn = 0; pn < C::PANELS; ++pn)
+          tma_load_3d(sQ + pn * C::Q_PANEL_BYTES + slot * Q_SLOT_BYTES, &mq, pn * 64, it.head0, it.b, bar_q(slot));
+      };
+      // K/V tiles are written by cp.async (generic proxy) and read by the tensor cores (async proxy)
+      auto proxy_fence = [] { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); };
+      uint32_t gt = 0, n = 0;
+      load_q(item_of(blockIdx.x), 0);
+      for (long long item = blockIdx.x; item < n_items; item += use_ctas, ++n) {
+        if (item + use_ctas < n_items) {
+          // the other slot's last reader was item n - 1: its last Q.K has to have retired
+          if (n > 0) tc5::mbar_wait_bounded(bar_sf((gt - 1) % C::SBUF), ((gt - 1) / C::SBUF) & 1u);
+          load_q(item_of(item + use_ctas), n + 1);
+        }
+        tc5::mbar_wait_bounded(bar_q(n & 1u), (n >> 1) & 1u);
+        const uint32_t q_lo = tc5::smem_desc_lo(sQ + (n & 1u) * Q_SLOT_BYTES, 16);
         auto issue_qk = [&](uint32_t g) {
           const uint32_t k_lo = tc5::smem_desc_lo(sK(g % STAGES), 16);
-          const uint32_t s_t = tmem + (g & 1u) * TPC;
+          const uint32_t s_t = tmem + (g % C::SBUF) * TPC;
 #pragma unroll
           for (int ks = 0; ks < D / 16; ++ks) {
             const uint32_t qoff = ((ks >> 2) * C::Q_PANEL_BYTES + (ks & 3) * 32) >> 4;
             const uint32_t koff = ((ks >> 2) * C::PANEL_BYTES + (ks & 3) * 32) >> 4;
             tc5::mma_ss(s_t, tc5::desc64(q_lo + qoff, HI), tc5::desc64(k_lo + koff, HI), IDESC_QK, ks > 0);
           }
-          tc5::commit(bar_sf(g & 1u));
+          tc5::commit(bar_sf(g % C::SBUF));
         };
-        // K/V tiles are written by cp.async (generic proxy) and read by the tensor cores (async proxy)
-        auto proxy_fence = [] { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); };
-        tc5::mbar_wait_bounded(bar_q, q_phase);
-        tc5::mbar_wait_bounded(bar_kf(gt % STAGES), (gt / STAGES) & 1u);
-        proxy_fence();
-        tc5::fence_after_sync();
-        issue_qk(gt);
-        for (int j = 0; j < tiles; ++j) {
-          const uint32_t g = gt + j;
-          if (j + 1 < tiles) {
-            tc5::mbar_wait_bounded(bar_kf((g + 1) % STAGES), ((g + 1) / STAGES) & 1u);
-            proxy_fence();
-            tc5::fence_after_sync();
-            if (items_done == 0) stamp(j + 1, 2);
-            issue_qk(g + 1);  // queued behind P.V of tile j-1, which read the S buffer this one overwrites
-          }
-          tc5::mbar_wait_bounded(bar_pr(g & 1u), (g >> 1) & 1u);
-          tc5::mbar_wait_bounded(bar_vf(g % STAGES), (g / STAGES) & 1u);
-          proxy_fence();
-          tc5::fence_after_sync();
-          if (items_done == 0) stamp(j, 3);
-          const uint32_t v_lo = tc5::smem_desc_lo(sV(g % STAGES), C::PANEL_BYTES);
-          const uint32_t p_t = tmem + (g & 1u) * TPC;
+        // Event loop: whichever of {K tile of the next Q.K landed, P and V of the next P.V ready} comes first
+        // is issued first.  Q.K may run up to three tiles ahead of P.V (tile n's scores go where tile n - 3's
+        // P was, and the tensor pipe keeps issue order).  The first P.V of an item overwrites an accumulator:
+        // it also waits until the softmax warps have read the previous item's out of TMEM.
+        int nq = 0, npv = 0;  // tiles whose Q.K / P.V have been issued
+        bool o_free = n == 0;
+        uint32_t idle = 0;
+        while (npv < tiles) {
+          bool did = false;
+          if (npv < nq) {
+            const uint32_t g = gt + npv;
+            if (!o_free) o_free = tc5::mbar_test(bar_drain, (n - 1) & 1u);
+            if (o_free && tc5::mbar_test(bar_pr(g % C::SBUF), (g / C::SBUF) & 1u) &&
+                tc5::mbar_test(bar_vf(g % STAGES), (g / STAGES) & 1u)) {
+              proxy_fence();
+              tc5::fence_after_sync();
+              if (n == 0) stamp(npv, 3);
+              const uint32_t v_lo = tc5::smem_desc_lo(sV(g % STAGES), C::PANEL_BYTES);
+              const uint32_t p_t = tmem + (g % C::SBUF) * TPC;
 #pragma unroll
-          for (int kk = 0; kk < TPC / 16; ++kk)
-            tc5::mma_ts(tmem + C::O_COL + (j & 1) * D, p_t + kk * 8, tc5::desc64(v_lo + kk * (2048 >> 4), HI), IDESC_PV,
-                        (j > 1 || kk > 0) ? 1u : 0u);
-          tc5::commit(bar_emp(g % STAGES));
-          tc5::commit(bar_o(j & 1));
+              for (int kk = 0; kk < TPC / 16; ++kk)
+                tc5::mma_ts(tmem + C::O_COL + (npv & 1) * D, p_t + kk * 8, tc5::desc64(v_lo + kk * (2048 >> 4), HI),
+                            IDESC_PV, (npv > 1 || kk > 0) ? 1u : 0u);
+              tc5::commit(bar_emp(g % STAGES));
+              tc5::commit(bar_o(npv & 1));
+              ++npv;
+              did = true;
+            }
+          }
+          if (nq < tiles && nq < npv + C::SBUF) {
+            const uint32_t g = gt + nq;
+            if (tc5::mbar_test(bar_kf(g % STAGES), (g / STAGES) & 1u)) {
+              proxy_fence();
+              tc5::fence_after_sync();
+              if (n == 0 && nq > 0) stamp(nq, 2);
+              issue_qk(g);
+              ++nq;
+              did = true;
+            }
+          }
+          if (did) idle = 0;
+          else if (++idle > (1u << 28)) __trap();  // a lost completion is a programming error: do not hang the GPU
         }
+        gt += tiles;
       }
-      __syncwarp();
-    } else if (warp == 0 || warp == 4) {
-      // ================================================================ softmax: two streams
-      // Warp 0 takes the even tiles, warp 4 the odd ones (both reach TMEM lanes 0..31), each with its own
-      // running maximum, sum and O accumulator: one warp doing every tile's 64 x 32 exponentials was the
-      // slowest link of the tile pipeline (measured: 0.8-1.0 us of softmax + 0.25 us hand-off per 128
-      // tokens against 1.2 us of HBM time).  The two streams are merged below like two chunks.
-      const int q = warp >> 2;
+    }
+    __syncwarp();
+  } else if (warp == 0 || warp == 4) {
+    // ================================================================ softmax: two streams
+    // Warp 0 takes the even tiles, warp 4 the odd ones (both reach TMEM lanes 0..31), each with its own
+    // running maximum, sum and O accumulator: one warp doing every tile's 64 x 32 exponentials was the
+    // slowest link of the tile pipeline (measured: 0.8-1.0 us of softmax + 0.25 us hand-off per 128
+    // tokens against 1.2 us of HBM time).  The two streams are merged at the end of the item like two chunks.
+    const int q = warp >> 2;
+    const uint32_t lane_base = tmem;  // TMEM lanes 0..31
+    const uint32_t o_addr = lane_base + C::O_COL + q * D;
+    uint32_t gt = 0, n = 0;
+    for (long long item = blockIdx.x; item < n_items; item += use_ctas, ++n) {
+      const Item it = item_of(item);
+      if (tid == 0) stamp_item(n, 0);
       float m_ref = 0.f, l = 0.f;
-      const uint32_t lane_base = tmem;  // TMEM lanes 0..31
-      const uint32_t o_addr = lane_base + C::O_COL + q * D;
       for (int j = q; j < tiles; j += 2) {
         const uint32_t g = gt + j;
-        tc5::mbar_wait_bounded(bar_sf(q), (g >> 1) & 1u);
+        tc5::mbar_wait_bounded(bar_sf(g % C::SBUF), (g / C::SBUF) & 1u);
         tc5::fence_after_sync();
-        if (lane == 0 && items_done == 0) stamp(j, 4);
-        group_softmax_step<T, D, TPC>(lane_base + q * TPC, o_addr, j < 2, p.qscale, m_ref, l, bar_o(q),
+        if (lane == 0 && n == 0) stamp(j, 4);
+        group_softmax_step<T, D, TPC>(lane_base + (g % C::SBUF) * TPC, o_addr, j < 2, p.qscale, m_ref, l, bar_o(q),
                                       ((g >> 1) - 1) & 1u);
         tc5::fence_before_sync();
         __syncwarp();
-        if (lane == 0 && items_done == 0) stamp(j, 5);
-        if (lane == 0) tc5::mbar_arrive(bar_pr(q));
+        if (lane == 0 && n == 0) stamp(j, 5);
+        if (lane == 0) tc5::mbar_arrive(bar_pr(g % C::SBUF));
       }
+      // this stream's last product has retired (gt is even: a stream's tiles are every other g)
       const uint32_t g_last = gt + tiles - 2 + q;
       tc5::mbar_wait_bounded(bar_o(q), (g_last >> 1) & 1u);
-      tc5::fence_after_sync();
-      // this stream's row: O (D fp32), m (log2 units), l -> registers; the odd stream parks its row in
-      // shared memory (the K/V ring is idle: its wait above was for the item's last product)
-      float orow[D];
-#pragma unroll
-      for (int c = 0; c < D / 32; ++c) {
-        uint32_t o[32];
-        tc5::tmem_ld32(o_addr + c * 32, o);
-        tc5::tmem_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) orow[c * 32 + i] = __uint_as_float(o[i]);
-      }
-      const uint32_t xrow = sK(0) + (uint32_t)lane * (D + 4) * 4;
+      const uint32_t xml = s_xml + (n & 1u) * 256 + (uint32_t)lane * 8;  // two items deep: warp 4 runs ahead
       if (q == 1) {
-#pragma unroll
-        for (int i = 0; i < D; i += 4)
-          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(xrow + i * 4), "f"(orow[i]), "f"(orow[i + 1]),
-                       "f"(orow[i + 2]), "f"(orow[i + 3]) : "memory");
-        asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(xrow + D * 4), "f"(m_ref * p.qscale), "f"(l) : "memory");
-      }
-      tc5::fence_before_sync();
-      // both softmax warps (64 threads) meet: named barrier 1
-      asm volatile("bar.sync 1, 64;" ::: "memory");
-      if (q == 0) {
+        asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(xml), "f"(m_ref * p.qscale), "f"(l) : "memory");
+        tc5::fence_before_sync();
+        asm volatile("bar.sync 1, 64;" ::: "memory");  // both softmax warps (64 threads): named barrier 1
+      } else {
+        tc5::mbar_wait_bounded(bar_o(1), ((g_last + 1) >> 1) & 1u);  // ... and the odd stream's
+        asm volatile("bar.sync 1, 64;" ::: "memory");
+        tc5::fence_after_sync();
+        // Both accumulators sit in TMEM lanes 0..31, which this warp reaches: fold the odd stream's row into
+        // the even one's like a second chunk and write the item's partial in the split kernel's layout.
         float mo, lo2;
-        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(mo), "=f"(lo2) : "r"(xrow + D * 4) : "memory");
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(mo), "=f"(lo2) : "r"(xml) : "memory");
         const float me = m_ref * p.qscale;
         const float Mx = fmaxf(me, mo);
         const float se = fast_exp2(me - Mx), so = fast_exp2(mo - Mx);
         const float Lsum = l * se + lo2 * so;
         const int m = lane >> p.gp_shift, hd = lane & gp_mask;
-        const bool row_ok = m < nmem && hd < g_valid;
-        const long long pi = ((long long)(b + m) * p.H + head0 + hd) * p.max_splits + split;
+        const bool row_ok = m < it.nmem && hd < g_valid;
+        const long long pi = ((long long)(it.b + m) * p.H + it.head0 + hd) * p.max_splits + it.split;
 #pragma unroll
-        for (int i = 0; i < D; i += 4) {
-          float x0, x1, x2, x3;
-          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x0), "=f"(x1), "=f"(x2), "=f"(x3) : "r"(xrow + i * 4) : "memory");
-          if (row_ok)
-            *reinterpret_cast<float4*>(p.part_o + pi * D + i) =
-                make_float4(orow[i] * se + x0 * so, orow[i + 1] * se + x1 * so, orow[i + 2] * se + x2 * so,
-                            orow[i + 3] * se + x3 * so);
+        for (int c = 0; c < D / 32; ++c) {
+          uint32_t oe[32], oo[32];
+          tc5::tmem_ld32(o_addr + c * 32, oe);
+          tc5::tmem_ld32(o_addr + D + c * 32, oo);
+          tc5::tmem_wait_ld();
+          if (row_ok) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4)
+              *reinterpret_cast<float4*>(p.part_o + pi * D + c * 32 + i) =
+                  make_float4(__uint_as_float(oe[i]) * se + __uint_as_float(oo[i]) * so,
+                              __uint_as_float(oe[i + 1]) * se + __uint_as_float(oo[i + 1]) * so,
+                              __uint_as_float(oe[i + 2]) * se + __uint_as_float(oo[i + 2]) * so,
+                              __uint_as_float(oe[i + 3]) * se + __uint_as_float(oo[i + 3]) * so);
+          }
         }
         if (row_ok) p.part_ml[pi] = make_float2(Mx, Lsum);
-      }
-    }
-    gt += tiles;
-
-    // ---- end of the item: every role is done with it (TMEM, the Q tile and the ring are free again);
-    // then, per member, the last of its chunk CTAs to arrive merges its partials (split kernel's protocol)
-    __syncthreads();
-    tc5::fence_after_sync();
-    stamp_item(1);
-    auto member_chunks = [&](int mm) -> int {
-      long long c = p.ctx_is_i64 ? reinterpret_cast<const long long*>(p.ctx)[b + mm]
-                                 : (long long)reinterpret_cast<const int*>(p.ctx)[b + mm];
-      if (c > p.max_ctx) c = p.max_ctx;
-      return (int)((c + p.chunk - 1) / p.chunk);
-    };
-    if (p.counters != nullptr) {
-      // lane m of warp 0 counts member m's arrival (the eight-odd members' atomics in parallel, not one
-      // thread after the other: that loop cost 5 us per item)
-      if (warp == 0) {
+        tc5::fence_before_sync();
         __threadfence();
-        bool last = false;
-        if (lane < nmem) {
-          const int na = member_chunks(lane);
-          int* cnt = p.counters + (long long)(b + lane) * X + x;
-          if (atomicAdd(cnt, 1) == na - 1) {
-            *cnt = 0;
-            last = true;
+        __syncwarp();
+        if (lane == 0) {
+          tc5::mbar_arrive(bar_drain);  // the next item's first products may overwrite the accumulators
+          stamp_item(n, 1);
+          if (n + 1 < my_items) {  // hand the item to the finishers (its last one is finished by the whole CTA)
+            if (n > 0) tc5::mbar_wait_bounded(bar_fin, (n - 1) & 1u);  // they are through with the one before
+            tc5::mbar_arrive(bar_done);
           }
         }
-        const uint32_t last_mask = __ballot_sync(0xffffffffu, last);
-        if (last_mask) __threadfence();
-        if (lane == 0) asm volatile("st.shared.u32 [%0], %1;" ::"r"(flag), "r"(last_mask) : "memory");
+        __syncwarp();
       }
-      __syncthreads();
-      const uint32_t last_mask = lds_word(flag);
-      stamp_item(2);
-      if (last_mask != 0) {
-        // Merge of the members this CTA completed: 32 rows x D/4 columns of float4 = 8 (row, column) items
-        // per thread.  All of a thread's items advance together, two partials at a time, so 16 loads
-        // are in flight per thread instead of one item's four (the merge of a whole sub-group took
-        // up to 86 us as eight dependent passes per thread); every item still folds in chunk order.
-        constexpr int IT = 32 * (D / 4) / 256;
-        float Mx[IT], Ls[IT], a0[IT], a1[IT], a2[IT], a3[IT];
-        long long pi0[IT];
-        int na_i[IT];
-        int na_max = 0;
-#pragma unroll
-        for (int u = 0; u < IT; ++u) {
-          const int itx = tid + u * 256;
-          const int r = itx / (D / 4);
-          const int mm = r >> p.gp_shift, hd = r & gp_mask;
-          const bool ok = mm < nmem && hd < g_valid && ((last_mask >> mm) & 1u);
-          na_i[u] = ok ? member_chunks(mm) : 0;
-          pi0[u] = ((long long)(b + (ok ? mm : 0)) * p.H + head0 + (ok ? hd : 0)) * p.max_splits;
-          Mx[u] = -INFINITY;
-          Ls[u] = a0[u] = a1[u] = a2[u] = a3[u] = 0.f;
-          na_max = max(na_max, na_i[u]);
-        }
-        for (int s0 = 0; s0 < na_max; s0 += 2) {
-          float2 ml[IT][2];
-          float4 v[IT][2];
-#pragma unroll
-          for (int u = 0; u < IT; ++u) {
-            const int dq = (tid + u * 256) % (D / 4);
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-              const int sidx = min(s0 + k, max(na_i[u] - 1, 0));
-              ml[u][k] = __ldcg(p.part_ml + pi0[u] + sidx);
-              v[u][k] = __ldcg(reinterpret_cast<const float4*>(p.part_o + (pi0[u] + sidx) * D + dq * 4));
-            }
-          }
-#pragma unroll
-          for (int u = 0; u < IT; ++u) {
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-              if (s0 + k < na_i[u]) {
-                const float Mn = fmaxf(Mx[u], ml[u][k].x);
-                const float so = fast_exp2(Mx[u] - Mn), sn = fast_exp2(ml[u][k].x - Mn);
-                Ls[u] = Ls[u] * so + ml[u][k].y * sn;
-                a0[u] = a0[u] * so + v[u][k].x * sn;
-                a1[u] = a1[u] * so + v[u][k].y * sn;
-                a2[u] = a2[u] * so + v[u][k].z * sn;
-                a3[u] = a3[u] * so + v[u][k].w * sn;
-                Mx[u] = Mn;
-              }
-            }
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < IT; ++u) {
-          if (na_i[u] == 0) continue;
-          const int itx = tid + u * 256;
-          const int r = itx / (D / 4), dq = itx % (D / 4);
-          const int mm = r >> p.gp_shift, hd = r & gp_mask;
-          const float inv = 1.f / Ls[u];
-          store_out4<T, D>(p, b + mm, head0 + hd, dq * 4, a0[u] * inv, a1[u] * inv, a2[u] * inv, a3[u] * inv);
-        }
-      }
-      __syncthreads();  // the flag word is rewritten by the next item
-      stamp_item(3);
-      if (p.dbg_times != nullptr && tid == 0 && items_done < 4) p.dbg_times[192 + (blockIdx.x * 4 + items_done) * 5 + 4] = last_mask;
+      gt += tiles;
     }
-    tc5::fence_before_sync();
+  } else if (warp >= 5) {
+    // ================================================================ finishers (96 threads): all items but the last
+    const int ft = tid - 160;
+    uint32_t n = 0;
+    for (long long item = blockIdx.x; n + 1 < my_items; item += use_ctas, ++n) {
+      const Item it = item_of(item);
+      tc5::mbar_wait_bounded(bar_done, n & 1u);
+      finish(it, n, ft, 96, 2);
+      if (ft == 0) tc5::mbar_arrive(bar_fin);
+    }
   }
 
+  // ---- the CTA's last item is finished by everybody: nothing is left to overlap it with
+  tc5::fence_before_sync();
+  __syncthreads();
+  finish(item_of(blockIdx.x + (long long)(my_items - 1) * use_ctas), my_items - 1, tid, 256, 3);
+  tc5::fence_before_sync();
   __syncthreads();
   if (warp == 2) tc5::tmem_dealloc(tmem, C::TMEM_COLS);
 }
