@@ -564,7 +564,12 @@ def run_ours(args, rank, world, local_rank):
     alg = workloads.algorithmic_bytes(t, kvh_local=w["KVH"], h_local=w["H"])
     alg_unique = workloads.algorithmic_bytes(t, kvh_local=w["KVH"], h_local=w["H"], unique=True)
     achieved = alg_unique / (kern_ms * 1e-3) / 1e9
-    roof = {"bound": "hbm", "kernel": "paged_decode_split_kernel" + (
+    # a prefix-sharing step is four launches: the pre-pass (lcp_kernel, group_kernel), the kernel of the shared
+    # chunks and the split kernel; its roofline figure is the step's (unique bytes over all of them)
+    wide_share = share and args.share_prefix != "narrow"
+    roof = {"bound": "hbm", "kernel": ("lcp_kernel + group_kernel + " + (
+                "paged_decode_group_kernel (mma.sync)" if args.share_prefix == "mma" else "paged_decode_group_tc5_kernel (tcgen05)")
+                + " + " if wide_share else "lcp_kernel + group_kernel + " if share else "") + "paged_decode_split_kernel" + (
                 "" if args.unfused else " (store and combine fused in)"), "achieved": achieved, "peak": peak,
             "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
             "frac_note": ("frac > 1: the measured peak is a read+write copy (MEASURED_PEAKS.json), this kernel almost only "
@@ -577,7 +582,7 @@ def run_ours(args, rank, world, local_rank):
     # measured DRAM bytes per launch exist only for the exact (workload, shard, kernel) ncu captured
     shard_n = world if world > 1 else args.shard_of
     math_key = "ffma2" if (args.cuda_cores or args.tma or sp.dtype == "f32") else "mma"
-    traffic_key = f"{args.workload}/shard{shard_n}/{math_key}/{args.kernel}" + ("/share" if share else "")
+    traffic_key = f"{args.workload}/shard{shard_n}/{math_key}/{args.kernel}" + (("/share" if args.share_prefix in ("auto", "on") else "/share-" + args.share_prefix) if share else "")
     roof["traffic_key"] = traffic_key
     # a read-only stream through a library reduction over the same K cache, timed the same way: what a
     # kernel that only reads can reach on this box (the copy-measured peak is not a ceiling for it)
@@ -629,7 +634,7 @@ def run_ours(args, rank, world, local_rank):
                            else "mma.sync m16n8k16 (tensor cores)"},
         "hbm_gbs_step": alg_unique / (ms_step * 1e-3) / 1e9,
         "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "parity": parity, "sustained": sustained,
-        "gpu_launches": K * ((3 if multi_split else 2) if args.unfused else 1),
+        "gpu_launches": K * (((3 if multi_split else 2) if args.unfused else 1) + (3 if wide_share else 2 if share else 0)),
         "clocks": clocks.summary(),
     }
     if world == 1 and args.workload == "c3" and args.shard_of == 1 and not args.no_neighbours:
