@@ -11,21 +11,28 @@
 // quarter of the members and lets all four walk every tile: a tile crosses L2 -> SM once, but costs four
 // warps' worth of ldmatrix + mma.sync + softmax per byte, and C5's shared chunks run issue-bound at about
 // half the HBM rate.  Here the sub-group's (member, head) pairs — at most 32 — are the ROWS of one
-// M = 128 accumulator tile, a 128-token K/V tile is the N (scores) and then the K (P.V) dimension:
-//   S (128 x 128 fp32, TMEM) = Q (rows x D, smem)  . K_tile^T (128 tokens x D, smem)     D/16 tcgen05.mma
-//   O (128 x D  fp32, TMEM) += P (rows x 128, TMEM) . V_tile   (128 tokens x D, smem)     8 tcgen05.mma
+// M = 128 accumulator tile, a 64-token K/V tile is the N (scores) and then the K (P.V) dimension:
+//   S (128 x 64 fp32, TMEM) = Q (rows x D, smem)  . K_tile^T (64 tokens x D, smem)      D/16 tcgen05.mma
+//   O (128 x D fp32, TMEM) += P (rows x 64, TMEM) . V_tile   (64 tokens x D, smem)      4 tcgen05.mma
 // One thread issues all of it; rows 32..127 of the tile are padding the tensor pipe does not miss.
 //
 // Shape of the kernel: one CTA per SM, persistent over the work items (sub-group, kv head, shared chunk)
-// that the device pre-pass listed (prefix_share.cu), 128 threads in four roles:
-//   warp 0  softmax: thread r owns row r = TMEM lane r (member r >> log2 Gp, head r & (Gp - 1)); a score
-//           row arrives with tcgen05.ld, P goes back over the first 64 columns of S as 16-bit pairs
-//   warps 1, 3  K/V producers: a 3-stage ring of (K tile, V tile) = 3 x 64 KB filled with 16-byte cp.async
+// that the device pre-pass listed (prefix_share.cu), 256 threads in roles that each walk the CTA's items on
+// their own and meet only through mbarriers (no CTA-wide barrier between items):
+//   warps 0, 4  softmax of the even / odd tiles, two independent streams (own maximum, sum, O accumulator):
+//           thread r owns row r = TMEM lane r (member r >> log2 Gp, head r & (Gp - 1)); a score row arrives
+//           with tcgen05.ld, P goes back over the first half of its S buffer as 16-bit pairs.  At the end of
+//           an item warp 0 folds the two streams (it reads both accumulators) and writes the item's partials
+//   warps 1, 3  K/V producers: a 6-stage ring of (K tile, V tile) = 6 x 32 KB filled with 16-byte cp.async
 //           copies, rows located through the leader's block-table row (the members' rows agree on these
-//           pages), written in the 128-byte-swizzled layout the MMA descriptors read; "full" barriers
-//           by cp.async.mbarrier.arrive, "empty" barriers armed by tcgen05.commit.  (Q comes by TMA.)
-//   warp 2  lane 0 issues every MMA, in the order QK(j+2), PV(j): the scores of the next two tiles are
-//           computed while this tile's softmax runs (three S buffers in TMEM)
+//           pages; entries prefetched in windows of 32), written in the 128-byte-swizzled layout the MMA
+//           descriptors read; "full" barriers by cp.async.mbarrier.arrive, "empty" barriers armed by
+//           tcgen05.commit.  They run into the next item as soon as the ring has room
+//   warp 2  lane 0 issues every MMA from an event loop (Q.K up to three tiles ahead of P.V, three S buffers
+//           in TMEM) and fetches the next item's Q rows by TMA into the other 4 KB slot of the Q tile
+//   warps 5-7  finishers: count the members' arrivals for the item just written and merge the partials of
+//           the members this CTA completed, while the next item streams; the CTA's last item is finished
+//           by all 256 threads
 // With 192 KB of K/V in flight per SM the loads are never exposed (the first tcgen05 attempt of round 1
 // had one K and one V buffer per CTA and lost to the mma.sync kernel for that reason).
 //
