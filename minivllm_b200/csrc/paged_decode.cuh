@@ -677,17 +677,31 @@ paged_decode_split_kernel(const DecodeParams p, const __grid_constant__ CUtensor
     if (g >= g_valid) continue;
     const long long pi0 = ((long long)b * p.H + head0 + g) * p.max_splits;
     float M = -INFINITY, Lsum = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-    for (int s = 0; s < n_act; ++s) {
-      const float2 ml = __ldcg(p.part_ml + pi0 + s);
-      const float4 v = __ldcg(reinterpret_cast<const float4*>(p.part_o + (pi0 + s) * D + dq * 4));
-      const float Mn = fmaxf(M, ml.x);
-      const float so = fast_exp2(M - Mn), sn = fast_exp2(ml.x - Mn);  // first: exp2(-inf) = 0
-      Lsum = Lsum * so + ml.y * sn;
-      a0 = a0 * so + v.x * sn;
-      a1 = a1 * so + v.y * sn;
-      a2 = a2 * so + v.z * sn;
-      a3 = a3 * so + v.w * sn;
-      M = Mn;
+    // eight partials' loads in flight at a time, folded in chunk order (the merge is the last thing on a
+    // sequence's critical path; see paged_decode_mma.cuh)
+    constexpr int MB = 8;
+    for (int s0 = 0; s0 < n_act; s0 += MB) {
+      float2 ml[MB];
+      float4 v[MB];
+#pragma unroll
+      for (int u = 0; u < MB; ++u) {
+        if (s0 + u < n_act) {
+          ml[u] = __ldcg(p.part_ml + pi0 + s0 + u);
+          v[u] = __ldcg(reinterpret_cast<const float4*>(p.part_o + (pi0 + s0 + u) * D + dq * 4));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < MB; ++u) {
+        if (s0 + u >= n_act) break;
+        const float Mn = fmaxf(M, ml[u].x);
+        const float so = fast_exp2(M - Mn), sn = fast_exp2(ml[u].x - Mn);  // first: exp2(-inf) = 0
+        Lsum = Lsum * so + ml[u].y * sn;
+        a0 = a0 * so + v[u].x * sn;
+        a1 = a1 * so + v[u].y * sn;
+        a2 = a2 * so + v[u].z * sn;
+        a3 = a3 * so + v[u].w * sn;
+        M = Mn;
+      }
     }
     const float inv = 1.f / Lsum;
     store_out4<T, D>(p, b, head0 + g, dq * 4, a0 * inv, a1 * inv, a2 * inv, a3 * inv);

@@ -270,17 +270,29 @@ __global__ void __launch_bounds__(128, 3) paged_decode_group_mma_kernel(const De
     const int na = member_chunks(m);
     const long long pi0 = ((long long)(b + m) * p.H + head0 + hd) * p.max_splits;
     float Mx = -INFINITY, Lsum = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-    for (int sidx = 0; sidx < na; ++sidx) {
-      const float2 ml = __ldcg(p.part_ml + pi0 + sidx);
-      const float4 v = __ldcg(reinterpret_cast<const float4*>(p.part_o + (pi0 + sidx) * D + dq * 4));
-      const float Mn = fmaxf(Mx, ml.x);
-      const float so = fast_exp2(Mx - Mn), sn = fast_exp2(ml.x - Mn);
-      Lsum = Lsum * so + ml.y * sn;
-      a0 = a0 * so + v.x * sn;
-      a1 = a1 * so + v.y * sn;
-      a2 = a2 * so + v.z * sn;
-      a3 = a3 * so + v.w * sn;
-      Mx = Mn;
+    constexpr int MB = 8;  // partials' loads in flight at a time; folded in chunk order
+    for (int s0 = 0; s0 < na; s0 += MB) {
+      float2 ml[MB];
+      float4 v[MB];
+#pragma unroll
+      for (int u = 0; u < MB; ++u) {
+        if (s0 + u < na) {
+          ml[u] = __ldcg(p.part_ml + pi0 + s0 + u);
+          v[u] = __ldcg(reinterpret_cast<const float4*>(p.part_o + (pi0 + s0 + u) * D + dq * 4));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < MB; ++u) {
+        if (s0 + u >= na) break;
+        const float Mn = fmaxf(Mx, ml[u].x);
+        const float so = fast_exp2(Mx - Mn), sn = fast_exp2(ml[u].x - Mn);
+        Lsum = Lsum * so + ml[u].y * sn;
+        a0 = a0 * so + v[u].x * sn;
+        a1 = a1 * so + v[u].y * sn;
+        a2 = a2 * so + v[u].z * sn;
+        a3 = a3 * so + v[u].w * sn;
+        Mx = Mn;
+      }
     }
     const float inv = 1.f / Lsum;
     store_out4<T, D>(p, b + m, head0 + hd, dq * 4, a0 * inv, a1 * inv, a2 * inv, a3 * inv);

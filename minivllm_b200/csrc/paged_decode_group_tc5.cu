@@ -311,7 +311,7 @@ paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const Deco
         // per thread and pass.  All of a thread's items advance together, two partials at a time, so 16
         // loads are in flight per thread instead of one item's four (the merge of a whole sub-group took
         // up to 86 us as eight dependent passes per thread); every item still folds in chunk order.
-        constexpr int IT = 4, NI = 32 * (D / 4);
+        constexpr int IT = 4, PB = 4, NI = 32 * (D / 4);
         for (int base_i = 0; base_i < NI; base_i += nt * IT) {
           float Mx[IT], Ls[IT], a0[IT], a1[IT], a2[IT], a3[IT];
           long long pi0[IT];
@@ -329,14 +329,14 @@ paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const Deco
             Ls[u] = a0[u] = a1[u] = a2[u] = a3[u] = 0.f;
             na_max = max(na_max, na_i[u]);
           }
-          for (int s0 = 0; s0 < na_max; s0 += 2) {
-            float2 ml[IT][2];
-            float4 v[IT][2];
+          for (int s0 = 0; s0 < na_max; s0 += PB) {
+            float2 ml[IT][PB];
+            float4 v[IT][PB];
 #pragma unroll
             for (int u = 0; u < IT; ++u) {
               const int dq = (base_i + ft + u * nt) % (D / 4);
 #pragma unroll
-              for (int k = 0; k < 2; ++k) {
+              for (int k = 0; k < PB; ++k) {
                 const int sidx = min(s0 + k, max(na_i[u] - 1, 0));
                 ml[u][k] = __ldcg(p.part_ml + pi0[u] + sidx);
                 v[u][k] = __ldcg(reinterpret_cast<const float4*>(p.part_o + (pi0[u] + sidx) * D + dq * 4));
@@ -345,7 +345,7 @@ paged_decode_group_tc5_kernel(const __grid_constant__ CUtensorMap mq, const Deco
 #pragma unroll
             for (int u = 0; u < IT; ++u) {
 #pragma unroll
-              for (int k = 0; k < 2; ++k) {
+              for (int k = 0; k < PB; ++k) {
                 if (s0 + k < na_i[u]) {
                   const float Mn = fmaxf(Mx[u], ml[u][k].x);
                   const float so = fast_exp2(Mx[u] - Mn), sn = fast_exp2(ml[u][k].x - Mn);

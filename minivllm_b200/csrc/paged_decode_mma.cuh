@@ -476,20 +476,23 @@ __device__ __forceinline__ void paged_decode_split_mma_body(const DecodeParams& 
     const int na = member_chunks(cm);
     const long long pi0 = ((long long)(b + cm) * p.H + head0 + hd) * p.max_splits;
     float Mx = -INFINITY, Lsum = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-    // four partials' loads in flight at a time (the merge is the last thing on a sequence's critical
-    // path; one dependent L2 round trip per partial would make many-chunk splits pay for it), folded
-    // in chunk order so that the result does not depend on the batching
-    for (int s0 = 0; s0 < na; s0 += 4) {
-      float2 ml[4];
-      float4 v[4];
+    // eight partials' loads in flight at a time (the merge is the last thing on a sequence's critical
+    // path: with one dependent L2 round trip per partial, and still with four per round trip, many-chunk
+    // splits paid for it — C5's 32 chunks: 8 round trips of ~1.5 us behind the last byte streamed),
+    // folded in chunk order so that the result does not depend on the batching
+    constexpr int MB = 8;
+    for (int s0 = 0; s0 < na; s0 += MB) {
+      float2 ml[MB];
+      float4 v[MB];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int sidx = s0 + u < na ? s0 + u : na - 1;
-        ml[u] = __ldcg(p.part_ml + pi0 + sidx);
-        v[u] = __ldcg(reinterpret_cast<const float4*>(p.part_o + (pi0 + sidx) * D + dq * 4));
+      for (int u = 0; u < MB; ++u) {
+        if (s0 + u < na) {
+          ml[u] = __ldcg(p.part_ml + pi0 + s0 + u);
+          v[u] = __ldcg(reinterpret_cast<const float4*>(p.part_o + (pi0 + s0 + u) * D + dq * 4));
+        }
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < MB; ++u) {
         if (s0 + u >= na) break;
         const float Mn = fmaxf(Mx, ml[u].x);
         const float so = fast_exp2(Mx - Mn), sn = fast_exp2(ml[u].x - Mn);
