@@ -763,6 +763,27 @@ def test_prefix_sharing_wide_form_on_tcgen05(cuda_device, dtype, H, KVH, D):
                 _assert_close(got.float().cpu().numpy(), want, dtype)
 
 
+def test_prefix_sharing_tcgen05_many_small_items(cuda_device):
+    """The tcgen05 group kernel with several hundred two- and four-tile work items (32k- and 16k-token shared
+    prefixes cut into 128- / 256-token chunks: up to 6 items per CTA, 130-260 partials per row): its roles run
+    whole items ahead of each other there — copies up to three items in front of the softmax, the finisher
+    warps behind it with merges longer than an item — so every hand-over between them is under load."""
+    from minivllm_b200 import _ext
+    groups = [(32768, [32800, 32769, 33000, 34000, 32900, 33500, 32773, 33333]),
+              (16384, [16400, 16500, 17000, 16385, 16390]), (0, [300])]
+    inp = _aliased_case(77, torch.bfloat16, 8, 2, 128, 16, groups)
+    dev = _dev(inp, cuda_device)
+    want = _oracle(inp).numpy()
+    base = _run(dev, chunk_tokens=256, flags=_ext.DECODE_FUSED_COMBINE | _ext.DECODE_SPLIT_GRID)
+    _assert_close(base.float().cpu().numpy(), want, torch.bfloat16)
+    for chunk in (128, 256):
+        for flags in (_ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX, _ext.DECODE_SHARE_PREFIX):
+            for _ in range(2):
+                got = _run(dev, chunk_tokens=chunk, flags=flags)
+                assert (got.float() - base.float()).abs().max() <= 2e-2
+                _assert_close(got.float().cpu().numpy(), want, torch.bfloat16)
+
+
 def test_prefix_sharing_golden_and_fused_step(cuda_device):
     from minivllm_b200 import _ext
     from minivllm_b200.layers.attention import decode_step
