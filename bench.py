@@ -545,8 +545,9 @@ def run_ours(args, rank, world, local_rank):
         e2e = {"value": B / (e2e_ms * 1e-3), "unit": "tokens/s", "ms_per_step": e2e_ms, "steps": ke,
                "h2d_bytes_per_step": hs.h2d_bytes, "d2h_bytes_per_step": hs.d2h_bytes,
                "api": "HostDecodeStep -> mvl_decode_step_host (per rank: its head shard); k, v, slots, lengths and "
-                      "tables in one pinned H2D copy, q read and result rows written by the kernel across PCIe "
-                      "(device-mapped pinned memory), stream-synchronised every step"}
+                      "tables in one pinned H2D copy, " + ("q read and result rows written" if hs.direct_q else
+                      "q in that copy too (prefix sharing: no PCIe round trip per work item), result rows written") +
+                      " by the kernel across PCIe (device-mapped pinned memory), stream-synchronised every step"}
 
     # a peer wait that gave up (a lost announcement) would show as a multi-second step: say so explicitly
     wait_timeouts = None

@@ -475,10 +475,13 @@ class HostDecodeStep:
     def __init__(self, k_cache: torch.Tensor, v_cache: torch.Tensor, batch: int, max_num_blocks: int,
                  num_heads: int, scale: float, index_dtype: torch.dtype = torch.int64,
                  chunk_tokens: int = 0, flags: int = 0, pieces: Optional[int] = None,
-                 direct_out: bool = True, direct_q: bool = True, direct_kv: bool = True):
+                 direct_out: bool = True, direct_q: Optional[bool] = None, direct_kv: bool = True):
         """``direct_out`` / ``direct_q`` (serial form only; default on): the kernels write the result rows
         straight into the pinned host buffer / read q straight from it over PCIe as they go, instead of
         a separate copy before and after (C3 on B200: 0.856 -> 0.766 ms per step; same bits).
+        ``direct_q`` unset: on, except with ``DECODE_SHARE_PREFIX`` — there every work item of the group
+        kernel and every chunk CTA behind it would start with a PCIe round trip for its q rows (C5 on two
+        boxes: 0.388 / 0.580 ms with q read across PCIe, 0.378 / 0.451 ms with q in the step's copy).
         ``direct_kv``: the new token's k / v rows likewise (read once, by the fused store).
         ``pieces``: how many runs of consecutive sequences the step is cut into so that the copies
         of one run travel while another computes (``mvl_decode_step_host_overlapped``); 1 = the strictly
@@ -520,6 +523,8 @@ class HostDecodeStep:
         self.q_d, self.k_d, self.v_d, self.slot_d, self.ctx_d, self.bt_d = views(self._d_arena)
         self.out_h = torch.empty((batch, num_heads, self.head_dim), dtype=dt, pin_memory=True)
         self.out_d = torch.empty((batch, num_heads, self.head_dim), dtype=dt, device=dev)
+        if direct_q is None:
+            direct_q = not (flags & _ext.DECODE_SHARE_PREFIX)
         self.direct_out, self.direct_q, self.direct_kv = bool(direct_out), bool(direct_q), bool(direct_kv)
         self.pieces = 1 if pieces is None else max(1, min(int(pieces), 8, batch))
         with torch.cuda.device(dev):
