@@ -40,6 +40,23 @@ def test_reference_arm_line():
     assert line["config"] == json.loads(json.dumps(bench.workload_config(args, workloads.build_tables("c3"), 1)))
 
 
+def test_reference_arm_under_torchrun_prints_one_line():
+    """Launched like the CUDA arm at N = 2: rank 0 alone measures and prints, the other rank exits 0 without work."""
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "bench.py"),
+                        "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "1"],
+                       cwd=ROOT, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    assert lines[0]["impl"] == "reference" and lines[0]["n_gpus"] == 2
+    assert lines[0]["config"]["parallelism"] == "kv-head-shard x2"
+
+
 @pytest.mark.skipif(torch.cuda.is_available(), reason="needs a box without a GPU")
 def test_cuda_arm_refuses_without_a_gpu():
     r = _bench("--steps", "1", "--warmup", "1")
