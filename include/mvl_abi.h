@@ -379,7 +379,8 @@ void mvl_debug_set_times(void* buf);
  * v together (the new token's rows, read once by the fused store) and for out (rows written as they
  * complete); slots, lengths and block tables are always copied, the kernels read them many times.  Same
  * results bit for bit; on B200 it takes 0.09 ms off a 0.86 ms step (C3), because neither the q copy in
- * front of the kernel nor the result copy behind it is exposed.
+ * front of the kernel nor the result copy behind it is exposed.  (With MVL_DECODE_SHARE_PREFIX prefer q in
+ * the copy: the shared-chunk kernel fetches q rows once per work item, a PCIe round trip each time.)
  */
 int mvl_decode_step_host(const void* q_host, const void* k_host, const void* v_host,
                          const void* slot_mapping_host, const void* context_lens_host,
