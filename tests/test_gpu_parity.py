@@ -814,3 +814,62 @@ def test_prefix_sharing_golden_and_fused_step(cuda_device):
                        dev["block_tables"], dev["context_lens"], inp["scale"], inp["H"], KVH, D, BS,
                        chunk_tokens=64, flags=flags)     # 4 sequences > 8/G = 2: the group kernel's case
     assert (wide.float() - outs[0].float()).abs().max() <= 2e-2
+
+def test_random_problems_against_the_oracle(cuda_device):
+    """Eighty seeded random problems through the C ABI against oracle/paged_oracle.c: group sizes 1-8, both head
+    dims, page sizes from 1 slot to 256, ragged lengths with empty and one-token sequences, stale table tails,
+    aliased prefixes, int32 / int64 lengths, all dtypes, every split size and kernel flag that is a no-op where
+    it does not apply."""
+    from minivllm_b200 import _ext
+    rng = np.random.RandomState(20261107)
+    flag_sets = [0, _ext.DECODE_FUSED_COMBINE, _ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX,
+                 _ext.DECODE_SHARE_PREFIX, _ext.DECODE_CUDA_CORES, _ext.DECODE_CUDA_CORES | _ext.DECODE_FUSED_COMBINE,
+                 _ext.DECODE_CUDA_CORES | _ext.DECODE_LOAD_TMA, _ext.DECODE_FUSED_COMBINE | _ext.DECODE_STREAM,
+                 _ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX | _ext.DECODE_GROUP_MMA,
+                 _ext.DECODE_FUSED_COMBINE | _ext.DECODE_SHARE_PREFIX | _ext.DECODE_SHARE_NARROW]
+    for case in range(80):
+        B, KVH = int(rng.randint(1, 10)), int(rng.randint(1, 5))
+        G = int(rng.choice([1, 2, 3, 4, 6, 8]))
+        D = int(rng.choice([64, 128]))
+        BS = int(rng.choice([1, 2, 8, 16, 16, 32, 256]))
+        dtype = [torch.float32, torch.bfloat16, torch.float16][int(rng.randint(3))]
+        H = KVH * G
+        hi = int(rng.choice([40, 300, 1500]))
+        ctx = rng.randint(0, hi + 1, size=B)
+        if case % 4 == 0:
+            ctx[rng.randint(B)] = 1
+        nblk = (ctx + BS - 1) // BS
+        width = int(nblk.max()) + int(rng.randint(0, 3)) + 1
+        pool = int(nblk.sum()) + 2
+        perm = rng.permutation(pool)
+        tables = np.full((B, width), -1, dtype=np.int32)
+        at = 0
+        for b in range(B):
+            tables[b, :nblk[b]] = perm[at:at + nblk[b]]
+            at += nblk[b]
+        if case % 3 == 0 and B > 1:          # aliased prefixes: later sequences start with the first one's whole blocks
+            for b in range(1, B):
+                share = min(int(ctx[0]) // BS, max(int(ctx[b]) - 1, 0) // BS)
+                tables[b, :share] = tables[0, :share]
+        if case % 2:                         # stale entries behind a sequence's last block
+            for b in range(B):
+                tables[b, nblk[b]:] = rng.randint(0, pool, size=width - nblk[b])
+        g = torch.Generator().manual_seed(case)
+        inp = dict(q=torch.randn(B, H, D, generator=g).to(dtype),
+                   k_cache=torch.randn(pool, BS, KVH, D, generator=g).to(dtype),
+                   v_cache=torch.randn(pool, BS, KVH, D, generator=g).to(dtype),
+                   block_tables=torch.from_numpy(tables),
+                   context_lens=torch.from_numpy(ctx.astype(np.int64 if case % 5 else np.int32)),
+                   scale=float(rng.choice([1.0 / D ** 0.5, 0.05, 0.3])), H=H, KVH=KVH, D=D, BS=BS)
+        want = _oracle(inp).numpy()
+        flags = flag_sets[case % len(flag_sets)]
+        chunk = int(rng.choice([0, 64, 128, 256, 1024]))
+        what = f"case {case}: B={B} KVH={KVH} G={G} D={D} BS={BS} {dtype} ctx={ctx.tolist()} flags={flags} chunk={chunk}"
+        dev = _dev(inp, cuda_device)
+        for _ in range(2):                   # twice: counters and work lists must be left clean
+            got = _run(dev, flags=flags, chunk_tokens=chunk).float().cpu().numpy()
+            assert np.isfinite(got).all(), what
+            a, r = TOL_EXACT[dtype]
+            excess = np.abs(got.astype(np.float64) - want) - (a + r * np.abs(want))
+            assert excess.max() <= 0, f"{what}: max abs err {np.abs(got - want).max():.3e}"
+            assert not got[ctx == 0].any(), what
