@@ -35,6 +35,38 @@ def test_library_exports_every_declared_symbol():
     assert sorted(_ext.PROTOTYPES) == names, "ctypes binding and header disagree"
 
 
+def _ctype_of(param, ret=False):
+    import ctypes as C
+    t = param.strip()
+    if t in ("void", ""):
+        return None
+    if "*" in t:
+        return C.c_char_p if (ret and "char" in t) else C.c_void_p
+    t = re.sub(r"\b(const|[a-z_][a-z_0-9]*)$", lambda m: m.group(0) if m.group(0) in
+               ("int", "float", "unsigned", "size_t", "int64_t", "int32_t", "const") else "", t).replace("const", "").strip()
+    return {"int": C.c_int, "float": C.c_float, "unsigned": C.c_uint, "unsigned int": C.c_uint, "size_t": C.c_size_t,
+            "int64_t": C.c_int64, "int32_t": C.c_int32}[t]
+
+
+def test_ctypes_prototypes_match_the_header_argument_by_argument():
+    """Every declaration of include/mvl_abi.h, parsed: return type and each parameter's type class (pointer, int,
+    int64_t, size_t, float, unsigned) equal the ctypes prototype the Python side calls through — a swapped or
+    missing argument in the binding would otherwise pass garbage without any error."""
+    text = open(os.path.join(ROOT, "include", "mvl_abi.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    text = re.sub(r"//[^\n]*", "", text)
+    decls = re.findall(r"([A-Za-z_][A-Za-z_0-9 \*]*?)\b(mvl_[a-z0-9_]+)\s*\(([^;{}]*)\)\s*;", text)
+    assert len(decls) == len(_ext.PROTOTYPES)
+    for ret, name, params in decls:
+        want_ret = _ctype_of(ret, ret=True)
+        want_args = [c for c in (_ctype_of(x) for x in params.split(",")) if c is not None]
+        got_ret, got_args = _ext.PROTOTYPES[name]
+        assert got_ret == want_ret, f"{name}: return type"
+        assert len(got_args) == len(want_args), f"{name}: {len(got_args)} arguments bound, {len(want_args)} declared"
+        for i, (g, w) in enumerate(zip(got_args, want_args)):
+            assert g == w, f"{name}: argument {i} bound as {g.__name__}, declared as {w.__name__}"
+
+
 def test_abi_version_and_strerror():
     lib = _ext.lib()
     assert lib.mvl_abi_version() == _ext.ABI_VERSION
