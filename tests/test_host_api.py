@@ -67,6 +67,50 @@ def test_ctypes_prototypes_match_the_header_argument_by_argument():
             assert g == w, f"{name}: argument {i} bound as {g.__name__}, declared as {w.__name__}"
 
 
+def test_header_is_plain_c_and_the_library_is_callable_from_c(tmp_path):
+    """The boundary is a C ABI: the header must compile as C99 (what cgo / JNI / a Rust bindgen would feed on), and
+    a C program that only has the header and the .so must be able to call it (argument validation needs no GPU)."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    inc = os.path.join(ROOT, "include")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-pedantic", "-fsyntax-only", "-x", "c",
+                    os.path.join(inc, "mvl_abi.h")], check=True, capture_output=True)
+    src = tmp_path / "use_abi.c"
+    src.write_text(r"""
+#include <dlfcn.h>
+#include <stdio.h>
+#include <string.h>
+#include "mvl_abi.h"
+typedef int (*version_fn)(void);
+typedef const char* (*strerror_fn)(int);
+typedef int (*store_fn)(const void*, const void*, void*, void*, const void*, int, int64_t, int, int, int64_t,
+                        int64_t, int64_t, int, void*);
+int main(int argc, char** argv) {
+  void* h = dlopen(argv[1], RTLD_NOW);
+  if (!h) { fprintf(stderr, "%s\n", dlerror()); return 2; }
+  version_fn version = (version_fn)dlsym(h, "mvl_abi_version");
+  strerror_fn err = (strerror_fn)dlsym(h, "mvl_strerror");
+  store_fn store = (store_fn)dlsym(h, "mvl_store_kvcache");
+  if (!version || !err || !store) return 3;
+  if (version() != MVL_ABI_VERSION) return 4;
+  if (strcmp(err(MVL_OK), "ok") != 0) return 5;
+  if (store(0, 0, 0, 0, 0, 1, 0, 8, 128, 1024, 1024, 64, MVL_DTYPE_BF16, 0) != MVL_OK) return 6;     /* no tokens */
+  if (store(0, 0, 0, 0, 0, 1, 4, 8, 128, 1024, 1024, 64, MVL_DTYPE_BF16, 0) != MVL_ERR_NULL_POINTER) return 7;
+  if (store(0, 0, 0, 0, 0, 1, 4, 8, 128, 1024, 1024, 64, 9, 0) != MVL_ERR_DTYPE) return 8;
+  printf("abi %d\n", version());
+  return 0;
+}
+""")
+    exe = tmp_path / "use_abi"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", inc, str(src), "-o", str(exe), "-ldl"], check=True,
+                   capture_output=True)
+    r = subprocess.run([str(exe), _ext.LIB_PATH], capture_output=True, text=True)
+    assert r.returncode == 0, (r.returncode, r.stderr)
+    assert r.stdout.strip() == f"abi {_ext.ABI_VERSION}"
+
+
 def test_abi_version_and_strerror():
     lib = _ext.lib()
     assert lib.mvl_abi_version() == _ext.ABI_VERSION
